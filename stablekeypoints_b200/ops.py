@@ -1,0 +1,344 @@
+"""Tensor-level wrappers over the C ABI (one function per entry point of include/skp_b200.h),
+plus the torch.autograd.Function glue.  PyTorch is plumbing here: allocation, streams,
+autograd bookkeeping.  All arithmetic runs in libskp_b200.so.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import _lib
+from ._lib import AttnLayer, call, ptr, stream_of
+
+
+def _f32(t: torch.Tensor) -> torch.Tensor:
+    if not t.is_cuda:
+        raise RuntimeError("stablekeypoints_b200 kernels need CUDA tensors (there is no CPU fallback)")
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"expected float32, got {t.dtype}")
+    return t.contiguous()
+
+
+def _guard(t: torch.Tensor):
+    return torch.cuda.device(t.device)
+
+
+# --------------------------------------------------------------------------------------
+# (2) readout
+# --------------------------------------------------------------------------------------
+def plane_argmax(maps: torch.Tensor, return_values: bool = False):
+    """First flat argmax per plane (`eval.py:39-60`).  maps (N,H,W) -> int64 (N)."""
+    maps = _f32(maps)
+    n, h, w = maps.shape
+    idx = torch.empty(n, dtype=torch.int64, device=maps.device)
+    val = torch.empty(n, dtype=torch.float32, device=maps.device) if return_values else None
+    with _guard(maps):
+        call("skp_plane_argmax", ptr(maps), n, h, w, ptr(idx), ptr(val), stream_of(maps))
+    return (idx, val) if return_values else idx
+
+
+def find_k_max_pixels(maps: torch.Tensor, num: int) -> torch.Tensor:
+    maps = _f32(maps)
+    n, h, w = maps.shape
+    out = torch.empty(num, n, 2, dtype=torch.float32, device=maps.device)
+    with _guard(maps):
+        call("skp_find_k_max_pixels", ptr(maps), n, h, w, num, ptr(out), stream_of(maps))
+    return out
+
+
+def weighted_avg_readout(maps: torch.Tensor, distance: float = 5.0, mutate: bool = False) -> torch.Tensor:
+    if mutate and not (maps.is_contiguous() and maps.dtype == torch.float32):
+        raise RuntimeError("in-place windowing needs a contiguous float32 tensor")
+    maps = _f32(maps)
+    n, h, w = maps.shape
+    out = torch.empty(n, 2, dtype=torch.float32, device=maps.device)
+    with _guard(maps):
+        call("skp_weighted_avg_readout", ptr(maps), n, h, w, float(distance), int(mutate), ptr(out), stream_of(maps))
+    return out
+
+
+def plane_stats(maps: torch.Tensor, sigma: float = 2.0, epsilon: float = 1e-5, num_subjects: int = 1,
+                want_kl: bool = True, want_entropy: bool = False, want_argmax: bool = False):
+    """Per-plane KL(gaussian || pixel-softmax) / pixel entropy / argmax in one launch."""
+    maps = _f32(maps)
+    n, h, w = maps.shape
+    dev = maps.device
+    kl = torch.empty(n, dtype=torch.float32, device=dev) if want_kl else None
+    ent = torch.empty(n, dtype=torch.float32, device=dev) if want_entropy else None
+    am = torch.empty(n, dtype=torch.int64, device=dev) if want_argmax else None
+    with _guard(maps):
+        call("skp_plane_stats", ptr(maps), n, h, w, float(sigma), float(epsilon), int(num_subjects),
+             ptr(kl), ptr(ent), ptr(am), stream_of(maps))
+    return kl, ent, am
+
+
+def gaussian_circles(pos: torch.Tensor, size: int, sigma: float) -> torch.Tensor:
+    pos = _f32(pos)
+    s, n, _ = pos.shape
+    out = torch.empty(n, size, size, dtype=torch.float32, device=pos.device)
+    with _guard(pos):
+        call("skp_gaussian_circles", ptr(pos), s, n, size, float(sigma), ptr(out), stream_of(pos))
+    return out
+
+
+# --------------------------------------------------------------------------------------
+# (3) selection
+# --------------------------------------------------------------------------------------
+def rank_ascending(score: torch.Tensor, top_k: int) -> torch.Tensor:
+    score = _f32(score)
+    out = torch.empty(top_k, dtype=torch.int64, device=score.device)
+    with _guard(score):
+        call("skp_rank_ascending", ptr(score), score.numel(), top_k, ptr(out), stream_of(score))
+    return out
+
+
+def furthest_point_sampling(argmax_flat: torch.Tensor, h: int, w: int, candidates: torch.Tensor, top_k: int,
+                            assume_unique: bool = True) -> torch.Tensor:
+    """`ptp_utils.py:115-159` on precomputed per-plane argmax indices.  With unique candidates
+    (always true for ranked lists) exactly top_k ids come back and no host sync is needed;
+    otherwise the count is read back, as the reference returns fewer ids when candidates run out."""
+    if argmax_flat.dtype != torch.int64 or candidates.dtype != torch.int64:
+        raise RuntimeError("indices must be int64")
+    candidates = candidates.contiguous()
+    if candidates.numel() < 2:
+        raise NameError("furthest_pair")   # what the reference raises (ptp_utils.py:140)
+    k = min(top_k, candidates.numel())
+    out = torch.empty(k, dtype=torch.int64, device=argmax_flat.device)
+    n_out = torch.zeros(1, dtype=torch.int32, device=argmax_flat.device)
+    with _guard(argmax_flat):
+        call("skp_furthest_point_sampling", ptr(argmax_flat.contiguous()), argmax_flat.numel(), h, w, ptr(candidates),
+             candidates.numel(), k, ptr(out), ptr(n_out), stream_of(argmax_flat))
+    if assume_unique:
+        return out
+    return out[: int(n_out.item())]
+
+
+# --------------------------------------------------------------------------------------
+# resampling
+# --------------------------------------------------------------------------------------
+def bilinear_upsample(x: torch.Tensor, size: int) -> torch.Tensor:
+    x = _f32(x)
+    lead = x.shape[:-2]
+    h, w = x.shape[-2:]
+    n = int(torch.tensor(lead).prod()) if len(lead) else 1
+    out = torch.empty(*lead, size, size, dtype=torch.float32, device=x.device)
+    with _guard(x):
+        call("skp_bilinear_upsample", ptr(x), n, h, w, ptr(out), size, size, stream_of(x))
+    return out
+
+
+def bicubic_upsample_nhwc(x: torch.Tensor, size: int) -> torch.Tensor:
+    x = _f32(x)
+    b, s, s2, c = x.shape
+    assert s == s2
+    out = torch.empty(b, size, size, c, dtype=torch.float32, device=x.device)
+    with _guard(x):
+        call("skp_bicubic_upsample_nhwc", ptr(x), b, s, c, ptr(out), size, stream_of(x))
+    return out
+
+
+def invert_theta(theta: torch.Tensor) -> torch.Tensor:
+    """Closed-form inverse of the augmented affine (`invertable_transform.py:77-84`); (..,2,3)."""
+    a, b, c = theta[..., 0, 0], theta[..., 0, 1], theta[..., 0, 2]
+    d, e, f = theta[..., 1, 0], theta[..., 1, 1], theta[..., 1, 2]
+    det = a * e - b * d
+    return torch.stack([torch.stack([e / det, -b / det, (b * f - c * e) / det], dim=-1),
+                        torch.stack([-d / det, a / det, (c * d - a * f) / det], dim=-1)], dim=-2)
+
+
+class _AffineWarp(torch.autograd.Function):
+    """grid_sample(img, affine_grid(theta)) — `invertable_transform.py:64-68, 86-90`."""
+
+    @staticmethod
+    def forward(ctx, img, theta):
+        img = _f32(img)
+        theta = _f32(theta.to(img.device))
+        n, c, h, w = img.shape
+        out = torch.empty_like(img)
+        with _guard(img):
+            call("skp_affine_warp", ptr(img), ptr(theta), n, c, h, w, ptr(out), stream_of(img))
+        ctx.save_for_backward(theta)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        (theta,) = ctx.saved_tensors
+        g = _f32(g)
+        n, c, h, w = g.shape
+        d = torch.zeros_like(g)
+        with _guard(g):
+            call("skp_affine_warp_bwd", ptr(g), ptr(theta), n, c, h, w, ptr(d), stream_of(g))
+        return d, None
+
+
+def affine_warp(img: torch.Tensor, theta: torch.Tensor) -> torch.Tensor:
+    return _AffineWarp.apply(img, theta)
+
+
+# --------------------------------------------------------------------------------------
+# (4) losses
+# --------------------------------------------------------------------------------------
+class _KeypointLosses(torch.autograd.Function):
+    """(sharpening, equivariance) of `optimize.py:157-206` on the selected planes, fused.
+
+    maps_a / maps_b are the FULL (T,H,W) maps; idx selects the K planes inside the kernel, so
+    the (K,H,W) gathers of `optimize.py:420-424` are never materialised.  The backward writes
+    compact (K,H,W) gradients and scatters them into (T,H,W) zeros (what autograd of the
+    reference's `attn_map[idx]` produces)."""
+
+    @staticmethod
+    def forward(ctx, maps_a, maps_b, idx, theta_inv, sigma, num_subjects):
+        maps_a = _f32(maps_a)
+        t, h, w = maps_a.shape
+        k = idx.numel()
+        idx = idx.to(device=maps_a.device, dtype=torch.int64).contiguous()
+        if maps_b is not None:
+            maps_b = _f32(maps_b)
+            theta_inv = _f32(theta_inv.to(maps_a.device)).reshape(2, 3)
+        parts = torch.empty(k, 2, dtype=torch.float32, device=maps_a.device)
+        with _guard(maps_a):
+            call("skp_keypoint_losses_fwd", ptr(maps_a), ptr(maps_b), ptr(idx), k, h, w, ptr(theta_inv), float(sigma),
+                 int(num_subjects), ptr(parts), stream_of(maps_a))
+        ctx.save_for_backward(maps_a, maps_b, idx, theta_inv)
+        ctx.cfg = (float(sigma), int(num_subjects))
+        tot = parts.sum(dim=0) / float(k * h * w)
+        return tot[0], tot[1]
+
+    @staticmethod
+    def backward(ctx, g_sharp, g_equiv):
+        maps_a, maps_b, idx, theta_inv = ctx.saved_tensors
+        sigma, ns = ctx.cfg
+        t, h, w = maps_a.shape
+        k = idx.numel()
+        d_a = torch.empty(k, h, w, dtype=torch.float32, device=maps_a.device)
+        d_b = torch.zeros(k, h, w, dtype=torch.float32, device=maps_a.device) if maps_b is not None else None
+        # upstream scalars are read on the host: two floats per step
+        gs, ge = float(g_sharp), float(g_equiv)
+        with _guard(maps_a):
+            call("skp_keypoint_losses_bwd", ptr(maps_a), ptr(maps_b), ptr(idx), k, h, w, ptr(theta_inv), sigma, ns,
+                 gs, ge, ptr(d_a), ptr(d_b), stream_of(maps_a))
+        ga = torch.zeros_like(maps_a).index_add_(0, idx, d_a)
+        gb = torch.zeros_like(maps_b).index_add_(0, idx, d_b) if maps_b is not None else None
+        return ga, gb, None, None, None, None
+
+
+def keypoint_losses(maps_a, maps_b, idx, theta_inv, sigma: float, num_subjects: int = 1):
+    """-> (mean sharpening loss, mean equivariance loss) for one image."""
+    return _KeypointLosses.apply(maps_a, maps_b, idx, theta_inv, sigma, num_subjects)
+
+
+# --------------------------------------------------------------------------------------
+# (5) TTA ensemble
+# --------------------------------------------------------------------------------------
+def tta_accumulate(maps: torch.Tensor, theta_inv: torch.Tensor, sum_: torch.Tensor, num_: torch.Tensor) -> None:
+    """maps (A,K,h,w) feature-resolution planes; sum_/num_ (K,H,W) updated in place."""
+    maps = _f32(maps)
+    a, k, h, w = maps.shape
+    kk, H, W = sum_.shape
+    assert kk == k and num_.shape == sum_.shape
+    theta_inv = _f32(theta_inv.to(maps.device)).reshape(a, 6)
+    with _guard(maps):
+        call("skp_tta_accumulate", ptr(maps), ptr(theta_inv), a, k, h, w, ptr(sum_), ptr(num_), H, W, stream_of(maps))
+
+
+def tta_finalize(sum_: torch.Tensor, num_: torch.Tensor) -> torch.Tensor:
+    out = torch.empty_like(sum_)
+    with _guard(sum_):
+        call("skp_tta_finalize", ptr(sum_), ptr(num_), sum_.numel(), ptr(out), stream_of(sum_))
+    return out
+
+
+# --------------------------------------------------------------------------------------
+# (1) fused attention maps
+# --------------------------------------------------------------------------------------
+def _layer_array(qs, ks, heads, scales, weights, dqs=None, dks=None):
+    arr = (AttnLayer * len(qs))()
+    for i, (q, k) in enumerate(zip(qs, ks)):
+        b, n, c = q.shape
+        s = int(round(n ** 0.5))
+        if s * s != n:
+            raise RuntimeError(f"layer {i}: q has {n} positions, not a square")
+        if k.shape[-1] != c or k.shape[0] not in (1, b):
+            raise RuntimeError(f"layer {i}: k shape {tuple(k.shape)} does not match q {tuple(q.shape)}")
+        arr[i].q = q.data_ptr()
+        arr[i].k = k.data_ptr()
+        arr[i].dq = dqs[i].data_ptr() if dqs is not None else None
+        arr[i].dk = dks[i].data_ptr() if dks is not None else None
+        arr[i].s, arr[i].C, arr[i].heads = s, c, int(heads[i])
+        arr[i].k_shared = int(k.shape[0] == 1 and b > 1)
+        arr[i].scale, arr[i].weight = float(scales[i]), float(weights[i])
+    return arr
+
+
+def _workspace(arr, n_layers, B, T, R, prec, device):
+    need = _lib.load().skp_attn_map_workspace_bytes(arr, n_layers, B, T, R, prec)
+    return torch.empty(max(int(need), 16), dtype=torch.uint8, device=device), int(need)
+
+
+class _AttentionMaps(torch.autograd.Function):
+    """maps[b,t,p] = sum_l w_l * mean_head softmax_t(scale_l q'_l k_l^T) — replaces the captured branch of the
+    patched forward (`ptp_utils.py:508-538`) and `collect_maps` (`optimize.py:27-79`).  Saved for
+    backward: q, k only (the reference keeps 262-655 MB of probabilities per layer alive)."""
+
+    @staticmethod
+    def forward(ctx, meta, token_idx, *tensors):
+        heads, scales, weights, R, prec = meta
+        n = len(heads)
+        qs = [_f32(t) for t in tensors[:n]]
+        ks = [_f32(t) for t in tensors[n:]]
+        B, T = qs[0].shape[0], ks[0].shape[1]
+        dev = qs[0].device
+        if token_idx is not None:
+            token_idx = token_idx.to(device=dev, dtype=torch.int64).contiguous()
+        t_out = token_idx.numel() if token_idx is not None else T
+        maps = torch.empty(B, t_out, R, R, dtype=torch.float32, device=dev)
+        arr = _layer_array(qs, ks, heads, scales, weights)
+        with _guard(maps):
+            ws, nbytes = _workspace(arr, n, B, T, R, prec, dev)
+            call("skp_attn_map_fwd", arr, n, B, T, R, ptr(token_idx), t_out if token_idx is not None else 0, ptr(maps),
+                 None, prec, ptr(ws), nbytes, stream_of(maps))
+        ctx.save_for_backward(token_idx, *qs, *ks)
+        ctx.meta = meta
+        return maps
+
+    @staticmethod
+    def backward(ctx, g):
+        heads, scales, weights, R, prec = ctx.meta
+        n = len(heads)
+        token_idx = ctx.saved_tensors[0]
+        qs = list(ctx.saved_tensors[1:1 + n])
+        ks = list(ctx.saved_tensors[1 + n:])
+        B, T = qs[0].shape[0], ks[0].shape[1]
+        dev = g.device
+        g = _f32(g)
+        # the losses touch K selected planes only (optimize.py:420-424): find them, compact them
+        live = (g.abs().amax(dim=(0, 2, 3)) > 0).nonzero().flatten()
+        dqs = [torch.zeros_like(q) for q in qs]
+        dks = [torch.zeros_like(k) for k in ks]
+        if live.numel():
+            tok = live if token_idx is None else token_idx[live]
+            arr = _layer_array(qs, ks, heads, scales, weights, dqs, dks)
+            chunk = max(1, min(32, min(q.shape[-1] // h for q, h in zip(qs, heads))))
+            with _guard(g):
+                ws, nbytes = _workspace(arr, n, B, T, R, prec, dev)
+                for i in range(0, live.numel(), chunk):
+                    sel = live[i:i + chunk]
+                    dsel = g.index_select(1, sel).contiguous()
+                    call("skp_attn_map_bwd", arr, n, B, T, R, ptr(tok[i:i + chunk].contiguous()), sel.numel(), ptr(dsel),
+                         prec, ptr(ws), nbytes, stream_of(g))
+        return (None, None, *dqs, *dks)
+
+
+def attention_maps(qs: Sequence[torch.Tensor], ks: Sequence[torch.Tensor], heads: Sequence[int], scales: Sequence[float],
+                   feature_res: int, token_idx: Optional[torch.Tensor] = None, weights: Optional[Sequence[float]] = None,
+                   precision: str = "auto") -> torch.Tensor:
+    """qs[l] (B, s_l^2, C_l) low-resolution to_q(x); ks[l] (B or 1, T, C_l) to_k(context).
+    -> (B, T', R, R) with T' = len(token_idx) or T.  Differentiable w.r.t. every q and k."""
+    n = len(qs)
+    if weights is None:
+        weights = [1.0 / n] * n
+    meta = (tuple(int(h) for h in heads), tuple(float(s) for s in scales), tuple(float(w) for w in weights),
+            int(feature_res), _lib.PRECISIONS[precision])
+    return _AttentionMaps.apply(meta, token_idx, *qs, *ks)

@@ -1,0 +1,55 @@
+"""CPU-side checks of the drop-in boundary: the C-ABI library loads and exports exactly the
+symbols include/skp_b200.h declares (no compute calls: there is no GPU here)."""
+import ctypes
+import os
+import re
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _header_symbols():
+    text = open(os.path.join(ROOT, "include", "skp_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(skp_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    from stablekeypoints_b200 import _lib
+    assert os.path.exists(_lib.LIB_PATH), "run ./build.sh (or __graft_entry__.build()) first"
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    declared = _header_symbols()
+    assert len(declared) >= 20
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in skp_b200.h but not exported"
+    assert sorted(_lib.SIGNATURES) == declared, "ctypes signatures out of sync with the header"
+    out = subprocess.run(["nm", "-D", "--defined-only", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    exported = sorted(set(re.findall(r" T (skp_[a-z0-9_]+)", out)))
+    assert exported == declared, "library exports symbols the header does not declare"
+
+
+def test_library_binds_and_reports_version():
+    from stablekeypoints_b200 import _lib
+    lib = _lib.load()
+    assert lib.skp_version() == 100
+    assert isinstance(lib.skp_last_error(), bytes)
+
+
+def test_cpu_tensors_are_refused():
+    import torch
+    from stablekeypoints_b200 import ops
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ops.plane_argmax(torch.rand(2, 8, 8))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ops.attention_maps([torch.rand(1, 16, 32)], [torch.rand(1, 5, 32)], [2], [0.25], 8)
+
+
+def test_product_package_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "stablekeypoints_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith(".py"):
+                src = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f"{f} imports oracle/"

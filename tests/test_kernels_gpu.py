@@ -1,0 +1,223 @@
+"""Parity of the CUDA kernels (through the C ABI) against the CPU oracle and the committed
+golden vectors produced by the live reference.  Run on the B200 box: pytest -m gpu.
+
+Tolerances (stated per north_star): integer outputs (argmax pixels, ranked / FPS token ids)
+bit-exact; attention maps rtol 1e-3 in the fp32-grade modes (simt_f32, tc_bf16x3), bf16 mode
+rtol 3e-2; soft-argmax keypoints 0.5 px.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import keypoint_oracle as O
+
+pytestmark = pytest.mark.gpu
+G = os.path.join(os.path.dirname(__file__), "golden")
+DEV = "cuda:0"
+
+
+def _load(name):
+    return {k: v for k, v in np.load(os.path.join(G, name)).items()}
+
+
+def _cu(x):
+    return torch.as_tensor(x).to(DEV)
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from stablekeypoints_b200 import ops as _ops
+    return _ops
+
+
+def _golden_layers():
+    d = _load("attention_maps.npz")
+    qs = [torch.from_numpy(d[f"q_low{i}"])[None] for i in range(4)]
+    ks = [torch.from_numpy(d[f"k{i}"])[None] for i in range(4)]
+    return d, qs, ks, [int(h) for h in d["heads"]], [float(s) for s in d["scale"]], int(d["R"])
+
+
+@pytest.mark.parametrize("precision,rtol", [("simt_f32", 1e-3), ("auto", 1e-3)])
+def test_attention_maps_golden(ops, precision, rtol):
+    d, qs, ks, heads, sc, R = _golden_layers()
+    A = ops.attention_maps([_cu(q) for q in qs], [_cu(k) for k in ks], heads, sc, R, precision=precision)[0]
+    ref = torch.from_numpy(d["ref_maps_A"])
+    assert torch.allclose(A.cpu(), ref, rtol=rtol, atol=1e-7)
+    assert torch.allclose(A.sum(0).cpu(), torch.ones(R, R), atol=1e-5)
+    Bm = ops.bilinear_upsample(A[:8].contiguous(), 128)
+    assert torch.allclose(Bm.cpu(), torch.from_numpy(d["ref_maps_B"]), rtol=rtol, atol=1e-7)
+    idx = torch.from_numpy(d["indices"])
+    Cm = ops.attention_maps([_cu(q) for q in qs], [_cu(k) for k in ks], heads, sc, R, token_idx=_cu(idx), precision=precision)[0]
+    assert torch.allclose(Cm.cpu(), ref[idx], rtol=rtol, atol=1e-7)
+    assert torch.allclose(ops.bilinear_upsample(Cm, 128).cpu(), torch.from_numpy(d["ref_maps_C"]), rtol=rtol, atol=1e-7)
+
+
+def _random_layers(spec, T, B, seed, shared_k=True):
+    g = torch.Generator().manual_seed(seed)
+    qs, ks, heads, scales = [], [], [], []
+    for (s, C, h) in spec:
+        qs.append(torch.randn(B, s * s, C, generator=g) * 1.5)
+        ks.append(torch.randn(1 if shared_k else B, T, C, generator=g))
+        heads.append(h)
+        scales.append((C // h) ** -0.5)
+    return qs, ks, heads, scales
+
+
+@pytest.mark.parametrize("precision", ["simt_f32", "auto"])
+@pytest.mark.parametrize("spec,T,R,B,shared", [
+    ([(4, 64, 4), (4, 64, 4), (8, 32, 2)], 37, 16, 2, True),          # unequal heads, ragged T
+    ([(8, 128, 2), (16, 64, 4), (32, 32, 2)], 130, 32, 1, False),     # three scales incl. s == R
+    ([(4, 96, 2)], 500, 16, 3, True),                                 # dim_head 48, full token count
+])
+def test_attention_maps_vs_oracle_unequal_heads(ops, precision, spec, T, R, B, shared):
+    qs, ks, heads, sc = _random_layers(spec, T, B, 3, shared)
+    got = ops.attention_maps([_cu(q) for q in qs], [_cu(k) for k in ks], heads, sc, R, precision=precision).cpu()
+    for b in range(B):
+        want = O.attention_maps_from_qk([q[b] for q in qs], [k[0 if shared else b] for k in ks], heads, sc, R)
+        assert torch.allclose(got[b], want, rtol=1e-3, atol=1e-7)
+
+
+def test_attention_maps_backward_matches_oracle_autograd(ops):
+    spec, T, R, B = [(4, 64, 4), (8, 32, 2)], 40, 16, 2
+    qs, ks, heads, sc = _random_layers(spec, T, B, 5, True)
+    idx = torch.tensor([7, 0, 33])
+    g = torch.Generator().manual_seed(9)
+    w = torch.randn(B, len(idx), R, R, generator=g)
+    # oracle in fp64 on CPU
+    q64 = [q.double().requires_grad_(True) for q in qs]
+    k64 = [k.double().requires_grad_(True) for k in ks]
+    loss = 0
+    for b in range(B):
+        m = O.attention_maps_from_qk([q[b] for q in q64], [k[0] for k in k64], heads, sc, R)
+        loss = loss + (m[idx] * w[b].double()).sum()
+    grads = torch.autograd.grad(loss, q64 + k64)
+    qc = [_cu(q).requires_grad_(True) for q in qs]
+    kc = [_cu(k).requires_grad_(True) for k in ks]
+    m = ops.attention_maps(qc, kc, heads, sc, R, precision="simt_f32")
+    (m[:, _cu(idx)] * _cu(w)).sum().backward()
+    for got, want in zip([t.grad for t in qc + kc], grads):
+        scale = float(want.abs().max())
+        assert torch.allclose(got.cpu().double(), want, rtol=2e-3, atol=2e-5 * scale)
+
+
+def test_full_size_properties_sd21_shape(ops):
+    """BASELINE.json config sizes (T=500, R=128, SD-2.1 heads): size-independent properties."""
+    spec = [(16, 1280, 20), (16, 1280, 20), (16, 1280, 20), (32, 640, 10)]
+    qs, ks, heads, sc = _random_layers(spec, 500, 1, 11, True)
+    qc, kc = [_cu(q) for q in qs], [_cu(k) for k in ks]
+    m = ops.attention_maps(qc, kc, heads, sc, 128, precision="auto")
+    assert m.shape == (1, 500, 128, 128)
+    assert torch.allclose(m.sum(1), torch.ones(1, 128, 128, device=DEV), atol=2e-5)   # softmax over tokens then means
+    assert float(m.min()) >= 0.0
+    idx = torch.tensor([499, 0, 250, 3, 77, 12, 498, 100, 9, 301])
+    c = ops.attention_maps(qc, kc, heads, sc, 128, token_idx=_cu(idx), precision="auto")
+    assert torch.allclose(c, m[:, _cu(idx)], rtol=1e-4, atol=1e-8)                  # gather commutes
+    # a few pixels against the fp64 oracle restricted to those pixels is covered by the SIMT cross-check:
+    m2 = ops.attention_maps(qc, kc, heads, sc, 128, precision="simt_f32")
+    assert torch.allclose(m, m2, rtol=1e-3, atol=1e-7)
+    am = ops.plane_argmax(m[0])
+    assert torch.equal(am.cpu(), torch.argmax(m[0].reshape(500, -1), dim=-1).cpu())
+
+
+def test_readout_and_selection_golden(ops):
+    d = _load("selection_readout.npz")
+    m = _cu(d["maps"])
+    n, h, w = m.shape
+    am = ops.plane_argmax(m)
+    rc = torch.stack([am // w, am % w], -1).float() + 0.5
+    assert np.array_equal(rc.cpu().numpy(), d["ref_max_pixel"])
+    assert np.array_equal(ops.find_k_max_pixels(m, 3).cpu().numpy(), d["ref_k_max_pixels3"])
+    wa = ops.weighted_avg_readout(m.clone()).cpu().numpy()
+    assert np.abs(wa - d["ref_weighted_avg"]).max() < 0.5      # north_star: soft-argmax within 0.5 px
+    assert np.allclose(wa, d["ref_weighted_avg"], atol=1e-3)
+    for ns in (1, 2):
+        kl, _, _ = ops.plane_stats(m, sigma=2.0, epsilon=1e-5, num_subjects=ns)
+        assert np.array_equal(ops.rank_ascending(kl, 25).cpu().numpy(), d[f"ref_topk_gaussian_ns{ns}"])
+        kl64 = O.gaussian_kl(torch.from_numpy(d["maps"]), 2.0, 1e-5, ns, dtype=torch.float64)
+        assert torch.allclose(kl.cpu().double(), kl64, rtol=1e-4)
+    _, ent, _ = ops.plane_stats(m, want_kl=False, want_entropy=True)
+    assert np.array_equal(ops.rank_ascending(ent, 25).cpu().numpy(), d["ref_entropy_sort"])
+    cand = _cu(d["ref_topk_gaussian_ns1"])
+    assert np.array_equal(ops.furthest_point_sampling(am, h, w, cand, 10).cpu().numpy(), d["ref_fps"])
+    pos = ops.find_k_max_pixels(m[:6].contiguous(), 2) / 64
+    assert np.allclose(ops.gaussian_circles(pos, 64, 2.0).cpu().numpy(), d["ref_gaussian_circles"], atol=2e-7)
+    m48 = _cu(d["maps48"])
+    am48 = ops.plane_argmax(m48)
+    got = ops.furthest_point_sampling(am48, 48, 48, torch.arange(25, device=DEV), 10)
+    assert np.array_equal(got.cpu().numpy(), d["ref_fps48"])
+
+
+def test_readout_edge_cases(ops):
+    t = torch.zeros(3, 16, 16)
+    t[0, 3, 4] = 1; t[0, 5, 1] = 1            # tie: first flat index wins
+    t[1] = -1.0; t[1, 15, 15] = -0.5           # all negative
+    t[2, 0, 0] = float("nan")                  # NaN counts as the maximum (torch.argmax)
+    am = ops.plane_argmax(_cu(t)).cpu()
+    assert am.tolist() == [3 * 16 + 4, 255, 0]
+    big = torch.rand(10, 512, 512)
+    assert torch.equal(ops.plane_argmax(_cu(big)).cpu(), torch.argmax(big.reshape(10, -1), -1))
+    odd = torch.rand(7, 33, 35)
+    assert torch.equal(ops.plane_argmax(_cu(odd)).cpu(), torch.argmax(odd.reshape(7, -1), -1))
+    s = torch.tensor([0.5, -1.0, 0.5, float("nan"), -0.0, 0.0, 3.0])
+    assert ops.rank_ascending(_cu(s), 7).cpu().tolist() == [1, 4, 5, 0, 2, 6, 3]
+    with pytest.raises(NameError):
+        ops.furthest_point_sampling(_cu(torch.zeros(4, dtype=torch.int64)), 8, 8, _cu(torch.tensor([1])), 2)
+
+
+def test_losses_warps_tta_golden(ops):
+    d = _load("losses_tta.npz")
+    img, theta = _cu(d["img"]), _cu(d["theta"])
+    wimg = ops.affine_warp(img, theta)
+    assert np.allclose(wimg.cpu().numpy(), d["ref_warped"], atol=2e-5)
+    assert np.allclose(ops.affine_warp(wimg, ops.invert_theta(theta)).cpu().numpy(), d["ref_unwarped"], atol=2e-5)
+    a = _cu(d["a"]).requires_grad_(True)
+    b = _cu(d["b"]).requires_grad_(True)
+    idx = torch.arange(10, device=DEV)
+    ls, le = ops.keypoint_losses(a, b, idx, ops.invert_theta(theta[0]), 2.0)
+    assert abs(ls.item() - float(d["ref_sharpening"])) < 1e-5 * abs(float(d["ref_sharpening"]))
+    assert abs(le.item() - float(d["ref_equivariance"])) < 1e-4 * abs(float(d["ref_equivariance"]))
+    (ls * 100 + le * 1000).backward()
+    for got, want in ((a.grad, d["ref_grad_a"]), (b.grad, d["ref_grad_b"])):
+        assert np.allclose(got.cpu().numpy(), want, rtol=1e-3, atol=2e-5 * np.abs(want).max())
+    # sharpening alone, on a subset of planes of a larger stack
+    a2 = _cu(d["a"]).requires_grad_(True)
+    sel = torch.tensor([4, 1, 7])
+    ls2, _ = ops.keypoint_losses(a2, None, _cu(sel), None, 2.0)
+    want = O.sharpening_loss(torch.from_numpy(d["a"])[sel], 2.0)
+    assert abs(ls2.item() - want.item()) < 1e-5 * abs(want.item())
+    # TTA ensemble
+    maps, thetas = _cu(d["tta_maps"]), _cu(d["tta_thetas"])
+    A, K, H, W = maps.shape
+    s_ = torch.zeros(K, H, W, device=DEV); n_ = torch.zeros(K, H, W, device=DEV)
+    ops.tta_accumulate(maps[:2].contiguous(), ops.invert_theta(thetas[:2]), s_, n_)
+    ops.tta_accumulate(maps[2:].contiguous(), ops.invert_theta(thetas[2:]), s_, n_)
+    ens = ops.tta_finalize(s_, n_)
+    assert np.allclose(ens.cpu().numpy(), d["ref_tta"], rtol=1e-4, atol=2e-5)
+    am = ops.plane_argmax(ens)
+    rc = torch.stack([am // W, am % W], -1).float() + 0.5
+    assert np.array_equal(rc.cpu().numpy(), d["ref_tta_keypoints"])
+
+
+def test_tta_with_fused_upsample_matches_oracle(ops):
+    g = torch.Generator().manual_seed(2)
+    maps = torch.rand(3, 4, 32, 32, generator=g)
+    thetas = torch.stack([O.affine_theta(10.0, 0.9, 0.1, -0.05), O.affine_theta(-7.0, 0.85, -0.2, 0.15),
+                          O.affine_theta(0.0, 1.0, 0.0, 0.0)])
+    up = [O.bilinear_upsample(m, 128) for m in maps]
+    want = O.tta_ensemble(up, list(thetas))
+    s_ = torch.zeros(4, 128, 128, device=DEV); n_ = torch.zeros(4, 128, 128, device=DEV)
+    ops.tta_accumulate(_cu(maps), ops.invert_theta(_cu(thetas)), s_, n_)
+    got = ops.tta_finalize(s_, n_).cpu()
+    assert torch.allclose(got, want, rtol=1e-4, atol=2e-5)
+
+
+def test_resampling_matches_oracle(ops):
+    g = torch.Generator().manual_seed(4)
+    x = torch.randn(2, 8, 8, 24, generator=g)
+    want = O.bicubic_upsample(x.permute(0, 3, 1, 2).double(), 32).permute(0, 2, 3, 1)
+    assert torch.allclose(ops.bicubic_upsample_nhwc(_cu(x), 32).cpu().double(), want, atol=1e-5)
+    y = torch.randn(5, 16, 16, generator=g)
+    assert torch.allclose(ops.bilinear_upsample(_cu(y), 64).cpu().double(), O.bilinear_upsample(y.double(), 64), atol=1e-6)
+    assert torch.equal(ops.bilinear_upsample(_cu(y), 16).cpu(), y)
