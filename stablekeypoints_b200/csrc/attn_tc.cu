@@ -1,10 +1,546 @@
-// placeholder until the tcgen05 kernel lands
+// Fused cross-attention-map forward on tcgen05 tensor cores (sm_100a).
+//
+//   maps[b, t, p] = sum_l w_l * mean_head softmax_t( scale_l * q'_l[b,head,p,:] . k_l[head,t,:] )
+//
+// replaces the captured branch of the reference's patched CrossAttention.forward
+// (unsupervised_keypoints/ptp_utils.py:508-538) and collect_maps (optimize.py:27-79).
+//
+// Design (DESIGN.md has the long version):
+//  * prep kernels: bicubic-upsample the module's low-resolution q to R x R, fold scale*log2(e)
+//    in, and write it as bf16 (hi [+ lo residual]) in a K-major [b*h][pixel][d] layout; k likewise
+//    as [h][token][d].  bf16x3 mode (hi*hi + hi*lo + lo*hi, fp32 accumulate) is the fp32-grade
+//    "parity" arithmetic; plain bf16 is the fast mode.
+//  * main kernel: one CTA per (image, 128 consecutive feature pixels, 256-token slice); a
+//    cluster of NSPLIT CTAs covers all tokens of the same pixels.  Warp 0 = TMA producer
+//    (128B-swizzled tiles, mbarrier ring), warp 1 = single-thread tcgen05.mma issuer
+//    (M=128, N=256, K=16, accumulators in TMEM, two 256-column buffers ping-pong across
+//    (layer, head) units), warps 2-9 = softmax: thread (row, column half) reads its logits with
+//    tcgen05.ld, takes max / exp2 / sum, parks the exponentials back in TMEM (tcgen05.st),
+//    exchanges (max, sum) with the other column half and the other CTAs of the cluster
+//    through (distributed) shared memory + mbarriers, then accumulates weight * P into 128
+//    fp32 registers.  The (h, R^2, T) probability tensor never exists; the output is written once.
+#include <cuda.h>
+#include <cuda_bf16.h>
+
 #include "common.cuh"
+#include "ptx_sm100.cuh"
+
 namespace skp {
-bool attn_map_tc_supported(const skp_attn_layer*, int, int, int, int, int) { return false; }
-size_t attn_map_tc_workspace(const skp_attn_layer*, int, int, int, int, int) { return 0; }
-int attn_map_fwd_tc(const skp_attn_layer*, int, int, int, int, const int64_t*, int, float*, float*, int, void*, size_t, cudaStream_t) {
-  set_error("tcgen05 kernel not built");
-  return SKP_ERR_UNSUPPORTED;
+
+constexpr int TC_MAX_LAYERS = 12;
+constexpr int TC_BM = 128;       // pixels per CTA (UMMA M)
+constexpr int TC_BN = 256;       // tokens per CTA (UMMA N)
+constexpr int TC_BK = 64;        // bf16 per k-block = one 128-byte swizzle row
+constexpr int TC_THREADS = 320;  // warp 0 TMA, warp 1 MMA, warps 2..9 softmax
+constexpr int TC_SOFTMAX_THREADS = 256;
+constexpr int TC_MAX_SEL = 32;   // selected-token planes per launch
+constexpr int TC_A_BYTES = TC_BM * TC_BK * 2;   // 16 KB
+constexpr int TC_B_BYTES = TC_BN * TC_BK * 2;   // 32 KB
+
+struct TcParams {
+  CUtensorMap q_map[TC_MAX_LAYERS][2];   // [layer][hi, lo]: dims (d, R*R, B*h), box (64, 128, 1)
+  CUtensorMap k_map[TC_MAX_LAYERS][2];   // [layer][hi, lo]: dims (d, T,   Bk*h), box (64, 256, 1)
+  int heads[TC_MAX_LAYERS], d[TC_MAX_LAYERS], k_shared[TC_MAX_LAYERS];
+  float weight[TC_MAX_LAYERS];           // layer weight / heads
+  int n_layers, T, R2, n_idx;
+  const int64_t* token_idx;
+  float* maps;
+};
+
+// ------------------------------------------------------------------------------------------
+// prep: q (B, s*s, C) fp32 -> bicubic to R x R, * scale*log2e, split to bf16 hi (+lo), laid out
+// [b*h + head][pixel][d]
+// ------------------------------------------------------------------------------------------
+template <int NPROD>
+__global__ void tc_prep_q_kernel(const float* __restrict__ q, int s, int C, int heads, int R, float mult,
+                                 __nv_bfloat16* __restrict__ hi, __nv_bfloat16* __restrict__ lo) {
+  const int p = blockIdx.x, b = blockIdx.y;
+  const int oy = p / R, ox = p % R;
+  const int d = C / heads, R2 = R * R;
+  int iy, ix;
+  float wy[4], wx[4];
+  int yy[4], xx[4];
+  if (s != R) {
+    const float ratio = static_cast<float>(s) / R;
+    bicubic_coeffs(oy, ratio, &iy, wy);
+    bicubic_coeffs(ox, ratio, &ix, wx);
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+      yy[a] = min(max(iy - 1 + a, 0), s - 1);
+      xx[a] = min(max(ix - 1 + a, 0), s - 1);
+    }
+  }
+  const float* src = q + static_cast<int64_t>(b) * s * s * C;
+  for (int cp = threadIdx.x; cp < C / 2; cp += blockDim.x) {
+    const int c = cp * 2;
+    float2 v;
+    if (s == R) {
+      v = *reinterpret_cast<const float2*>(src + static_cast<int64_t>(p) * C + c);
+    } else {
+      v = make_float2(0.f, 0.f);
+#pragma unroll
+      for (int a = 0; a < 4; ++a) {
+        float2 row = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 t = __ldg(reinterpret_cast<const float2*>(src + static_cast<int64_t>(yy[a] * s + xx[e]) * C + c));
+          row.x += wx[e] * t.x;
+          row.y += wx[e] * t.y;
+        }
+        v.x += wy[a] * row.x;
+        v.y += wy[a] * row.y;
+      }
+    }
+    v.x *= mult;
+    v.y *= mult;
+    const int head = c / d, dd = c % d;
+    const int64_t o = ((static_cast<int64_t>(b) * heads + head) * R2 + p) * d + dd;
+    const __nv_bfloat16 hx = __float2bfloat16_rn(v.x), hy = __float2bfloat16_rn(v.y);
+    *reinterpret_cast<__nv_bfloat162*>(hi + o) = __halves2bfloat162(hx, hy);
+    if (NPROD == 3) {
+      *reinterpret_cast<__nv_bfloat162*>(lo + o) =
+          __halves2bfloat162(__float2bfloat16_rn(v.x - __bfloat162float(hx)), __float2bfloat16_rn(v.y - __bfloat162float(hy)));
+    }
+  }
 }
+
+// k (Bk, T, C) fp32 -> bf16 hi (+lo) laid out [bk*h + head][token][d]
+template <int NPROD>
+__global__ void tc_prep_k_kernel(const float* __restrict__ k, int T, int C, int heads, __nv_bfloat16* __restrict__ hi,
+                                 __nv_bfloat16* __restrict__ lo) {
+  const int t = blockIdx.x, bk = blockIdx.y;
+  const int d = C / heads;
+  const float* src = k + (static_cast<int64_t>(bk) * T + t) * C;
+  for (int cp = threadIdx.x; cp < C / 2; cp += blockDim.x) {
+    const int c = cp * 2;
+    const float2 v = *reinterpret_cast<const float2*>(src + c);
+    const int head = c / d, dd = c % d;
+    const int64_t o = ((static_cast<int64_t>(bk) * heads + head) * T + t) * d + dd;
+    const __nv_bfloat16 hx = __float2bfloat16_rn(v.x), hy = __float2bfloat16_rn(v.y);
+    *reinterpret_cast<__nv_bfloat162*>(hi + o) = __halves2bfloat162(hx, hy);
+    if (NPROD == 3) {
+      *reinterpret_cast<__nv_bfloat162*>(lo + o) =
+          __halves2bfloat162(__float2bfloat16_rn(v.x - __bfloat162float(hx)), __float2bfloat16_rn(v.y - __bfloat162float(hy)));
+    }
+  }
 }
+
+}  // namespace skp
+
+namespace skp {
+
+// shared-memory carve-up (offsets from a 1024-byte aligned base)
+template <int NPROD>
+struct TcSmem {
+  static constexpr int kStages = NPROD == 3 ? 2 : 4;
+  static constexpr int kStageBytes = (NPROD == 3 ? 2 : 1) * (TC_A_BYTES + TC_B_BYTES);
+  static constexpr int kTiles = kStages * kStageBytes;                 // 192 KB either way
+  static constexpr int kBarOff = kTiles;                               // full[], empty[], tfull[2], tempty[2], xfull[2]
+  static constexpr int kNumBars = 2 * kStages + 6;
+  static constexpr int kTmemPtrOff = kBarOff + 8 * kNumBars;
+  static constexpr int kTokOff = kTmemPtrOff + 8;                      // int tok[TC_MAX_SEL]
+  static constexpr int kStatsOff = kTokOff + 4 * TC_MAX_SEL;           // float2 stats[2 buf][4 part][128 row]
+  static constexpr int kTotal = kStatsOff + 2 * 4 * TC_BM * 8;
+  static constexpr int kDynamic = kTotal + 1024;                       // slack for manual 1024 B alignment
+};
+
+template <int NPROD, int NSPLIT, bool SELECT>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
+  using SM = TcSmem<NPROD>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = ptx::smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  uint8_t* base_ptr = smem_raw + (base - raw);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t cta_rank = NSPLIT > 1 ? ptx::cluster_ctarank() : 0u;
+  const int tile = blockIdx.x / NSPLIT;
+  const int b = blockIdx.y;
+  const int p0 = tile * TC_BM;
+  const int tok0 = static_cast<int>(cta_rank) * TC_BN;
+
+  auto bar_full = [&](int s) { return base + SM::kBarOff + 8u * s; };
+  auto bar_empty = [&](int s) { return base + SM::kBarOff + 8u * (SM::kStages + s); };
+  auto bar_tfull = [&](int i) { return base + SM::kBarOff + 8u * (2 * SM::kStages + i); };
+  auto bar_tempty = [&](int i) { return base + SM::kBarOff + 8u * (2 * SM::kStages + 2 + i); };
+  auto bar_xfull = [&](int i) { return base + SM::kBarOff + 8u * (2 * SM::kStages + 4 + i); };
+  volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(base_ptr + SM::kTmemPtrOff);
+  int* tok_s = reinterpret_cast<int*>(base_ptr + SM::kTokOff);
+  float2* stats = reinterpret_cast<float2*>(base_ptr + SM::kStatsOff);
+
+  // ---- one-time setup ---------------------------------------------------------------------
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < SM::kStages; ++s) {
+      ptx::mbar_init(bar_full(s), 1);
+      ptx::mbar_init(bar_empty(s), 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(bar_tfull(i), 1);
+      ptx::mbar_init(bar_tempty(i), TC_SOFTMAX_THREADS);
+      ptx::mbar_init(bar_xfull(i), TC_SOFTMAX_THREADS * NSPLIT);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (SELECT && threadIdx.x < TC_MAX_SEL) tok_s[threadIdx.x] = threadIdx.x < P.n_idx ? static_cast<int>(P.token_idx[threadIdx.x]) : -1;
+  if (warp == 1) {
+    ptx::tmem_alloc(ptx::smem_u32(const_cast<uint32_t*>(tmem_ptr)), 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (NSPLIT > 1) ptx::cluster_sync();   // peers' barriers are initialised before any remote arrive
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // =========================== TMA producer (one lane) ===================================
+    if (lane == 0) {
+      for (int l = 0; l < P.n_layers; ++l) {
+        ptx::prefetch_tensormap(&P.q_map[l][0]);
+        ptx::prefetch_tensormap(&P.k_map[l][0]);
+        if (NPROD == 3) {
+          ptx::prefetch_tensormap(&P.q_map[l][1]);
+          ptx::prefetch_tensormap(&P.k_map[l][1]);
+        }
+      }
+      uint32_t it = 0;
+      for (int l = 0; l < P.n_layers; ++l) {
+        const int h = P.heads[l], d = P.d[l];
+        const int nkb = (d + TC_BK - 1) / TC_BK;
+        for (int head = 0; head < h; ++head) {
+          const int qz = b * h + head;
+          const int kz = (P.k_shared[l] ? 0 : b * h) + head;
+          for (int kb = 0; kb < nkb; ++kb, ++it) {
+            const int s = it % SM::kStages;
+            const uint32_t ph = (it / SM::kStages) & 1u;
+            ptx::mbar_wait(bar_empty(s), ph ^ 1u);
+            ptx::mbar_arrive_expect_tx(bar_full(s), SM::kStageBytes);
+            const uint32_t st = base + s * SM::kStageBytes;
+            ptx::tma_load_3d(st, &P.q_map[l][0], bar_full(s), kb * TC_BK, p0, qz);
+            ptx::tma_load_3d(st + TC_A_BYTES, &P.k_map[l][0], bar_full(s), kb * TC_BK, tok0, kz);
+            if (NPROD == 3) {
+              ptx::tma_load_3d(st + TC_A_BYTES + TC_B_BYTES, &P.q_map[l][1], bar_full(s), kb * TC_BK, p0, qz);
+              ptx::tma_load_3d(st + 2 * TC_A_BYTES + TC_B_BYTES, &P.k_map[l][1], bar_full(s), kb * TC_BK, tok0, kz);
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // =========================== MMA issuer (one lane) =====================================
+    if (lane == 0) {
+      constexpr uint32_t idesc = ptx::umma_idesc_bf16(TC_BM, TC_BN);
+      uint32_t it = 0, u = 0;
+      for (int l = 0; l < P.n_layers; ++l) {
+        const int h = P.heads[l], d = P.d[l];
+        const int nkb = (d + TC_BK - 1) / TC_BK;
+        for (int head = 0; head < h; ++head, ++u) {
+          const uint32_t buf = u & 1u;
+          ptx::mbar_wait(bar_tempty(buf), ((u >> 1) & 1u) ^ 1u);   // softmax drained this TMEM buffer
+          ptx::tc_fence_after();
+          const uint32_t d_tmem = tmem_base + buf * TC_BN;
+          for (int kb = 0; kb < nkb; ++kb, ++it) {
+            const int s = it % SM::kStages;
+            ptx::mbar_wait(bar_full(s), (it / SM::kStages) & 1u);
+            ptx::tc_fence_after();
+            const uint32_t st = base + s * SM::kStageBytes;
+            const int nk16 = (min(TC_BK, d - kb * TC_BK) + 15) / 16;
+            for (int kk = 0; kk < nk16; ++kk) {
+              const uint64_t a_hi = ptx::umma_desc_sw128(st + kk * 32);
+              const uint64_t b_hi = ptx::umma_desc_sw128(st + TC_A_BYTES + kk * 32);
+              const uint32_t first = (kb | kk) != 0;
+              if (NPROD == 3) {
+                const uint64_t a_lo = ptx::umma_desc_sw128(st + TC_A_BYTES + TC_B_BYTES + kk * 32);
+                const uint64_t b_lo = ptx::umma_desc_sw128(st + 2 * TC_A_BYTES + TC_B_BYTES + kk * 32);
+                ptx::umma_bf16(d_tmem, a_hi, b_lo, idesc, first);
+                ptx::umma_bf16(d_tmem, a_lo, b_hi, idesc, 1u);
+                ptx::umma_bf16(d_tmem, a_hi, b_hi, idesc, 1u);
+              } else {
+                ptx::umma_bf16(d_tmem, a_hi, b_hi, idesc, first);
+              }
+            }
+            ptx::umma_commit(bar_empty(s));      // smem slot free once these MMAs retire
+          }
+          ptx::umma_commit(bar_tfull(buf));      // logits of this (layer, head) are in TMEM
+        }
+      }
+    }
+  } else {
+    // =========================== softmax / accumulate warps =================================
+    const int quad = warp & 3;                 // TMEM lane quadrant this warp may access
+    const int ch = (warp - 2) >> 2;            // column half of the CTA's 256 tokens
+    const int row = quad * 32 + lane;
+    const int col0 = ch * 128;
+    const int ncol = max(0, min(128, P.T - (tok0 + col0)));
+    const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+    const int part = static_cast<int>(cta_rank) * 2 + ch;
+    constexpr int NPART = 2 * NSPLIT;
+    float acc[SELECT ? TC_MAX_SEL : 128];
+#pragma unroll
+    for (int j = 0; j < (SELECT ? TC_MAX_SEL : 128); ++j) acc[j] = 0.0f;
+
+    uint32_t u = 0;
+    for (int l = 0; l < P.n_layers; ++l) {
+      const int h = P.heads[l];
+      const float wgt = P.weight[l];
+      for (int head = 0; head < h; ++head, ++u) {
+        const uint32_t buf = u & 1u, par = (u >> 1) & 1u;
+        ptx::mbar_wait(bar_tfull(buf), par);
+        ptx::tc_fence_after();
+        const uint32_t taddr = t_lane + buf * TC_BN + col0;
+        uint32_t v[32];
+        // ---- pass A: row max over my columns
+        float m = -INFINITY;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          if (ncol > 32 * c) {
+            ptx::tmem_ld32(taddr + 32 * c, v);
+            ptx::tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (32 * c + j < ncol) m = fmaxf(m, __uint_as_float(v[j]));
+          }
+        }
+        // ---- pass B: exponentials (parked back in TMEM) and their sum
+        float sum = 0.0f;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          if (ncol > 32 * c) {
+            ptx::tmem_ld32(taddr + 32 * c, v);
+            ptx::tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const float e = (32 * c + j < ncol) ? ptx::ex2(__uint_as_float(v[j]) - m) : 0.0f;
+              sum += e;
+              v[j] = __float_as_uint(e);
+            }
+            if (!SELECT) ptx::tmem_st32(taddr + 32 * c, v);
+          }
+        }
+        if (!SELECT) ptx::tmem_st_wait();
+        // ---- exchange (max, sum) with the other column half and the other CTAs of the cluster
+        {
+          const uint32_t slot = base + SM::kStatsOff + ((buf * 4 + part) * TC_BM + row) * 8;
+          if (NSPLIT == 1) {
+            stats[(buf * 4 + part) * TC_BM + row] = make_float2(m, sum);
+            ptx::mbar_arrive(bar_xfull(buf));
+            ptx::mbar_wait(bar_xfull(buf), par);
+          } else {
+#pragma unroll
+            for (uint32_t dst = 0; dst < static_cast<uint32_t>(NSPLIT); ++dst) {
+              ptx::st_cluster_v2(ptx::mapa(slot, dst), m, sum);
+              ptx::mbar_arrive_cluster(ptx::mapa(bar_xfull(buf), dst));
+            }
+            ptx::mbar_wait_cluster(bar_xfull(buf), par);
+          }
+        }
+        float mg = -INFINITY;
+#pragma unroll
+        for (int q = 0; q < NPART; ++q) mg = fmaxf(mg, stats[(buf * 4 + q) * TC_BM + row].x);
+        float total = 0.0f;
+#pragma unroll
+        for (int q = 0; q < NPART; ++q) {
+          const float2 sq = stats[(buf * 4 + q) * TC_BM + row];
+          total += sq.y * ptx::ex2(sq.x - mg);
+        }
+        const float cf = ncol > 0 ? wgt * ptx::ex2(m - mg) / total : 0.0f;
+        // ---- pass C: accumulate weight/heads * P
+        if (!SELECT) {
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            if (ncol > 32 * c) {
+              ptx::tmem_ld32(taddr + 32 * c, v);
+              ptx::tmem_ld_wait();
+#pragma unroll
+              for (int j = 0; j < 32; ++j) acc[32 * c + j] = fmaf(cf, __uint_as_float(v[j]), acc[32 * c + j]);
+            }
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < TC_MAX_SEL; ++j) {
+            const int t = tok_s[j] - tok0 - col0;   // warp-uniform
+            if (j < P.n_idx && t >= 0 && t < ncol) {
+              const uint32_t sv = ptx::tmem_ld1(taddr + t);
+              ptx::tmem_ld_wait();
+              acc[j] = fmaf(cf, ptx::ex2(__uint_as_float(sv) - m), acc[j]);
+            }
+          }
+        }
+        ptx::tc_fence_before();
+        ptx::mbar_arrive(bar_tempty(buf));
+      }
+    }
+    // ---- write-out: lanes hold consecutive pixels -> 128 B coalesced stores per token
+    if (!SELECT) {
+      float* out = P.maps + (static_cast<int64_t>(b) * P.T + tok0 + col0) * P.R2 + p0 + row;
+#pragma unroll
+      for (int j = 0; j < 128; ++j)
+        if (j < ncol) out[static_cast<int64_t>(j) * P.R2] = acc[j];
+    } else {
+#pragma unroll
+      for (int j = 0; j < TC_MAX_SEL; ++j) {
+        const int t = tok_s[j] - tok0 - col0;
+        if (j < P.n_idx && t >= 0 && t < ncol) P.maps[(static_cast<int64_t>(b) * P.n_idx + j) * P.R2 + p0 + row] = acc[j];
+      }
+    }
+  }
+
+  // ---- teardown -------------------------------------------------------------------------------
+  __syncwarp();
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (NSPLIT > 1) ptx::cluster_sync();   // nobody exits while a peer may still store into its smem
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+}  // namespace skp
+
+// ==========================================================================================
+// host side
+// ==========================================================================================
+namespace skp {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || !p) return nullptr;
+    fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// bf16 tensor [batch][rows][d] (d contiguous) -> 3-D map with a (64, box_rows, 1) box, 128B swizzle
+static int encode_map(CUtensorMap* m, void* ptr, int d, int rows, int batch, int box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) {
+    set_error("cuTensorMapEncodeTiled entry point not available");
+    return SKP_ERR_CUDA;
+  }
+  cuuint64_t dims[3] = {static_cast<cuuint64_t>(d), static_cast<cuuint64_t>(rows), static_cast<cuuint64_t>(batch)};
+  cuuint64_t strides[2] = {static_cast<cuuint64_t>(d) * 2, static_cast<cuuint64_t>(d) * 2 * rows};
+  cuuint32_t box[3] = {static_cast<cuuint32_t>(TC_BK), static_cast<cuuint32_t>(box_rows), 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed with CUresult %d (d=%d rows=%d batch=%d)", static_cast<int>(r), d, rows, batch);
+    return SKP_ERR_CUDA;
+  }
+  return SKP_OK;
+}
+
+bool attn_map_tc_supported(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int n_idx) {
+  if (!h_layers || n_layers < 1 || n_layers > TC_MAX_LAYERS || B < 1 || B > 65535) return false;
+  if (T < 1 || T > 2 * TC_BN || (static_cast<int64_t>(R) * R) % TC_BM != 0) return false;
+  if (n_idx > TC_MAX_SEL) return false;
+  for (int l = 0; l < n_layers; ++l) {
+    const skp_attn_layer& a = h_layers[l];
+    if (a.heads < 1 || a.C % a.heads != 0) return false;
+    const int d = a.C / a.heads;
+    if (d % 16 != 0 || d > 512 || a.s < 1 || R % a.s != 0) return false;
+  }
+  return true;
+}
+
+static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+size_t attn_map_tc_workspace(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int precision) {
+  const int nbuf = precision == SKP_PREC_TC_BF16 ? 1 : 2;
+  size_t total = 0;
+  for (int l = 0; l < n_layers; ++l) {
+    const skp_attn_layer& a = h_layers[l];
+    total += nbuf * align_up(static_cast<size_t>(B) * R * R * a.C * 2, 1024);
+    total += nbuf * align_up(static_cast<size_t>(a.k_shared ? 1 : B) * T * a.C * 2, 1024);
+  }
+  return total + 1024;
+}
+
+template <int NPROD, int NSPLIT, bool SELECT>
+static int launch_tc(const TcParams& P, int B, int R2, cudaStream_t st) {
+  using SM = TcSmem<NPROD>;
+  auto kern = attn_map_fwd_tc_kernel<NPROD, NSPLIT, SELECT>;
+  SKP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::kDynamic));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(static_cast<unsigned>(R2 / TC_BM * NSPLIT), static_cast<unsigned>(B), 1);
+  cfg.blockDim = dim3(TC_THREADS, 1, 1);
+  cfg.dynamicSmemBytes = SM::kDynamic;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = NSPLIT;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = NSPLIT > 1 ? 1 : 0;
+  SKP_CUDA(cudaLaunchKernelEx(&cfg, kern, P));
+  return SKP_OK;
+}
+
+int attn_map_fwd_tc(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, const int64_t* token_idx, int n_idx,
+                    float* maps, float* row_stats, int precision, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+  (void)row_stats;
+  const size_t need = attn_map_tc_workspace(h_layers, n_layers, B, T, R, precision);
+  if (!workspace || workspace_bytes < need) {
+    set_error("skp_attn_map_fwd: workspace %zu B < required %zu B", workspace_bytes, need);
+    return SKP_ERR_WORKSPACE;
+  }
+  const bool x3 = precision != SKP_PREC_TC_BF16;
+  const int R2 = R * R;
+  TcParams P;
+  memset(&P, 0, sizeof(P));
+  char* ws = reinterpret_cast<char*>(align_up(reinterpret_cast<size_t>(workspace), 1024));
+  for (int l = 0; l < n_layers; ++l) {
+    const skp_attn_layer& a = h_layers[l];
+    SKP_REQUIRE(a.q && a.k, "skp_attn_map_fwd: layer %d has null q/k", l);
+    const int d = a.C / a.heads;
+    const int Bk = a.k_shared ? 1 : B;
+    const size_t qbytes = align_up(static_cast<size_t>(B) * R2 * a.C * 2, 1024);
+    const size_t kbytes = align_up(static_cast<size_t>(Bk) * T * a.C * 2, 1024);
+    __nv_bfloat16* q_hi = reinterpret_cast<__nv_bfloat16*>(ws); ws += qbytes;
+    __nv_bfloat16* q_lo = nullptr;
+    if (x3) { q_lo = reinterpret_cast<__nv_bfloat16*>(ws); ws += qbytes; }
+    __nv_bfloat16* k_hi = reinterpret_cast<__nv_bfloat16*>(ws); ws += kbytes;
+    __nv_bfloat16* k_lo = nullptr;
+    if (x3) { k_lo = reinterpret_cast<__nv_bfloat16*>(ws); ws += kbytes; }
+    const float mult = a.scale * 1.4426950408889634f;
+    dim3 gq(R2, B), gk(T, Bk);
+    if (x3) {
+      tc_prep_q_kernel<3><<<gq, 256, 0, st>>>(a.q, a.s, a.C, a.heads, R, mult, q_hi, q_lo);
+      tc_prep_k_kernel<3><<<gk, 256, 0, st>>>(a.k, T, a.C, a.heads, k_hi, k_lo);
+    } else {
+      tc_prep_q_kernel<1><<<gq, 256, 0, st>>>(a.q, a.s, a.C, a.heads, R, mult, q_hi, q_lo);
+      tc_prep_k_kernel<1><<<gk, 256, 0, st>>>(a.k, T, a.C, a.heads, k_hi, k_lo);
+    }
+    SKP_LAUNCH_CHECK();
+    int rc = encode_map(&P.q_map[l][0], q_hi, d, R2, B * a.heads, TC_BM);
+    if (rc == SKP_OK) rc = encode_map(&P.k_map[l][0], k_hi, d, T, Bk * a.heads, TC_BN);
+    if (rc == SKP_OK && x3) rc = encode_map(&P.q_map[l][1], q_lo, d, R2, B * a.heads, TC_BM);
+    if (rc == SKP_OK && x3) rc = encode_map(&P.k_map[l][1], k_lo, d, T, Bk * a.heads, TC_BN);
+    if (rc != SKP_OK) return rc;
+    P.heads[l] = a.heads; P.d[l] = d; P.k_shared[l] = a.k_shared;
+    P.weight[l] = a.weight / a.heads;
+  }
+  P.n_layers = n_layers; P.T = T; P.R2 = R2;
+  P.n_idx = token_idx ? n_idx : 0;
+  P.token_idx = token_idx; P.maps = maps;
+  const bool sel = token_idx != nullptr;
+  const bool split = T > TC_BN;
+  if (x3) {
+    if (split) return sel ? launch_tc<3, 2, true>(P, B, R2, st) : launch_tc<3, 2, false>(P, B, R2, st);
+    return sel ? launch_tc<3, 1, true>(P, B, R2, st) : launch_tc<3, 1, false>(P, B, R2, st);
+  }
+  if (split) return sel ? launch_tc<1, 2, true>(P, B, R2, st) : launch_tc<1, 2, false>(P, B, R2, st);
+  return sel ? launch_tc<1, 1, true>(P, B, R2, st) : launch_tc<1, 1, false>(P, B, R2, st);
+}
+
+}  // namespace skp

@@ -32,6 +32,18 @@ def ops():
     return _ops
 
 
+def _assert_rank_equal_up_to_ties(got, want, score64, rel_tol=3e-6):
+    """Ranked ids must be identical except where the fp64 scores of the two candidates for a
+    rank differ by less than rel_tol (the reference's own fp32 sums are not reproducible below
+    that: SURVEY.md 7.3 'bit-exact integer outputs are only well-defined away from ties')."""
+    got, want = np.asarray(got), np.asarray(want)
+    assert got.shape == want.shape
+    for g_, w_ in zip(got, want):
+        if g_ != w_:
+            a, b = float(score64[g_]), float(score64[w_])
+            assert abs(a - b) <= rel_tol * max(abs(a), abs(b)), f"rank mismatch {g_} vs {w_}: scores {a} {b}"
+
+
 def _golden_layers():
     d = _load("attention_maps.npz")
     qs = [torch.from_numpy(d[f"q_low{i}"])[None] for i in range(4)]
@@ -134,11 +146,15 @@ def test_readout_and_selection_golden(ops):
     assert np.allclose(wa, d["ref_weighted_avg"], atol=1e-3)
     for ns in (1, 2):
         kl, _, _ = ops.plane_stats(m, sigma=2.0, epsilon=1e-5, num_subjects=ns)
-        assert np.array_equal(ops.rank_ascending(kl, 25).cpu().numpy(), d[f"ref_topk_gaussian_ns{ns}"])
         kl64 = O.gaussian_kl(torch.from_numpy(d["maps"]), 2.0, 1e-5, ns, dtype=torch.float64)
         assert torch.allclose(kl.cpu().double(), kl64, rtol=1e-4)
+        _assert_rank_equal_up_to_ties(ops.rank_ascending(kl, 25).cpu().numpy(), d[f"ref_topk_gaussian_ns{ns}"], kl64)
     _, ent, _ = ops.plane_stats(m, want_kl=False, want_entropy=True)
-    assert np.array_equal(ops.rank_ascending(ent, 25).cpu().numpy(), d["ref_entropy_sort"])
+    ent64 = O.pixel_entropy(torch.from_numpy(d["maps"]), dtype=torch.float64)
+    assert torch.allclose(ent.cpu().double(), ent64, rtol=1e-6)
+    _assert_rank_equal_up_to_ties(ops.rank_ascending(ent, 25).cpu().numpy(), d["ref_entropy_sort"], ent64)
+    # on identical float scores the ranking kernel itself is exact
+    assert torch.equal(ops.rank_ascending(ent, 25).cpu(), torch.argsort(ent.cpu(), stable=True)[:25])
     cand = _cu(d["ref_topk_gaussian_ns1"])
     assert np.array_equal(ops.furthest_point_sampling(am, h, w, cand, 10).cpu().numpy(), d["ref_fps"])
     pos = ops.find_k_max_pixels(m[:6].contiguous(), 2) / 64
