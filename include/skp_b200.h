@@ -76,11 +76,14 @@ size_t skp_attn_map_workspace_bytes(const skp_attn_layer* h_layers, int n_layers
                                     int precision);
 
 /* maps (B, T', R, R): T' = n_idx when token_idx != NULL (gather, optimize.py:58-59) else T.
+ * token_idx holds n_idx ids for image b at token_idx + b*idx_stride (idx_stride 0: the same
+ * ids for every image, the reference's case; n_idx: one row per image, used when the images
+ * of a batch carry their own selected tokens, optimize.py:403-424).
  * out[b,t,p] = sum_l weight_l * mean_head softmax_t(scale_l * q'_l[b,head,p,:].k_l[b,head,t,:]).
  * row_stats (optional, may be NULL): (B, sum_l heads_l, R*R, 2) = (row max, sum exp) in log2
  * units, consumed by skp_attn_map_bwd. */
 int skp_attn_map_fwd(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R,
-                     const int64_t* token_idx, int n_idx, float* maps, float* row_stats,
+                     const int64_t* token_idx, int n_idx, int64_t idx_stride, float* maps, float* row_stats,
                      int precision, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Backward of the above for a gradient that is non-zero on n_idx token planes only
@@ -88,7 +91,7 @@ int skp_attn_map_fwd(const skp_attn_layer* h_layers, int n_layers, int B, int T,
  * dmaps_sel (B, n_idx, R, R) = d loss / d maps[b, token_idx[j]].  Accumulates into
  * layer.dq / layer.dk.  Linear in dmaps_sel, so callers may chunk planes. */
 int skp_attn_map_bwd(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R,
-                     const int64_t* token_idx, int n_idx, const float* dmaps_sel,
+                     const int64_t* token_idx, int n_idx, int64_t idx_stride, const float* dmaps_sel,
                      int precision, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------

@@ -11,7 +11,7 @@ void set_error(const char* fmt, ...) {
 }
 }  // namespace skp
 
-extern "C" int skp_version(void) { return 100; }
+extern "C" int skp_version(void) { return 101; }
 extern "C" const char* skp_last_error(void) { return skp::g_err; }
 extern "C" int skp_device_arch(int device) {
   cudaDeviceProp p;

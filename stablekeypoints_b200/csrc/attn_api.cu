@@ -2,13 +2,13 @@
 #include "common.cuh"
 
 namespace skp {
-int attn_map_fwd_simt(const skp_attn_layer*, int, int, int, int, const int64_t*, int, float*, float*, cudaStream_t);
-int attn_map_bwd_simt(const skp_attn_layer*, int, int, int, int, const int64_t*, int, const float*, void*, size_t, cudaStream_t);
+int attn_map_fwd_simt(const skp_attn_layer*, int, int, int, int, const int64_t*, int, int64_t, float*, float*, cudaStream_t);
+int attn_map_bwd_simt(const skp_attn_layer*, int, int, int, int, const int64_t*, int, int64_t, const float*, void*, size_t, cudaStream_t);
 size_t attn_map_bwd_simt_workspace(const skp_attn_layer*, int, int, int);
 // tcgen05 path (attn_tc.cu)
 bool attn_map_tc_supported(const skp_attn_layer*, int, int, int, int, int n_idx);
 size_t attn_map_tc_workspace(const skp_attn_layer*, int, int, int, int, int precision);
-int attn_map_fwd_tc(const skp_attn_layer*, int, int, int, int, const int64_t*, int, float*, float*, int precision, void*,
+int attn_map_fwd_tc(const skp_attn_layer*, int, int, int, int, const int64_t*, int, int64_t, float*, float*, int precision, void*,
                     size_t, cudaStream_t);
 }  // namespace skp
 
@@ -29,19 +29,19 @@ extern "C" size_t skp_attn_map_workspace_bytes(const skp_attn_layer* h_layers, i
 }
 
 extern "C" int skp_attn_map_fwd(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, const int64_t* token_idx,
-                                int n_idx, float* maps, float* row_stats, int precision, void* workspace,
+                                int n_idx, int64_t idx_stride, float* maps, float* row_stats, int precision, void* workspace,
                                 size_t workspace_bytes, void* stream) {
   SKP_REQUIRE(maps, "skp_attn_map_fwd: maps is null");
   SKP_REQUIRE(!token_idx || n_idx >= 1, "skp_attn_map_fwd: token_idx given but n_idx < 1");
   int p = resolve_precision(h_layers, n_layers, B, T, R, token_idx ? n_idx : 0, precision);
   if (p == SKP_PREC_SIMT_F32)
-    return attn_map_fwd_simt(h_layers, n_layers, B, T, R, token_idx, n_idx, maps, row_stats, as_stream(stream));
+    return attn_map_fwd_simt(h_layers, n_layers, B, T, R, token_idx, n_idx, idx_stride, maps, row_stats, as_stream(stream));
   if (p == SKP_PREC_TC_BF16 || p == SKP_PREC_TC_BF16X3) {
     if (!attn_map_tc_supported(h_layers, n_layers, B, T, R, token_idx ? n_idx : 0)) {
       set_error("skp_attn_map_fwd: shape not supported by the tcgen05 kernel (need dim_head %% 16 == 0, T <= 512, R*R %% 128 == 0)");
       return SKP_ERR_UNSUPPORTED;
     }
-    return attn_map_fwd_tc(h_layers, n_layers, B, T, R, token_idx, n_idx, maps, row_stats, p, workspace, workspace_bytes,
+    return attn_map_fwd_tc(h_layers, n_layers, B, T, R, token_idx, n_idx, idx_stride, maps, row_stats, p, workspace, workspace_bytes,
                            as_stream(stream));
   }
   set_error("skp_attn_map_fwd: unknown precision %d", precision);
@@ -49,8 +49,8 @@ extern "C" int skp_attn_map_fwd(const skp_attn_layer* h_layers, int n_layers, in
 }
 
 extern "C" int skp_attn_map_bwd(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, const int64_t* token_idx,
-                                int n_idx, const float* dmaps_sel, int precision, void* workspace, size_t workspace_bytes,
+                                int n_idx, int64_t idx_stride, const float* dmaps_sel, int precision, void* workspace, size_t workspace_bytes,
                                 void* stream) {
   (void)precision;   // the backward currently always runs the fp32 CUDA-core kernel
-  return attn_map_bwd_simt(h_layers, n_layers, B, T, R, token_idx, n_idx, dmaps_sel, workspace, workspace_bytes, as_stream(stream));
+  return attn_map_bwd_simt(h_layers, n_layers, B, T, R, token_idx, n_idx, idx_stride, dmaps_sel, workspace, workspace_bytes, as_stream(stream));
 }

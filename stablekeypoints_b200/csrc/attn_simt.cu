@@ -132,7 +132,7 @@ __device__ __forceinline__ void softmax_rows(float* Ss, int lds, int T, float* s
 
 __global__ void __launch_bounds__(SIMT_THREADS, 1)
 attn_map_fwd_simt_kernel(const SimtLayers L, int T, int R, const int64_t* __restrict__ token_idx, int n_idx,
-                         float* __restrict__ maps, float* __restrict__ row_stats) {
+                         int64_t idx_stride, float* __restrict__ maps, float* __restrict__ row_stats) {
   extern __shared__ float smem[];
   const int Tout = token_idx ? n_idx : T;
   const int ldq = L.dmax + 1, ldk = L.dmax + 1, lds = T + 1;
@@ -144,6 +144,7 @@ attn_map_fwd_simt_kernel(const SimtLayers L, int T, int R, const int64_t* __rest
   const int b = blockIdx.y;
   const int p0 = blockIdx.x * SIMT_TP;
   const int R2 = R * R;
+  if (token_idx) token_idx += b * idx_stride;
   for (int e = threadIdx.x; e < Tout * SIMT_TP; e += blockDim.x) Acc[e] = 0.0f;
   for (int l = 0; l < L.n_layers; ++l) {
     const int C = L.C[l], h = L.heads[l], d = C / h, s = L.s[l];
@@ -180,7 +181,7 @@ attn_map_fwd_simt_kernel(const SimtLayers L, int T, int R, const int64_t* __rest
 //   dk[t][c]  += scale * sum_px dS[px][t] q'[px][c]       (atomics across pixel tiles / images)
 __global__ void __launch_bounds__(SIMT_THREADS, 1)
 attn_map_bwd_simt_kernel(const SimtLayers L, int T, int R, const int64_t* __restrict__ token_idx, int n_idx,
-                         const float* __restrict__ dmaps_sel) {
+                         int64_t idx_stride, const float* __restrict__ dmaps_sel) {
   extern __shared__ float smem[];
   const int ldq = L.dmax + 1, ldk = L.dmax + 1, lds = T + 1;
   float* Qs = smem;                          // [TP][ldq]   (unscaled-by-log2e copy kept in Qr)
@@ -191,6 +192,7 @@ attn_map_bwd_simt_kernel(const SimtLayers L, int T, int R, const int64_t* __rest
   const int b = blockIdx.z;
   const int p0 = blockIdx.x * SIMT_TP;
   const int R2 = R * R;
+  token_idx += b * idx_stride;
   int l = 0;
   while (l + 1 < L.n_layers && static_cast<int>(blockIdx.y) >= L.head_base[l + 1]) ++l;
   const int head = blockIdx.y - L.head_base[l];
@@ -340,7 +342,7 @@ int fill_simt_layers(const skp_attn_layer* h_layers, int n_layers, int B, int T,
 }
 
 int attn_map_fwd_simt(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, const int64_t* token_idx,
-                      int n_idx, float* maps, float* row_stats, cudaStream_t st) {
+                      int n_idx, int64_t idx_stride, float* maps, float* row_stats, cudaStream_t st) {
   SimtLayers L;
   int rc = fill_simt_layers(h_layers, n_layers, B, T, R, &L);
   if (rc != SKP_OK) return rc;
@@ -350,7 +352,7 @@ int attn_map_fwd_simt(const skp_attn_layer* h_layers, int n_layers, int B, int T
   SKP_REQUIRE(smem <= 227 * 1024, "attn_map_fwd (SIMT): T=%d, dim_head=%d need %zu B of shared memory (> 227 KB)", T, L.dmax, smem);
   SKP_CUDA(cudaFuncSetAttribute(attn_map_fwd_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
   dim3 grid(R * R / SIMT_TP, B);
-  attn_map_fwd_simt_kernel<<<grid, SIMT_THREADS, smem, st>>>(L, T, R, token_idx, n_idx, maps, row_stats);
+  attn_map_fwd_simt_kernel<<<grid, SIMT_THREADS, smem, st>>>(L, T, R, token_idx, n_idx, idx_stride, maps, row_stats);
   SKP_LAUNCH_CHECK();
   return SKP_OK;
 }
@@ -371,7 +373,8 @@ size_t attn_map_bwd_simt_workspace(const skp_attn_layer* h_layers, int n_layers,
 }
 
 int attn_map_bwd_simt(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, const int64_t* token_idx,
-                      int n_idx, const float* dmaps_sel, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+                      int n_idx, int64_t idx_stride, const float* dmaps_sel, void* workspace, size_t workspace_bytes,
+                      cudaStream_t st) {
   SimtLayers L;
   int rc = fill_simt_layers(h_layers, n_layers, B, T, R, &L);
   if (rc != SKP_OK) return rc;
@@ -394,7 +397,7 @@ int attn_map_bwd_simt(const skp_attn_layer* h_layers, int n_layers, int B, int T
   SKP_CUDA(cudaFuncSetAttribute(attn_map_bwd_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
   SKP_REQUIRE(L.total_heads <= 65535 && B <= 65535, "attn_map_bwd: grid too large");
   dim3 grid(R * R / SIMT_TP, L.total_heads, B);
-  attn_map_bwd_simt_kernel<<<grid, SIMT_THREADS, smem, st>>>(L, T, R, token_idx, n_idx, dmaps_sel);
+  attn_map_bwd_simt_kernel<<<grid, SIMT_THREADS, smem, st>>>(L, T, R, token_idx, n_idx, idx_stride, dmaps_sel);
   SKP_LAUNCH_CHECK();
   for (int l = 0; l < n_layers; ++l) {
     const skp_attn_layer& a = h_layers[l];

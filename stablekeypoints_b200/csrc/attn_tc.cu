@@ -43,6 +43,7 @@ struct TcParams {
   int heads[TC_MAX_LAYERS], d[TC_MAX_LAYERS], k_shared[TC_MAX_LAYERS];
   float weight[TC_MAX_LAYERS];           // layer weight / heads
   int n_layers, T, R2, n_idx;
+  int64_t idx_stride;
   const int64_t* token_idx;
   float* maps;
 };
@@ -182,7 +183,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
     }
     ptx::fence_barrier_init();
   }
-  if (SELECT && threadIdx.x < TC_MAX_SEL) tok_s[threadIdx.x] = threadIdx.x < P.n_idx ? static_cast<int>(P.token_idx[threadIdx.x]) : -1;
+  if (SELECT && threadIdx.x < TC_MAX_SEL) tok_s[threadIdx.x] = threadIdx.x < P.n_idx ? static_cast<int>(P.token_idx[blockIdx.y * P.idx_stride + threadIdx.x]) : -1;
   if (warp == 1) {
     ptx::tmem_alloc(ptx::smem_u32(const_cast<uint32_t*>(tmem_ptr)), 512);
     ptx::tmem_relinquish();
@@ -487,7 +488,7 @@ static int launch_tc(const TcParams& P, int B, int R2, cudaStream_t st) {
 }
 
 int attn_map_fwd_tc(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, const int64_t* token_idx, int n_idx,
-                    float* maps, float* row_stats, int precision, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+                    int64_t idx_stride, float* maps, float* row_stats, int precision, void* workspace, size_t workspace_bytes, cudaStream_t st) {
   (void)row_stats;
   const size_t need = attn_map_tc_workspace(h_layers, n_layers, B, T, R, precision);
   if (!workspace || workspace_bytes < need) {
@@ -532,7 +533,7 @@ int attn_map_fwd_tc(const skp_attn_layer* h_layers, int n_layers, int B, int T, 
   }
   P.n_layers = n_layers; P.T = T; P.R2 = R2;
   P.n_idx = token_idx ? n_idx : 0;
-  P.token_idx = token_idx; P.maps = maps;
+  P.token_idx = token_idx; P.maps = maps; P.idx_stride = idx_stride;
   const bool sel = token_idx != nullptr;
   const bool split = T > TC_BN;
   if (x3) {

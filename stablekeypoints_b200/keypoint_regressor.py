@@ -1,0 +1,135 @@
+"""Token voting and keypoint precomputation — host mirror of the hot-path part of the
+reference's `unsupervised_keypoints/keypoint_regressor.py`.
+
+Reference lines replaced:
+  find_best_indices         keypoint_regressor.py:16-121
+  precompute_all_keypoints  keypoint_regressor.py:124-224
+"""
+from __future__ import annotations
+
+import torch
+
+from . import distributed as dist_
+from . import ops
+from .eval import find_max_pixel, pixel_from_weighted_avg, run_image_with_context_augmented
+from .optimize import _make_dataset, select_tokens
+
+
+def vote_top_k(indices_list: torch.Tensor, top_k: int) -> torch.Tensor:
+    """`keypoint_regressor.py:114-119`: most frequently selected token ids.  The reference's
+    `counts.argsort(descending=True)` leaves the order of equally-voted ids unspecified; here
+    ties go to the smaller id (stable sort), which is one of the orders it may produce."""
+    ids, counts = torch.unique(indices_list.reshape(-1).cpu(), return_counts=True)
+    order = torch.sort(counts, descending=True, stable=True).indices
+    return ids[order][:top_k]
+
+
+@torch.no_grad()
+def find_best_indices(
+    ldm,
+    context,
+    num_steps=100,
+    device="cuda",
+    noise_level=-1,
+    upsample_res=256,
+    layers=[0, 1, 2, 3, 4, 5],
+    from_where=["down_cross", "mid_cross", "up_cross"],
+    num_tokens=1000,
+    top_k=30,
+    dataset_loc="~",
+    dataset_name="celeba_aligned",
+    min_dist=0.05,
+    furthest_point_num_samples=50,
+    controllers=None,
+    num_gpus=1,
+    top_k_strategy="entropy",
+    sigma=3,
+    validation=False,
+    num_subjects=1,
+    dataset=None,
+):
+    """`keypoint_regressor.py:16-121` -> (top_k,) int64 CPU tensor.  Images are sharded across
+    ranks (no collective on the data path); the per-image votes are gathered once."""
+    from . import ptp_utils
+    world, rank = dist_.world_size(), dist_.rank()
+    dataset = _make_dataset(dataset_name, dataset_loc, dataset)
+    loader = torch.utils.data.DataLoader(dist_.shard_dataset(dataset, rank, world), batch_size=num_gpus,
+                                         shuffle=True, drop_last=True)
+    it = iter(loader)
+    votes = []
+    for _ in range(num_steps // (num_gpus * world)):
+        try:
+            mini_batch = next(it)
+        except StopIteration:
+            it = iter(loader)
+            mini_batch = next(it)
+        image = mini_batch["img"].to(device, non_blocking=True)
+        maps = ptp_utils.run_and_find_attn_batched(
+            ldm, image, context, layers=layers, noise_level=noise_level, from_where=from_where,
+            upsample_res=upsample_res, device=device, controllers=controllers)
+        for m in maps.unbind(0):
+            votes.append(select_tokens(m, m, top_k_strategy, furthest_point_num_samples, top_k, sigma, num_subjects))
+    votes = torch.stack(votes) if votes else torch.empty(0, top_k, dtype=torch.int64, device=device)
+    votes = dist_.all_gather_cat(votes)
+    return vote_top_k(votes, top_k)
+
+
+@torch.no_grad()
+def precompute_all_keypoints(
+    ldm,
+    context,
+    top_indices,
+    device="cuda",
+    noise_level=-1,
+    layers=[0, 1, 2, 3, 4, 5],
+    from_where=["down_cross", "mid_cross", "up_cross"],
+    augment_degrees=30,
+    augment_scale=(0.9, 1.1),
+    augment_translate=(0.1, 0.1),
+    augmentation_iterations=20,
+    dataset_loc="~",
+    visualize=False,
+    dataset_name="celeba_aligned",
+    controllers=None,
+    num_gpus=1,
+    max_num_points=50_000,
+    max_loc_strategy="argmax",
+    save_folder="outputs",
+    validation=False,
+    dataset=None,
+):
+    """`keypoint_regressor.py:124-224` -> (source (N,K,2), target (N,n,2), visibility|None), in
+    dataset order.  Images are sharded across ranks; one all_gather of the (N_local,K,2) keypoints
+    at the end (the reference shuffles with batch_size 1; order does not affect the regressor)."""
+    world, rank = dist_.world_size(), dist_.rank()
+    dataset = _make_dataset(dataset_name, dataset_loc, dataset)
+    n = min(len(dataset), max_num_points)
+    mine = list(dist_.shard_range(n, rank, world))
+    per = (n + world - 1) // world
+    src, tgt, vis = [], [], []
+    for i in mine:
+        sample = dataset[i]
+        maps = run_image_with_context_augmented(
+            ldm, sample["img"], context, top_indices, device=device, from_where=from_where, layers=layers,
+            noise_level=noise_level, augmentation_iterations=augmentation_iterations, augment_degrees=augment_degrees,
+            augment_scale=augment_scale, augment_translate=augment_translate, controllers=controllers,
+            save_folder=save_folder, num_gpus=num_gpus)
+        kp = find_max_pixel(maps) / 512.0 if max_loc_strategy == "argmax" else pixel_from_weighted_avg(maps) / 512.0
+        src.append(kp)
+        tgt.append(torch.as_tensor(sample["kpts"]).to(device=device, dtype=torch.float32))
+        if "visibility" in sample:
+            vis.append(torch.as_tensor(sample["visibility"]).to(device=device, dtype=torch.float32))
+
+    def _gather(rows):
+        if not rows and world == 1:
+            return None
+        t = torch.stack(rows) if rows else None
+        if world == 1:
+            return t
+        if t is None or t.shape[0] < per:      # pad the short shard so all_gather shapes agree
+            like = rows[0] if rows else torch.zeros(1, device=device)
+            pad = torch.zeros(per - len(rows), *like.shape, device=device, dtype=like.dtype)
+            t = pad if t is None else torch.cat([t, pad])
+        return dist_.interleave_shards(dist_.all_gather_cat(t), n)
+
+    return _gather(src), _gather(tgt), (_gather(vis) if vis else None)

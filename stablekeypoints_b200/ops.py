@@ -290,15 +290,20 @@ class _AttentionMaps(torch.autograd.Function):
         ks = [_f32(t) for t in tensors[n:]]
         B, T = qs[0].shape[0], ks[0].shape[1]
         dev = qs[0].device
+        stride = 0
         if token_idx is not None:
             token_idx = token_idx.to(device=dev, dtype=torch.int64).contiguous()
-        t_out = token_idx.numel() if token_idx is not None else T
+            if token_idx.dim() == 2:          # one row of ids per image
+                if token_idx.shape[0] != B:
+                    raise RuntimeError(f"token_idx has {token_idx.shape[0]} rows for {B} images")
+                stride = token_idx.shape[1]
+        t_out = token_idx.shape[-1] if token_idx is not None else T
         maps = torch.empty(B, t_out, R, R, dtype=torch.float32, device=dev)
         arr = _layer_array(qs, ks, heads, scales, weights)
         with _guard(maps):
             ws, nbytes = _workspace(arr, n, B, T, R, prec, dev)
-            call("skp_attn_map_fwd", arr, n, B, T, R, ptr(token_idx), t_out if token_idx is not None else 0, ptr(maps),
-                 None, prec, ptr(ws), nbytes, stream_of(maps))
+            call("skp_attn_map_fwd", arr, n, B, T, R, ptr(token_idx), t_out if token_idx is not None else 0, stride,
+                 ptr(maps), None, prec, ptr(ws), nbytes, stream_of(maps))
         ctx.save_for_backward(token_idx, *qs, *ks)
         ctx.meta = meta
         return maps
@@ -313,22 +318,99 @@ class _AttentionMaps(torch.autograd.Function):
         B, T = qs[0].shape[0], ks[0].shape[1]
         dev = g.device
         g = _f32(g)
-        # the losses touch K selected planes only (optimize.py:420-424): find them, compact them
-        live = (g.abs().amax(dim=(0, 2, 3)) > 0).nonzero().flatten()
         dqs = [torch.zeros_like(q) for q in qs]
         dks = [torch.zeros_like(k) for k in ks]
+        chunk = max(1, min(32, min(q.shape[-1] // h for q, h in zip(qs, heads))))
+        arr = _layer_array(qs, ks, heads, scales, weights, dqs, dks)
+        if token_idx is not None and token_idx.dim() == 2:
+            # per-image ids: the gradient is already compact, (B, n_idx, R, R)
+            with _guard(g):
+                ws, nbytes = _workspace(arr, n, B, T, R, prec, dev)
+                for i in range(0, token_idx.shape[1], chunk):
+                    tok = token_idx[:, i:i + chunk].contiguous()
+                    dsel = g[:, i:i + chunk].contiguous()
+                    call("skp_attn_map_bwd", arr, n, B, T, R, ptr(tok), tok.shape[1], tok.shape[1], ptr(dsel),
+                         prec, ptr(ws), nbytes, stream_of(g))
+            return (None, None, *dqs, *dks)
+        # the losses touch K selected planes only (optimize.py:420-424): find them, compact them
+        live = (g.abs().amax(dim=(0, 2, 3)) > 0).nonzero().flatten()
         if live.numel():
             tok = live if token_idx is None else token_idx[live]
-            arr = _layer_array(qs, ks, heads, scales, weights, dqs, dks)
-            chunk = max(1, min(32, min(q.shape[-1] // h for q, h in zip(qs, heads))))
             with _guard(g):
                 ws, nbytes = _workspace(arr, n, B, T, R, prec, dev)
                 for i in range(0, live.numel(), chunk):
                     sel = live[i:i + chunk]
                     dsel = g.index_select(1, sel).contiguous()
-                    call("skp_attn_map_bwd", arr, n, B, T, R, ptr(tok[i:i + chunk].contiguous()), sel.numel(), ptr(dsel),
+                    call("skp_attn_map_bwd", arr, n, B, T, R, ptr(tok[i:i + chunk].contiguous()), sel.numel(), 0, ptr(dsel),
                          prec, ptr(ws), nbytes, stream_of(g))
         return (None, None, *dqs, *dks)
+
+
+def _attn_backward_compact(meta, token_idx, g, qs, ks):
+    """dq, dk for a compact gradient g (B, n_idx, R, R) on planes token_idx (n_idx,) or (B, n_idx)."""
+    heads, scales, weights, R, prec = meta
+    n = len(heads)
+    B, T = qs[0].shape[0], ks[0].shape[1]
+    g = _f32(g)
+    dqs = [torch.zeros_like(q) for q in qs]
+    dks = [torch.zeros_like(k) for k in ks]
+    chunk = max(1, min(32, min(q.shape[-1] // h for q, h in zip(qs, heads))))
+    arr = _layer_array(qs, ks, heads, scales, weights, dqs, dks)
+    per_image = token_idx.dim() == 2
+    with _guard(g):
+        ws, nbytes = _workspace(arr, n, B, T, R, prec, g.device)
+        for i in range(0, token_idx.shape[-1], chunk):
+            tok = token_idx[..., i:i + chunk].contiguous()
+            dsel = g[:, i:i + chunk].contiguous()
+            call("skp_attn_map_bwd", arr, n, B, T, R, ptr(tok), tok.shape[-1], tok.shape[-1] if per_image else 0,
+                 ptr(dsel), prec, ptr(ws), nbytes, stream_of(g))
+    return dqs, dks
+
+
+class _SelectedPlanes(torch.autograd.Function):
+    """maps_full[b, token_idx[b]] as a differentiable function of (q, k).
+
+    Forward gathers K planes per image from maps that `attention_maps` already produced under
+    no_grad (token selection is integer-valued, so nothing differentiates through it); backward
+    is the compact attention-map backward.  This is how `optimize_embedding` avoids both a
+    second forward and the dense (T,R,R) zero-padded gradients autograd would otherwise build
+    for `attn_map[top_embedding_indices]` (`optimize.py:420-424`)."""
+
+    @staticmethod
+    def forward(ctx, meta, token_idx, maps_full, *tensors):
+        n = len(meta[0])
+        qs = [_f32(t) for t in tensors[:n]]
+        ks = [_f32(t) for t in tensors[n:]]
+        B, K = token_idx.shape
+        R = meta[3]
+        out = torch.gather(maps_full, 1, token_idx.view(B, K, 1, 1).expand(B, K, R, R))
+        ctx.save_for_backward(token_idx, *qs, *ks)
+        ctx.meta = meta
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        n = len(ctx.meta[0])
+        token_idx = ctx.saved_tensors[0]
+        qs = list(ctx.saved_tensors[1:1 + n])
+        ks = list(ctx.saved_tensors[1 + n:])
+        dqs, dks = _attn_backward_compact(ctx.meta, token_idx, g, qs, ks)
+        return (None, None, None, *dqs, *dks)
+
+
+def _meta(heads, scales, weights, feature_res, precision, n):
+    if weights is None:
+        weights = [1.0 / n] * n
+    return (tuple(int(h) for h in heads), tuple(float(s) for s in scales), tuple(float(w) for w in weights),
+            int(feature_res), _lib.PRECISIONS[precision])
+
+
+def selected_planes(maps_full: torch.Tensor, token_idx: torch.Tensor, qs, ks, heads, scales, feature_res: int,
+                    weights=None, precision: str = "auto") -> torch.Tensor:
+    """(B, K, R, R) = maps_full[b, token_idx[b]] with gradients flowing to qs / ks (see _SelectedPlanes)."""
+    token_idx = token_idx.to(device=maps_full.device, dtype=torch.int64).contiguous()
+    return _SelectedPlanes.apply(_meta(heads, scales, weights, feature_res, precision, len(qs)), token_idx,
+                                 maps_full, *qs, *ks)
 
 
 def attention_maps(qs: Sequence[torch.Tensor], ks: Sequence[torch.Tensor], heads: Sequence[int], scales: Sequence[float],

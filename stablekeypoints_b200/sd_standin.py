@@ -138,10 +138,6 @@ class ResnetBlock(nn.Module):
         return h + (x if self.skip is None else self.skip(x))
 
 
-class _StopForward(Exception):
-    """Raised by the early-exit hook once the last captured layer has run."""
-
-
 # --------------------------------------------------------------------------------------
 # UNet
 # --------------------------------------------------------------------------------------
@@ -272,7 +268,6 @@ class UNet2DConditionStandIn(nn.Module):
             prev = cout
         self.conv_norm_out = nn.GroupNorm(32, ch[0])
         self.conv_out = nn.Conv2d(ch[0], cfg.in_channels, 3, padding=1)
-        self.stop_after_capture = False   # caller-side UNet economy; set by our load_ldm only
 
     def forward(self, sample, timestep, encoder_hidden_states):
         temb = self.time_embedding(timestep_embedding(timestep.reshape(-1).expand(sample.shape[0]),
@@ -282,11 +277,8 @@ class UNet2DConditionStandIn(nn.Module):
         for blk in self.down_blocks:
             x = blk(x, temb, encoder_hidden_states, skips)
         x = self.mid_block(x, temb, encoder_hidden_states)
-        try:
-            for blk in self.up_blocks:
-                x = blk(x, temb, encoder_hidden_states, skips)
-        except _StopForward:
-            return {"sample": None}
+        for blk in self.up_blocks:
+            x = blk(x, temb, encoder_hidden_states, skips)
         x = self.conv_out(F.silu(self.conv_norm_out(x)))
         return {"sample": x}
 

@@ -33,7 +33,7 @@ def test_library_exports_every_declared_symbol():
 def test_library_binds_and_reports_version():
     from stablekeypoints_b200 import _lib
     lib = _lib.load()
-    assert lib.skp_version() == 100
+    assert lib.skp_version() >= 101
     assert isinstance(lib.skp_last_error(), bytes)
 
 
