@@ -45,6 +45,9 @@ int skp_version(void);
 const char* skp_last_error(void);
 /* compute capability major*10+minor of `device`, or negative status */
 int skp_device_arch(int device);
+/* number of CUDA kernels this library has launched in this process so far (diagnostics:
+ * bench.py reports the difference over its timed region as gpu_launches) */
+long long skp_kernel_launches(void);
 
 /* ---------------------------------------------------------------------------------------
  * (1) Fused cross-attention map.

@@ -30,6 +30,7 @@ SIGNATURES = {
     "skp_version": (_I, []),
     "skp_last_error": (C.c_char_p, []),
     "skp_device_arch": (_I, [_I]),
+    "skp_kernel_launches": (C.c_longlong, []),
     "skp_attn_map_workspace_bytes": (_Z, [C.POINTER(AttnLayer), _I, _I, _I, _I, _I]),
     "skp_attn_map_fwd": (_I, [C.POINTER(AttnLayer), _I, _I, _I, _I, _P, _I, _L, _P, _P, _I, _P, _Z, _P]),
     "skp_attn_map_bwd": (_I, [C.POINTER(AttnLayer), _I, _I, _I, _I, _P, _I, _L, _P, _I, _P, _Z, _P]),
@@ -75,10 +76,41 @@ def check(rc: int, what: str) -> None:
         raise RuntimeError(f"{what} failed ({rc}): {load().skp_last_error().decode()}")
 
 
+# Optional per-entry-point device timing (bench.py's live roofline numbers): when `timing` is a
+# dict, every call is bracketed by CUDA events on the stream it launches on (the last argument
+# of every entry point is the stream), and `timing_summary()` turns them into ms after a sync.
+timing = None
+
+
+def timing_start() -> None:
+    global timing
+    timing = {}
+
+
+def timing_summary() -> dict:
+    """{entry point: {"calls": n, "ms": total device ms}}; stops timing."""
+    global timing
+    out = {}
+    if timing:
+        torch.cuda.synchronize()
+        for name, evs in timing.items():
+            out[name] = {"calls": len(evs), "ms": sum(a.elapsed_time(b) for a, b in evs)}
+    timing = None
+    return out
+
+
 def call(name: str, *args) -> None:
     global launches
     launches += 1
+    if timing is None:
+        check(getattr(load(), name)(*args), name)
+        return
+    st = torch.cuda.ExternalStream(args[-1].value) if args[-1].value else torch.cuda.default_stream()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(st)
     check(getattr(load(), name)(*args), name)
+    b.record(st)
+    timing.setdefault(name, []).append((a, b))
 
 
 def ptr(t):

@@ -1,4 +1,6 @@
 // Library-level entry points: version, error string, device probe.
+#include <atomic>
+
 #include "common.cuh"
 
 namespace skp {
@@ -9,9 +11,15 @@ void set_error(const char* fmt, ...) {
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
 }
+static std::atomic<long long> g_launches{0};
+int note_launch() {
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return 0;
+}
 }  // namespace skp
 
-extern "C" int skp_version(void) { return 101; }
+extern "C" int skp_version(void) { return 102; }
+extern "C" long long skp_kernel_launches(void) { return skp::g_launches.load(std::memory_order_relaxed); }
 extern "C" const char* skp_last_error(void) { return skp::g_err; }
 extern "C" int skp_device_arch(int device) {
   cudaDeviceProp p;

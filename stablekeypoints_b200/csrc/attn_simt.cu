@@ -352,7 +352,7 @@ int attn_map_fwd_simt(const skp_attn_layer* h_layers, int n_layers, int B, int T
   SKP_REQUIRE(smem <= 227 * 1024, "attn_map_fwd (SIMT): T=%d, dim_head=%d need %zu B of shared memory (> 227 KB)", T, L.dmax, smem);
   SKP_CUDA(cudaFuncSetAttribute(attn_map_fwd_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
   dim3 grid(R * R / SIMT_TP, B);
-  attn_map_fwd_simt_kernel<<<grid, SIMT_THREADS, smem, st>>>(L, T, R, token_idx, n_idx, idx_stride, maps, row_stats);
+  attn_map_fwd_simt_kernel<<<(::skp::note_launch(), grid), SIMT_THREADS, smem, st>>>(L, T, R, token_idx, n_idx, idx_stride, maps, row_stats);
   SKP_LAUNCH_CHECK();
   return SKP_OK;
 }
@@ -397,18 +397,18 @@ int attn_map_bwd_simt(const skp_attn_layer* h_layers, int n_layers, int B, int T
   SKP_CUDA(cudaFuncSetAttribute(attn_map_bwd_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
   SKP_REQUIRE(L.total_heads <= 65535 && B <= 65535, "attn_map_bwd: grid too large");
   dim3 grid(R * R / SIMT_TP, L.total_heads, B);
-  attn_map_bwd_simt_kernel<<<grid, SIMT_THREADS, smem, st>>>(L, T, R, token_idx, n_idx, idx_stride, dmaps_sel);
+  attn_map_bwd_simt_kernel<<<(::skp::note_launch(), grid), SIMT_THREADS, smem, st>>>(L, T, R, token_idx, n_idx, idx_stride, dmaps_sel);
   SKP_LAUNCH_CHECK();
   for (int l = 0; l < n_layers; ++l) {
     const skp_attn_layer& a = h_layers[l];
     if (a.s == R) {
       const int64_t n = static_cast<int64_t>(B) * R * R * a.C;
-      add_inplace_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(a.dq, L.dq_up[l], n);
+      add_inplace_kernel<<<(::skp::note_launch(), static_cast<unsigned>((n + 255) / 256)), 256, 0, st>>>(a.dq, L.dq_up[l], n);
     } else {
       dim3 g1((a.C + 127) / 128, R * a.s, B), g2((a.C + 127) / 128, a.s * a.s, B);
       SKP_REQUIRE(R * a.s <= 65535, "attn_map_bwd: R*s too large for the adjoint grid");
-      bicubic_adjoint_x_kernel<<<g1, 128, 0, st>>>(L.dq_up[l], a.s, a.C, R, tmp);
-      bicubic_adjoint_y_kernel<<<g2, 128, 0, st>>>(tmp, a.s, a.C, R, a.dq);
+      bicubic_adjoint_x_kernel<<<(::skp::note_launch(), g1), 128, 0, st>>>(L.dq_up[l], a.s, a.C, R, tmp);
+      bicubic_adjoint_y_kernel<<<(::skp::note_launch(), g2), 128, 0, st>>>(tmp, a.s, a.C, R, a.dq);
     }
     SKP_LAUNCH_CHECK();
   }

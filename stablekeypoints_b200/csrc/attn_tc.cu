@@ -483,6 +483,7 @@ static int launch_tc(const TcParams& P, int B, int R2, cudaStream_t st) {
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = NSPLIT > 1 ? 1 : 0;
+  note_launch();
   SKP_CUDA(cudaLaunchKernelEx(&cfg, kern, P));
   return SKP_OK;
 }
@@ -516,11 +517,11 @@ int attn_map_fwd_tc(const skp_attn_layer* h_layers, int n_layers, int B, int T, 
     const float mult = a.scale * 1.4426950408889634f;
     dim3 gq(R2, B), gk(T, Bk);
     if (x3) {
-      tc_prep_q_kernel<3><<<gq, 256, 0, st>>>(a.q, a.s, a.C, a.heads, R, mult, q_hi, q_lo);
-      tc_prep_k_kernel<3><<<gk, 256, 0, st>>>(a.k, T, a.C, a.heads, k_hi, k_lo);
+      tc_prep_q_kernel<3><<<(::skp::note_launch(), gq), 256, 0, st>>>(a.q, a.s, a.C, a.heads, R, mult, q_hi, q_lo);
+      tc_prep_k_kernel<3><<<(::skp::note_launch(), gk), 256, 0, st>>>(a.k, T, a.C, a.heads, k_hi, k_lo);
     } else {
-      tc_prep_q_kernel<1><<<gq, 256, 0, st>>>(a.q, a.s, a.C, a.heads, R, mult, q_hi, q_lo);
-      tc_prep_k_kernel<1><<<gk, 256, 0, st>>>(a.k, T, a.C, a.heads, k_hi, k_lo);
+      tc_prep_q_kernel<1><<<(::skp::note_launch(), gq), 256, 0, st>>>(a.q, a.s, a.C, a.heads, R, mult, q_hi, q_lo);
+      tc_prep_k_kernel<1><<<(::skp::note_launch(), gk), 256, 0, st>>>(a.k, T, a.C, a.heads, k_hi, k_lo);
     }
     SKP_LAUNCH_CHECK();
     int rc = encode_map(&P.q_map[l][0], q_hi, d, R2, B * a.heads, TC_BM);

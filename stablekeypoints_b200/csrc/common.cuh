@@ -34,6 +34,9 @@ void set_error(const char* fmt, ...);
 
 #define SKP_LAUNCH_CHECK() SKP_CUDA(cudaPeekAtLastError())
 
+// process-wide count of kernels this library has launched (skp_kernel_launches(); bench.py's gpu_launches)
+int note_launch();
+
 inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
 constexpr int kNumSMs = 148;   // B200

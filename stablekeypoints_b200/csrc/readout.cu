@@ -480,23 +480,23 @@ extern "C" int skp_plane_argmax(const float* maps, int N, int H, int W, int64_t*
   chunks = chunks < 1 ? 1 : chunks;
   while (chunks > 1 && ((plane + chunks - 1) / chunks) % 4 != 0) --chunks;
   dim3 grid(chunks, N);
-  plane_argmax_kernel<<<grid, 256, 0, st>>>(maps, plane, reinterpret_cast<unsigned long long*>(flat_idx));
+  plane_argmax_kernel<<<(::skp::note_launch(), grid), 256, 0, st>>>(maps, plane, reinterpret_cast<unsigned long long*>(flat_idx));
   SKP_LAUNCH_CHECK();
-  argmax_decode_kernel<<<(N + 127) / 128, 128, 0, st>>>(reinterpret_cast<unsigned long long*>(flat_idx), N, maxval);
+  argmax_decode_kernel<<<(::skp::note_launch(), (N + 127) / 128), 128, 0, st>>>(reinterpret_cast<unsigned long long*>(flat_idx), N, maxval);
   SKP_LAUNCH_CHECK();
   return SKP_OK;
 }
 
 extern "C" int skp_find_k_max_pixels(const float* maps, int N, int H, int W, int num, float* out, void* stream) {
   SKP_REQUIRE(maps && out && N > 0 && H > 0 && W > 0 && num >= 1 && num <= 8, "skp_find_k_max_pixels: bad arguments");
-  k_max_pixels_kernel<<<N, 512, 0, as_stream(stream)>>>(maps, N, H, W, num, out);
+  k_max_pixels_kernel<<<(::skp::note_launch(), N), 512, 0, as_stream(stream)>>>(maps, N, H, W, num, out);
   SKP_LAUNCH_CHECK();
   return SKP_OK;
 }
 
 extern "C" int skp_weighted_avg_readout(float* maps, int N, int H, int W, float distance, int mutate, float* out, void* stream) {
   SKP_REQUIRE(maps && out && N > 0 && H > 0 && W > 0, "skp_weighted_avg_readout: bad arguments");
-  weighted_avg_kernel<<<N, 512, 0, as_stream(stream)>>>(maps, H, W, distance, mutate, out);
+  weighted_avg_kernel<<<(::skp::note_launch(), N), 512, 0, as_stream(stream)>>>(maps, H, W, distance, mutate, out);
   SKP_LAUNCH_CHECK();
   return SKP_OK;
 }
@@ -505,7 +505,7 @@ extern "C" int skp_plane_stats(const float* maps, int N, int H, int W, float sig
                                float* kl, float* entropy, int64_t* argmax_out, void* stream) {
   SKP_REQUIRE(maps && N > 0 && H > 0 && W > 0 && num_subjects >= 1 && num_subjects <= 8, "skp_plane_stats: bad arguments");
   SKP_REQUIRE(kl || entropy || argmax_out, "skp_plane_stats: no output requested");
-  plane_stats_kernel<<<N, 512, 0, as_stream(stream)>>>(maps, H, W, sigma, epsilon, num_subjects, kl, entropy, argmax_out);
+  plane_stats_kernel<<<(::skp::note_launch(), N), 512, 0, as_stream(stream)>>>(maps, H, W, sigma, epsilon, num_subjects, kl, entropy, argmax_out);
   SKP_LAUNCH_CHECK();
   return SKP_OK;
 }
@@ -513,7 +513,7 @@ extern "C" int skp_plane_stats(const float* maps, int N, int H, int W, float sig
 extern "C" int skp_gaussian_circles(const float* pos, int S, int N, int size, float sigma, float* out, void* stream) {
   SKP_REQUIRE(pos && out && S >= 1 && N > 0 && size > 0, "skp_gaussian_circles: bad arguments");
   dim3 grid((size * size + 255) / 256, N);
-  gaussian_circles_kernel<<<grid, 256, 0, as_stream(stream)>>>(pos, S, N, size, sigma, out);
+  gaussian_circles_kernel<<<(::skp::note_launch(), grid), 256, 0, as_stream(stream)>>>(pos, S, N, size, sigma, out);
   SKP_LAUNCH_CHECK();
   return SKP_OK;
 }
@@ -522,7 +522,7 @@ extern "C" int skp_rank_ascending(const float* score, int N, int top_k, int64_t*
   SKP_REQUIRE(score && out && N > 0 && N <= 4096 && top_k >= 0 && top_k <= N, "skp_rank_ascending: need 0 < N <= 4096, top_k <= N");
   int P = 1;
   while (P < N) P <<= 1;
-  rank_ascending_kernel<<<1, 512, P * sizeof(unsigned long long), as_stream(stream)>>>(score, N, top_k, out);
+  rank_ascending_kernel<<<(::skp::note_launch(), 1), 512, P * sizeof(unsigned long long), as_stream(stream)>>>(score, N, top_k, out);
   SKP_LAUNCH_CHECK();
   return SKP_OK;
 }
@@ -533,7 +533,7 @@ extern "C" int skp_furthest_point_sampling(const int64_t* argmax_flat, int N, in
   SKP_REQUIRE(n_cand >= 2 && n_cand <= 1024 && top_k >= 2 && top_k <= n_cand && N > 0,
               "skp_furthest_point_sampling: need 2 <= top_k <= n_cand <= 1024 (the reference raises NameError below 2 candidates)");
   size_t smem = sizeof(float) * 2 * n_cand + sizeof(int) * (n_cand + top_k);
-  fps_kernel<<<1, 256, smem, as_stream(stream)>>>(argmax_flat, N, H, W, candidates, n_cand, top_k, out, n_out);
+  fps_kernel<<<(::skp::note_launch(), 1), 256, smem, as_stream(stream)>>>(argmax_flat, N, H, W, candidates, n_cand, top_k, out, n_out);
   SKP_LAUNCH_CHECK();
   return SKP_OK;
 }
@@ -543,7 +543,7 @@ extern "C" int skp_keypoint_losses_fwd(const float* maps_a, const float* maps_b,
   SKP_REQUIRE(maps_a && idx && loss_parts && K > 0 && H > 0 && W > 0, "skp_keypoint_losses_fwd: bad arguments");
   SKP_REQUIRE(!maps_b || theta_inv, "skp_keypoint_losses_fwd: theta_inv required with maps_b");
   SKP_REQUIRE(num_subjects >= 1 && num_subjects <= 8, "skp_keypoint_losses_fwd: 1 <= num_subjects <= 8");
-  keypoint_losses_kernel<false><<<K, 512, 0, as_stream(stream)>>>(maps_a, maps_b, idx, H, W, theta_inv, sigma, num_subjects,
+  keypoint_losses_kernel<false><<<(::skp::note_launch(), K), 512, 0, as_stream(stream)>>>(maps_a, maps_b, idx, H, W, theta_inv, sigma, num_subjects,
                                                                   loss_parts, 0.f, 0.f, nullptr, nullptr);
   SKP_LAUNCH_CHECK();
   return SKP_OK;
@@ -556,7 +556,7 @@ extern "C" int skp_keypoint_losses_bwd(const float* maps_a, const float* maps_b,
   SKP_REQUIRE(!maps_b || theta_inv, "skp_keypoint_losses_bwd: theta_inv required with maps_b");
   SKP_REQUIRE(num_subjects >= 1 && num_subjects <= 8, "skp_keypoint_losses_bwd: 1 <= num_subjects <= 8");
   const float nrm = 2.0f / (static_cast<float>(K) * H * W);
-  keypoint_losses_kernel<true><<<K, 512, 0, as_stream(stream)>>>(maps_a, maps_b, idx, H, W, theta_inv, sigma, num_subjects,
+  keypoint_losses_kernel<true><<<(::skp::note_launch(), K), 512, 0, as_stream(stream)>>>(maps_a, maps_b, idx, H, W, theta_inv, sigma, num_subjects,
                                                                  nullptr, g_sharp * nrm, g_equiv * nrm, d_a_sel, d_b_sel);
   SKP_LAUNCH_CHECK();
   return SKP_OK;

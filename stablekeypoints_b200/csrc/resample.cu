@@ -176,7 +176,7 @@ extern "C" int skp_bilinear_upsample(const float* in, int N, int h, int w, float
   SKP_REQUIRE(in && out && N > 0 && h > 0 && w > 0 && H > 0 && W > 0, "skp_bilinear_upsample: bad arguments");
   SKP_REQUIRE(H <= 65535 && N <= 65535, "skp_bilinear_upsample: grid too large");
   dim3 grid((W + 127) / 128, H, N);
-  bilinear_upsample_kernel<<<grid, 128, 0, as_stream(stream)>>>(in, h, w, out, H, W);
+  bilinear_upsample_kernel<<<(::skp::note_launch(), grid), 128, 0, as_stream(stream)>>>(in, h, w, out, H, W);
   SKP_LAUNCH_CHECK();
   return SKP_OK;
 }
@@ -185,7 +185,7 @@ extern "C" int skp_bicubic_upsample_nhwc(const float* in, int B, int s, int C, f
   SKP_REQUIRE(in && out && B > 0 && s > 0 && C > 0 && R > 0, "skp_bicubic_upsample_nhwc: bad arguments");
   SKP_REQUIRE(B <= 65535 && R <= 65535, "skp_bicubic_upsample_nhwc: grid too large");
   dim3 grid(((C + 127) / 128) * R, R, B);
-  bicubic_upsample_nhwc_kernel<<<grid, 128, 0, as_stream(stream)>>>(in, s, C, out, R);
+  bicubic_upsample_nhwc_kernel<<<(::skp::note_launch(), grid), 128, 0, as_stream(stream)>>>(in, s, C, out, R);
   SKP_LAUNCH_CHECK();
   return SKP_OK;
 }
@@ -194,7 +194,7 @@ extern "C" int skp_affine_warp(const float* img, const float* theta, int N, int 
   SKP_REQUIRE(img && theta && out && N > 0 && C > 0 && H > 0 && W > 0, "skp_affine_warp: bad arguments");
   SKP_REQUIRE(H <= 65535 && N <= 65535, "skp_affine_warp: grid too large");
   dim3 grid((W + 127) / 128, H, N);
-  affine_warp_kernel<false><<<grid, 128, 0, as_stream(stream)>>>(img, theta, C, H, W, out);
+  affine_warp_kernel<false><<<(::skp::note_launch(), grid), 128, 0, as_stream(stream)>>>(img, theta, C, H, W, out);
   SKP_LAUNCH_CHECK();
   return SKP_OK;
 }
@@ -203,7 +203,7 @@ extern "C" int skp_affine_warp_bwd(const float* dout, const float* theta, int N,
   SKP_REQUIRE(dout && theta && dimg && N > 0 && C > 0 && H > 0 && W > 0, "skp_affine_warp_bwd: bad arguments");
   SKP_REQUIRE(H <= 65535 && N <= 65535, "skp_affine_warp_bwd: grid too large");
   dim3 grid((W + 127) / 128, H, N);
-  affine_warp_kernel<true><<<grid, 128, 0, as_stream(stream)>>>(dout, theta, C, H, W, dimg);
+  affine_warp_kernel<true><<<(::skp::note_launch(), grid), 128, 0, as_stream(stream)>>>(dout, theta, C, H, W, dimg);
   SKP_LAUNCH_CHECK();
   return SKP_OK;
 }
@@ -214,14 +214,14 @@ extern "C" int skp_tta_accumulate(const float* maps, const float* theta_inv, int
               "skp_tta_accumulate: bad arguments (K <= 32)");
   SKP_REQUIRE(H <= 65535, "skp_tta_accumulate: grid too large");
   dim3 grid((W + 127) / 128, H);
-  tta_accumulate_kernel<<<grid, 128, 0, as_stream(stream)>>>(maps, theta_inv, A, K, h, w, sum_, num_, H, W);
+  tta_accumulate_kernel<<<(::skp::note_launch(), grid), 128, 0, as_stream(stream)>>>(maps, theta_inv, A, K, h, w, sum_, num_, H, W);
   SKP_LAUNCH_CHECK();
   return SKP_OK;
 }
 
 extern "C" int skp_tta_finalize(const float* sum_, const float* num_, int64_t n, float* out, void* stream) {
   SKP_REQUIRE(sum_ && num_ && out && n > 0, "skp_tta_finalize: bad arguments");
-  tta_finalize_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, as_stream(stream)>>>(sum_, num_, n, out);
+  tta_finalize_kernel<<<(::skp::note_launch(), static_cast<unsigned>((n + 255) / 256)), 256, 0, as_stream(stream)>>>(sum_, num_, n, out);
   SKP_LAUNCH_CHECK();
   return SKP_OK;
 }

@@ -194,6 +194,7 @@ def optimize_embedding(
     dataset=None,
     context_dim=None,
     log_fn=None,
+    step_hook=None,
 ):
     """`optimize.py:269-475` with the same arguments.  `num_gpus` keeps the reference's meaning
     "images per UNet pass" (its DataLoader batch, `optimize.py:356`); here those images share
@@ -219,8 +220,9 @@ def optimize_embedding(
     if batch_size % (per_pass * world) != 0:
         raise ValueError(f"batch_size {batch_size} must be a multiple of num_gpus*world_size = {per_pass * world}")
     accum = batch_size // (per_pass * world)
+    host_data = not torch.as_tensor(dataset[0]["img"]).is_cuda
     loader = torch.utils.data.DataLoader(dist_.shard_dataset(dataset, rank, world), batch_size=per_pass,
-                                         shuffle=True, drop_last=True)
+                                         shuffle=True, drop_last=True, pin_memory=host_data)
     it = iter(loader)
     start = it_start = time.time()
     run_eq = run_sh = run_tot = 0.0
@@ -245,7 +247,9 @@ def optimize_embedding(
             dist_.allreduce_mean_(context.grad)
             optimizer.step()
             optimizer.zero_grad()
-            if log_fn is not None or not wandb_log:
+            if log_fn is False:
+                pass                      # silent: no device->host read, the step stays asynchronous
+            elif log_fn is not None or not wandb_log:
                 rec = {"loss": float(run_tot), "running_equivariance_attn_loss": float(run_eq),
                        "running_sharpening_loss": float(run_sh), "iteration time": time.time() - it_start}
                 if log_fn is not None:
@@ -258,6 +262,8 @@ def optimize_embedding(
                            "running_sharpening_loss": float(run_sh), "iteration time": time.time() - it_start})
             run_eq = run_sh = run_tot = 0.0
             it_start = time.time()
-    if rank == 0:
+            if step_hook is not None:
+                step_hook((iteration + 1) // accum)
+    if rank == 0 and log_fn is not False:
         print(f"optimization took {time.time() - start} seconds")
     return context.detach()
