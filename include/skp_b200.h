@@ -92,10 +92,13 @@ int skp_attn_map_fwd(const skp_attn_layer* h_layers, int n_layers, int B, int T,
 /* Backward of the above for a gradient that is non-zero on n_idx token planes only
  * (the losses read attn_map[top_k indices], optimize.py:420-424).
  * dmaps_sel (B, n_idx, R, R) = d loss / d maps[b, token_idx[j]].  Accumulates into
- * layer.dq / layer.dk.  Linear in dmaps_sel, so callers may chunk planes. */
+ * layer.dq / layer.dk.  Linear in dmaps_sel, so callers may chunk planes.
+ * row_stats: the (B, sum_l heads_l, R*R, 2) tensor skp_attn_map_fwd wrote for the SAME q/k, or
+ * NULL.  With it (and dim_head <= 64, n_idx <= 16, T <= 512) the backward runs on tcgen05
+ * (attn_tc_bwd.cu); without it the fp32 CUDA-core kernel recomputes the softmax statistics. */
 int skp_attn_map_bwd(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R,
                      const int64_t* token_idx, int n_idx, int64_t idx_stride, const float* dmaps_sel,
-                     int precision, void* workspace, size_t workspace_bytes, void* stream);
+                     const float* row_stats, int precision, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------
  * Resampling (SURVEY.md Appendix A semantics == torch.nn.functional, align_corners=False)

@@ -10,6 +10,11 @@ bool attn_map_tc_supported(const skp_attn_layer*, int, int, int, int, int n_idx)
 size_t attn_map_tc_workspace(const skp_attn_layer*, int, int, int, int, int precision);
 int attn_map_fwd_tc(const skp_attn_layer*, int, int, int, int, const int64_t*, int, int64_t, float*, float*, int precision, void*,
                     size_t, cudaStream_t);
+// tcgen05 backward (attn_tc_bwd.cu)
+bool attn_map_bwd_tc_supported(const skp_attn_layer*, int, int, int, int, int n_idx);
+size_t attn_map_bwd_tc_workspace(const skp_attn_layer*, int, int, int, int, int precision);
+int attn_map_bwd_tc(const skp_attn_layer*, int, int, int, int, const int64_t*, int, int64_t, const float*, const float*, int precision,
+                    void*, size_t, cudaStream_t);
 }  // namespace skp
 
 using namespace skp;
@@ -25,6 +30,10 @@ extern "C" size_t skp_attn_map_workspace_bytes(const skp_attn_layer* h_layers, i
   size_t bwd = attn_map_bwd_simt_workspace(h_layers, n_layers, B, R);
   int p = resolve_precision(h_layers, n_layers, B, T, R, 0, precision);
   size_t fwd = (p == SKP_PREC_SIMT_F32) ? 0 : attn_map_tc_workspace(h_layers, n_layers, B, T, R, p);
+  if (p != SKP_PREC_SIMT_F32 && attn_map_bwd_tc_supported(h_layers, n_layers, B, T, R, 1)) {
+    size_t b2 = attn_map_bwd_tc_workspace(h_layers, n_layers, B, T, R, p);
+    fwd = fwd > b2 ? fwd : b2;
+  }
   return fwd > bwd ? fwd : bwd;
 }
 
@@ -49,8 +58,11 @@ extern "C" int skp_attn_map_fwd(const skp_attn_layer* h_layers, int n_layers, in
 }
 
 extern "C" int skp_attn_map_bwd(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, const int64_t* token_idx,
-                                int n_idx, int64_t idx_stride, const float* dmaps_sel, int precision, void* workspace, size_t workspace_bytes,
-                                void* stream) {
-  (void)precision;   // the backward currently always runs the fp32 CUDA-core kernel
+                                int n_idx, int64_t idx_stride, const float* dmaps_sel, const float* row_stats, int precision,
+                                void* workspace, size_t workspace_bytes, void* stream) {
+  int p = resolve_precision(h_layers, n_layers, B, T, R, n_idx, precision);
+  if (p != SKP_PREC_SIMT_F32 && row_stats && attn_map_bwd_tc_supported(h_layers, n_layers, B, T, R, n_idx))
+    return attn_map_bwd_tc(h_layers, n_layers, B, T, R, token_idx, n_idx, idx_stride, dmaps_sel, row_stats, p, workspace,
+                           workspace_bytes, as_stream(stream));
   return attn_map_bwd_simt(h_layers, n_layers, B, T, R, token_idx, n_idx, idx_stride, dmaps_sel, workspace, workspace_bytes, as_stream(stream));
 }

@@ -19,33 +19,17 @@
 //    exchanges (max, sum) with the other column half and the other CTAs of the cluster
 //    through (distributed) shared memory + mbarriers, then accumulates weight * P into 128
 //    fp32 registers.  The (h, R^2, T) probability tensor never exists; the output is written once.
-#include <cuda.h>
-#include <cuda_bf16.h>
-
-#include "common.cuh"
-#include "ptx_sm100.cuh"
+#include "attn_tc.cuh"
 
 namespace skp {
 
-constexpr int TC_MAX_LAYERS = 12;
-constexpr int TC_BM = 128;       // pixels per CTA (UMMA M)
-constexpr int TC_BN = 256;       // tokens per CTA (UMMA N)
-constexpr int TC_BK = 64;        // bf16 per k-block = one 128-byte swizzle row
-constexpr int TC_THREADS = 320;  // warp 0 TMA, warp 1 MMA, warps 2..9 softmax
-constexpr int TC_SOFTMAX_THREADS = 256;
-constexpr int TC_MAX_SEL = 32;   // selected-token planes per launch
-constexpr int TC_A_BYTES = TC_BM * TC_BK * 2;   // 16 KB
-constexpr int TC_B_BYTES = TC_BN * TC_BK * 2;   // 32 KB
-
 struct TcParams {
-  CUtensorMap q_map[TC_MAX_LAYERS][2];   // [layer][hi, lo]: dims (d, R*R, B*h), box (64, 128, 1)
-  CUtensorMap k_map[TC_MAX_LAYERS][2];   // [layer][hi, lo]: dims (d, T,   Bk*h), box (64, 256, 1)
-  int heads[TC_MAX_LAYERS], d[TC_MAX_LAYERS], k_shared[TC_MAX_LAYERS];
-  float weight[TC_MAX_LAYERS];           // layer weight / heads
-  int n_layers, T, R2, n_idx;
+  TcOperands ops;
+  int T, R2, n_idx;
   int64_t idx_stride;
   const int64_t* token_idx;
   float* maps;
+  float* row_stats;   // optional (B, total_heads, R2, 2): (row max, sum exp2) in log2 units
 };
 
 // ------------------------------------------------------------------------------------------
@@ -197,32 +181,32 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
   if (warp == 0) {
     // =========================== TMA producer (one lane) ===================================
     if (lane == 0) {
-      for (int l = 0; l < P.n_layers; ++l) {
-        ptx::prefetch_tensormap(&P.q_map[l][0]);
-        ptx::prefetch_tensormap(&P.k_map[l][0]);
+      for (int l = 0; l < P.ops.n_layers; ++l) {
+        ptx::prefetch_tensormap(&P.ops.q_map[l][0]);
+        ptx::prefetch_tensormap(&P.ops.k_map[l][0]);
         if (NPROD == 3) {
-          ptx::prefetch_tensormap(&P.q_map[l][1]);
-          ptx::prefetch_tensormap(&P.k_map[l][1]);
+          ptx::prefetch_tensormap(&P.ops.q_map[l][1]);
+          ptx::prefetch_tensormap(&P.ops.k_map[l][1]);
         }
       }
       uint32_t it = 0;
-      for (int l = 0; l < P.n_layers; ++l) {
-        const int h = P.heads[l], d = P.d[l];
+      for (int l = 0; l < P.ops.n_layers; ++l) {
+        const int h = P.ops.heads[l], d = P.ops.d[l];
         const int nkb = (d + TC_BK - 1) / TC_BK;
         for (int head = 0; head < h; ++head) {
           const int qz = b * h + head;
-          const int kz = (P.k_shared[l] ? 0 : b * h) + head;
+          const int kz = (P.ops.k_shared[l] ? 0 : b * h) + head;
           for (int kb = 0; kb < nkb; ++kb, ++it) {
             const int s = it % SM::kStages;
             const uint32_t ph = (it / SM::kStages) & 1u;
             ptx::mbar_wait(bar_empty(s), ph ^ 1u);
             ptx::mbar_arrive_expect_tx(bar_full(s), SM::kStageBytes);
             const uint32_t st = base + s * SM::kStageBytes;
-            ptx::tma_load_3d(st, &P.q_map[l][0], bar_full(s), kb * TC_BK, p0, qz);
-            ptx::tma_load_3d(st + TC_A_BYTES, &P.k_map[l][0], bar_full(s), kb * TC_BK, tok0, kz);
+            ptx::tma_load_3d(st, &P.ops.q_map[l][0], bar_full(s), kb * TC_BK, p0, qz);
+            ptx::tma_load_3d(st + TC_A_BYTES, &P.ops.k_map[l][0], bar_full(s), kb * TC_BK, tok0, kz);
             if (NPROD == 3) {
-              ptx::tma_load_3d(st + TC_A_BYTES + TC_B_BYTES, &P.q_map[l][1], bar_full(s), kb * TC_BK, p0, qz);
-              ptx::tma_load_3d(st + 2 * TC_A_BYTES + TC_B_BYTES, &P.k_map[l][1], bar_full(s), kb * TC_BK, tok0, kz);
+              ptx::tma_load_3d(st + TC_A_BYTES + TC_B_BYTES, &P.ops.q_map[l][1], bar_full(s), kb * TC_BK, p0, qz);
+              ptx::tma_load_3d(st + 2 * TC_A_BYTES + TC_B_BYTES, &P.ops.k_map[l][1], bar_full(s), kb * TC_BK, tok0, kz);
             }
           }
         }
@@ -233,8 +217,8 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
     if (lane == 0) {
       constexpr uint32_t idesc = ptx::umma_idesc_bf16(TC_BM, TC_BN);
       uint32_t it = 0, u = 0;
-      for (int l = 0; l < P.n_layers; ++l) {
-        const int h = P.heads[l], d = P.d[l];
+      for (int l = 0; l < P.ops.n_layers; ++l) {
+        const int h = P.ops.heads[l], d = P.ops.d[l];
         const int nkb = (d + TC_BK - 1) / TC_BK;
         for (int head = 0; head < h; ++head, ++u) {
           const uint32_t buf = u & 1u;
@@ -282,9 +266,9 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
     for (int j = 0; j < (SELECT ? TC_MAX_SEL : 128); ++j) acc[j] = 0.0f;
 
     uint32_t u = 0;
-    for (int l = 0; l < P.n_layers; ++l) {
-      const int h = P.heads[l];
-      const float wgt = P.weight[l];
+    for (int l = 0; l < P.ops.n_layers; ++l) {
+      const int h = P.ops.heads[l];
+      const float wgt = P.ops.weight[l];
       for (int head = 0; head < h; ++head, ++u) {
         const uint32_t buf = u & 1u, par = (u >> 1) & 1u;
         ptx::mbar_wait(bar_tfull(buf), par);
@@ -345,6 +329,9 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
           const float2 sq = stats[(buf * 4 + q) * TC_BM + row];
           total += sq.y * ptx::ex2(sq.x - mg);
         }
+        if (P.row_stats != nullptr && part == 0)
+          reinterpret_cast<float2*>(P.row_stats)[(static_cast<int64_t>(b) * P.ops.total_heads + u) * P.R2 + p0 + row] =
+              make_float2(mg, total);
         const float cf = ncol > 0 ? wgt * ptx::ex2(m - mg) / total : 0.0f;
         // ---- pass C: accumulate weight/heads * P
         if (!SELECT) {
@@ -421,7 +408,7 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 // bf16 tensor [batch][rows][d] (d contiguous) -> 3-D map with a (64, box_rows, 1) box, 128B swizzle
-static int encode_map(CUtensorMap* m, void* ptr, int d, int rows, int batch, int box_rows) {
+int tc_encode_map(CUtensorMap* m, void* ptr, int d, int rows, int batch, int box_rows) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) {
     set_error("cuTensorMapEncodeTiled entry point not available");
@@ -453,15 +440,14 @@ bool attn_map_tc_supported(const skp_attn_layer* h_layers, int n_layers, int B, 
   return true;
 }
 
-static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 size_t attn_map_tc_workspace(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int precision) {
   const int nbuf = precision == SKP_PREC_TC_BF16 ? 1 : 2;
   size_t total = 0;
   for (int l = 0; l < n_layers; ++l) {
     const skp_attn_layer& a = h_layers[l];
-    total += nbuf * align_up(static_cast<size_t>(B) * R * R * a.C * 2, 1024);
-    total += nbuf * align_up(static_cast<size_t>(a.k_shared ? 1 : B) * T * a.C * 2, 1024);
+    total += nbuf * tc_align_up(static_cast<size_t>(B) * R * R * a.C * 2, 1024);
+    total += nbuf * tc_align_up(static_cast<size_t>(a.k_shared ? 1 : B) * T * a.C * 2, 1024);
   }
   return total + 1024;
 }
@@ -488,26 +474,18 @@ static int launch_tc(const TcParams& P, int B, int R2, cudaStream_t st) {
   return SKP_OK;
 }
 
-int attn_map_fwd_tc(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, const int64_t* token_idx, int n_idx,
-                    int64_t idx_stride, float* maps, float* row_stats, int precision, void* workspace, size_t workspace_bytes, cudaStream_t st) {
-  (void)row_stats;
-  const size_t need = attn_map_tc_workspace(h_layers, n_layers, B, T, R, precision);
-  if (!workspace || workspace_bytes < need) {
-    set_error("skp_attn_map_fwd: workspace %zu B < required %zu B", workspace_bytes, need);
-    return SKP_ERR_WORKSPACE;
-  }
-  const bool x3 = precision != SKP_PREC_TC_BF16;
+int tc_prepare(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, bool x3, void* workspace, cudaStream_t st,
+               TcOperands* O, char** ws_end) {
   const int R2 = R * R;
-  TcParams P;
-  memset(&P, 0, sizeof(P));
-  char* ws = reinterpret_cast<char*>(align_up(reinterpret_cast<size_t>(workspace), 1024));
+  char* ws = reinterpret_cast<char*>(tc_align_up(reinterpret_cast<size_t>(workspace), 1024));
+  int base = 0;
   for (int l = 0; l < n_layers; ++l) {
     const skp_attn_layer& a = h_layers[l];
-    SKP_REQUIRE(a.q && a.k, "skp_attn_map_fwd: layer %d has null q/k", l);
+    SKP_REQUIRE(a.q && a.k, "skp_attn_map: layer %d has null q/k", l);
     const int d = a.C / a.heads;
     const int Bk = a.k_shared ? 1 : B;
-    const size_t qbytes = align_up(static_cast<size_t>(B) * R2 * a.C * 2, 1024);
-    const size_t kbytes = align_up(static_cast<size_t>(Bk) * T * a.C * 2, 1024);
+    const size_t qbytes = tc_align_up(static_cast<size_t>(B) * R2 * a.C * 2, 1024);
+    const size_t kbytes = tc_align_up(static_cast<size_t>(Bk) * T * a.C * 2, 1024);
     __nv_bfloat16* q_hi = reinterpret_cast<__nv_bfloat16*>(ws); ws += qbytes;
     __nv_bfloat16* q_lo = nullptr;
     if (x3) { q_lo = reinterpret_cast<__nv_bfloat16*>(ws); ws += qbytes; }
@@ -524,17 +502,37 @@ int attn_map_fwd_tc(const skp_attn_layer* h_layers, int n_layers, int B, int T, 
       tc_prep_k_kernel<1><<<(::skp::note_launch(), gk), 256, 0, st>>>(a.k, T, a.C, a.heads, k_hi, k_lo);
     }
     SKP_LAUNCH_CHECK();
-    int rc = encode_map(&P.q_map[l][0], q_hi, d, R2, B * a.heads, TC_BM);
-    if (rc == SKP_OK) rc = encode_map(&P.k_map[l][0], k_hi, d, T, Bk * a.heads, TC_BN);
-    if (rc == SKP_OK && x3) rc = encode_map(&P.q_map[l][1], q_lo, d, R2, B * a.heads, TC_BM);
-    if (rc == SKP_OK && x3) rc = encode_map(&P.k_map[l][1], k_lo, d, T, Bk * a.heads, TC_BN);
+    int rc = tc_encode_map(&O->q_map[l][0], q_hi, d, R2, B * a.heads, TC_BM);
+    if (rc == SKP_OK) rc = tc_encode_map(&O->k_map[l][0], k_hi, d, T, Bk * a.heads, TC_BN);
+    if (rc == SKP_OK && x3) rc = tc_encode_map(&O->q_map[l][1], q_lo, d, R2, B * a.heads, TC_BM);
+    if (rc == SKP_OK && x3) rc = tc_encode_map(&O->k_map[l][1], k_lo, d, T, Bk * a.heads, TC_BN);
     if (rc != SKP_OK) return rc;
-    P.heads[l] = a.heads; P.d[l] = d; P.k_shared[l] = a.k_shared;
-    P.weight[l] = a.weight / a.heads;
+    O->k_ptr[l][0] = k_hi; O->k_ptr[l][1] = k_lo;
+    O->heads[l] = a.heads; O->d[l] = d; O->k_shared[l] = a.k_shared; O->head_base[l] = base;
+    O->weight[l] = a.weight / a.heads; O->scale[l] = a.scale;
+    base += a.heads;
   }
-  P.n_layers = n_layers; P.T = T; P.R2 = R2;
+  O->n_layers = n_layers; O->total_heads = base;
+  if (ws_end) *ws_end = ws;
+  return SKP_OK;
+}
+
+int attn_map_fwd_tc(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, const int64_t* token_idx, int n_idx,
+                    int64_t idx_stride, float* maps, float* row_stats, int precision, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+  const size_t need = attn_map_tc_workspace(h_layers, n_layers, B, T, R, precision);
+  if (!workspace || workspace_bytes < need) {
+    set_error("skp_attn_map_fwd: workspace %zu B < required %zu B", workspace_bytes, need);
+    return SKP_ERR_WORKSPACE;
+  }
+  const bool x3 = precision != SKP_PREC_TC_BF16;
+  const int R2 = R * R;
+  TcParams P;
+  memset(&P, 0, sizeof(P));
+  int rc = tc_prepare(h_layers, n_layers, B, T, R, x3, workspace, st, &P.ops, nullptr);
+  if (rc != SKP_OK) return rc;
+  P.T = T; P.R2 = R2;
   P.n_idx = token_idx ? n_idx : 0;
-  P.token_idx = token_idx; P.maps = maps; P.idx_stride = idx_stride;
+  P.token_idx = token_idx; P.maps = maps; P.idx_stride = idx_stride; P.row_stats = row_stats;
   const bool sel = token_idx != nullptr;
   const bool split = T > TC_BN;
   if (x3) {

@@ -1,0 +1,43 @@
+// Declarations shared by the tcgen05 attention-map kernels (attn_tc.cu forward, attn_tc_bwd.cu backward).
+#pragma once
+
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "ptx_sm100.cuh"
+
+namespace skp {
+
+constexpr int TC_MAX_LAYERS = 12;
+constexpr int TC_BM = 128;       // pixels per tile (UMMA M)
+constexpr int TC_BN = 256;       // tokens per CTA (UMMA N)
+constexpr int TC_BK = 64;        // bf16 per k-block = one 128-byte swizzle row
+constexpr int TC_THREADS = 320;  // warp 0 TMA, warp 1 MMA, warps 2..9 softmax
+constexpr int TC_SOFTMAX_THREADS = 256;
+constexpr int TC_MAX_SEL = 32;   // selected-token planes per forward launch
+constexpr int TC_A_BYTES = TC_BM * TC_BK * 2;   // 16 KB
+constexpr int TC_B_BYTES = TC_BN * TC_BK * 2;   // 32 KB
+
+// bf16 operands of every captured layer, staged in the workspace by tc_prepare():
+//   q' = bicubic(q) * scale*log2e as [b*h + head][pixel][d] hi (+ lo residual), k as [bk*h + head][token][d]
+struct TcOperands {
+  CUtensorMap q_map[TC_MAX_LAYERS][2];   // [layer][hi, lo]: dims (d, R*R, B*h), box (64, 128, 1)
+  CUtensorMap k_map[TC_MAX_LAYERS][2];   // [layer][hi, lo]: dims (d, T,   Bk*h), box (64, 256, 1)
+  __nv_bfloat16* k_ptr[TC_MAX_LAYERS][2];
+  int heads[TC_MAX_LAYERS], d[TC_MAX_LAYERS], k_shared[TC_MAX_LAYERS], head_base[TC_MAX_LAYERS];
+  float weight[TC_MAX_LAYERS];           // layer weight / heads
+  float scale[TC_MAX_LAYERS];
+  int n_layers, total_heads;
+};
+
+bool attn_map_tc_supported(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int n_idx);
+size_t attn_map_tc_workspace(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int precision);
+// runs the prep kernels on `st`, encodes the tensor maps; *ws_end = first free byte of the workspace
+int tc_prepare(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, bool x3, void* workspace, cudaStream_t st,
+               TcOperands* out, char** ws_end);
+int tc_encode_map(CUtensorMap* m, void* ptr, int d, int rows, int batch, int box_rows);
+
+inline size_t tc_align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+}  // namespace skp

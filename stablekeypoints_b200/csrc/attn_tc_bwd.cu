@@ -1,0 +1,526 @@
+// Backward of the fused cross-attention map on tcgen05 tensor cores (sm_100a): gradient of
+//   maps[b, t, p] = sum_l w_l * mean_head softmax_t( scale_l * q'_l[b,head,p,:] . k_l[head,t,:] )
+// w.r.t. the module's low-resolution q and k, for an upstream gradient that is non-zero on the
+// n_idx selected token planes only (optimize.py:420-424).  It is what
+// autograd does in the reference through ptp_utils.py:513-538 + optimize.py:27-79, without the
+// stored (h, R^2, T) probabilities.
+//
+// Per unit = (layer, head, image, 128-pixel tile), on one persistent CTA per (token half, unit range):
+//   S     = Q' K^T              (tcgen05, bf16x3 or bf16; logits of this CTA's 256 tokens, TMEM)
+//   S_sel = Q' K_sel^T          (the n_idx selected tokens' logits, N = 16, TMEM)
+//   P     = exp2(S - m) / l     with the row max / sum (m, l) SAVED BY THE FORWARD (row_stats)
+//   delta = sum_j P_sel[j] dP[j],  dS = P * (dP - delta)      -> bf16 tile in shared memory
+//   dQ'   = dS K                (tcgen05; A = dS K-major, B = K hi as an MN-major operand)
+//   dK   += dS^T Q'             (tcgen05; A = dS and B = Q' hi both as MN-major operands; TMEM-
+//                                resident across all units of a head, flushed once per head)
+//   dq   += U^T dQ'             (adjoint of the bicubic upsample, separable: x-gather through
+//                                shared memory, y taps as red.global.add.v4.f32)
+// No cluster, no cross-CTA exchange: the two token halves only meet in the global reductions.
+#include "attn_tc.cuh"
+
+namespace skp {
+
+constexpr int BW_SEL = 16;            // selected tokens per launch (UMMA N of the S_sel product)
+constexpr int BW_KSEL_BYTES = BW_SEL * 128;   // 16 rows x 128 B
+constexpr int BW_DS_BYTES = TC_BM * TC_BN * 2;   // 64 KB: dS tile, 4 slabs of [128 px][64 tok] bf16
+constexpr int BW_WXT_FLOATS = 5 * 256;        // x-adjoint table: s * (5 * R/s) = 5 R floats, R <= 256
+constexpr float kLog2eBw = 1.4426950408889634f;
+
+struct BwdParams {
+  TcOperands ops;
+  CUtensorMap ksel_map[TC_MAX_LAYERS][2];   // [layer][hi, lo]: dims (d, 16, B*h), box (64, 16, 1)
+  float* dq[TC_MAX_LAYERS];                 // (B, s*s, C), accumulated into
+  float* dk[TC_MAX_LAYERS];                 // (Bk, T, C), accumulated into
+  int s[TC_MAX_LAYERS], C[TC_MAX_LAYERS];
+  int B, T, R, R2, n_idx, tiles, n_units, n_chunks;
+  int64_t idx_stride;
+  const int64_t* token_idx;
+  const float* dmaps_sel;                   // (B, n_idx, R2)
+  const float* row_stats;                   // (B, total_heads, R2, 2)
+};
+
+// k_sel[(b*h + head)][j][dd] = k[bk][token_idx[b][j]][head*d + dd]  (rows j >= n_idx are zero)
+template <int NPROD>
+__global__ void bw_prep_ksel_kernel(const float* __restrict__ k, int T, int C, int heads, int k_shared,
+                                    const int64_t* __restrict__ token_idx, int n_idx, int64_t idx_stride,
+                                    __nv_bfloat16* __restrict__ hi, __nv_bfloat16* __restrict__ lo) {
+  const int j = blockIdx.x, b = blockIdx.y;
+  const int d = C / heads;
+  const int t = j < n_idx ? static_cast<int>(token_idx[b * idx_stride + j]) : -1;
+  const float* src = k + (static_cast<int64_t>(k_shared ? 0 : b) * T + (t < 0 ? 0 : t)) * C;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float v = (t >= 0 && t < T) ? src[c] : 0.0f;
+    const int head = c / d, dd = c % d;
+    const int64_t o = ((static_cast<int64_t>(b) * heads + head) * BW_SEL + j) * d + dd;
+    const __nv_bfloat16 h = __float2bfloat16_rn(v);
+    hi[o] = h;
+    if (NPROD == 3) lo[o] = __float2bfloat16_rn(v - __bfloat162float(h));
+  }
+}
+
+template <int NPROD>
+struct BwSmem {
+  static constexpr int kQStage = (NPROD == 3 ? 2 : 1) * TC_A_BYTES;
+  static constexpr int kQOff = 0;                                   // 2 stages
+  static constexpr int kKOff = kQOff + 2 * kQStage;                 // k hi (+ lo)
+  static constexpr int kKBytes = (NPROD == 3 ? 2 : 1) * TC_B_BYTES;
+  static constexpr int kKselOff = kKOff + kKBytes;
+  static constexpr int kKselBytes = (NPROD == 3 ? 2 : 1) * BW_KSEL_BYTES;
+  static constexpr int kDsOff = kKselOff + kKselBytes;              // dS tile; aliased by the fp32 dQ' staging
+  static constexpr int kWxtOff = kDsOff + BW_DS_BYTES;
+  static constexpr int kBarOff = kWxtOff + BW_WXT_FLOATS * 4;       // q_full[2], q_empty[2], s_full, ds_full, mma_done
+  static constexpr int kTmemPtrOff = kBarOff + 8 * 8;
+  static constexpr int kTokOff = kTmemPtrOff + 8;                   // int tok[16]
+  static constexpr int kTotal = kTokOff + 4 * BW_SEL;
+  static constexpr int kDynamic = kTotal + 1024;
+};
+
+__device__ __forceinline__ uint64_t bw_desc(uint32_t addr, uint32_t lbo, uint32_t sbo) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((addr & 0x3FFFFu) >> 4);
+  d |= static_cast<uint64_t>(lbo >> 4) << 16;
+  d |= static_cast<uint64_t>(sbo >> 4) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(2) << 61;      // SWIZZLE_128B
+  return d;
+}
+__device__ __host__ constexpr uint32_t bw_idesc(int M, int N, int a_mn, int b_mn) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(a_mn) << 15) | (static_cast<uint32_t>(b_mn) << 16) |
+         (static_cast<uint32_t>(N >> 3) << 17) | (static_cast<uint32_t>(M >> 4) << 24);
+}
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ void named_bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+}
+
+struct BwUnit {
+  int l, head, hg, b, tile;
+};
+__device__ __forceinline__ BwUnit bw_decode(const BwdParams& P, int u) {
+  BwUnit x;
+  const int per_head = P.B * P.tiles;
+  x.hg = u / per_head;
+  const int rem = u - x.hg * per_head;
+  x.b = rem / P.tiles;
+  x.tile = rem - x.b * P.tiles;
+  int l = 0;
+  while (l + 1 < P.ops.n_layers && x.hg >= P.ops.head_base[l + 1]) ++l;
+  x.l = l;
+  x.head = x.hg - P.ops.head_base[l];
+  return x;
+}
+// does the dK accumulator have to be flushed after unit u (last of its head / image / range)?
+__device__ __forceinline__ bool bw_flush_after(const BwdParams& P, int u, int u_end) {
+  if (u + 1 >= u_end) return true;
+  const int per_head = P.B * P.tiles;
+  const int hg = u / per_head, hg1 = (u + 1) / per_head;
+  if (hg != hg1) return true;
+  int l = 0;
+  while (l + 1 < P.ops.n_layers && hg >= P.ops.head_base[l + 1]) ++l;
+  if (P.ops.k_shared[l]) return false;
+  return (u - hg * per_head) / P.tiles != (u + 1 - hg * per_head) / P.tiles;
+}
+
+template <int NPROD, int NH>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
+  using SM = BwSmem<NPROD>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = ptx::smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  uint8_t* base_ptr = smem_raw + (base - raw);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int half = blockIdx.x % NH, chunk = blockIdx.x / NH;
+  const int u_begin = static_cast<int>(static_cast<int64_t>(chunk) * P.n_units / P.n_chunks);
+  const int u_end = static_cast<int>(static_cast<int64_t>(chunk + 1) * P.n_units / P.n_chunks);
+  const int tok0 = half * TC_BN;
+  const int ntok = max(0, min(TC_BN, P.T - tok0));          // tokens this CTA owns
+  const int n_mh = ntok > 128 ? 2 : 1;
+
+  auto bar_qfull = [&](int s) { return base + SM::kBarOff + 8u * s; };
+  auto bar_qempty = [&](int s) { return base + SM::kBarOff + 8u * (2 + s); };
+  const uint32_t bar_sfull = base + SM::kBarOff + 8u * 4;
+  const uint32_t bar_dsfull = base + SM::kBarOff + 8u * 5;
+  const uint32_t bar_mmadone = base + SM::kBarOff + 8u * 6;
+  volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(base_ptr + SM::kTmemPtrOff);
+  volatile int* tok_s = reinterpret_cast<volatile int*>(base_ptr + SM::kTokOff);
+  float* wxt = reinterpret_cast<float*>(base_ptr + SM::kWxtOff);
+  float* stg = reinterpret_cast<float*>(base_ptr + SM::kDsOff);       // [128][64] fp32, chunk-swizzled
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(bar_qfull(s), 1);
+      ptx::mbar_init(bar_qempty(s), 1);
+    }
+    ptx::mbar_init(bar_sfull, 1);
+    ptx::mbar_init(bar_dsfull, TC_SOFTMAX_THREADS);
+    ptx::mbar_init(bar_mmadone, 1);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(ptx::smem_u32(const_cast<uint32_t*>(tmem_ptr)), 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  const uint32_t tm_S = tmem_base, tm_dQ = tmem_base + 256, tm_dK = tmem_base + 320, tm_sel = tmem_base + 448;
+
+  if (warp == 0) {
+    // =========================== TMA producer (one lane) ===================================
+    if (lane == 0) {
+      int prev_hg = -1, prev_b = -1;
+      uint32_t it = 0;
+      for (int u = u_begin; u < u_end; ++u, ++it) {
+        const BwUnit x = bw_decode(P, u);
+        const int h = P.ops.heads[x.l];
+        const int st = it & 1;
+        ptx::mbar_wait(bar_qempty(st), ((it >> 1) & 1u) ^ 1u);
+        const bool need_k = x.hg != prev_hg || (!P.ops.k_shared[x.l] && x.b != prev_b);
+        const bool need_ksel = need_k || x.b != prev_b;
+        if (need_ksel && it > 0) ptx::mbar_wait(bar_qempty((it - 1) & 1), ((it - 1) >> 1) & 1u);   // previous unit done with k / k_sel
+        const uint32_t bytes = SM::kQStage + (need_k ? SM::kKBytes : 0) + (need_ksel ? SM::kKselBytes : 0);
+        ptx::mbar_arrive_expect_tx(bar_qfull(st), bytes);
+        const int qz = x.b * h + x.head;
+        const uint32_t qs = base + SM::kQOff + st * SM::kQStage;
+        ptx::tma_load_3d(qs, &P.ops.q_map[x.l][0], bar_qfull(st), 0, x.tile * TC_BM, qz);
+        if (NPROD == 3) ptx::tma_load_3d(qs + TC_A_BYTES, &P.ops.q_map[x.l][1], bar_qfull(st), 0, x.tile * TC_BM, qz);
+        if (need_k) {
+          const int kz = (P.ops.k_shared[x.l] ? 0 : x.b * h) + x.head;
+          ptx::tma_load_3d(base + SM::kKOff, &P.ops.k_map[x.l][0], bar_qfull(st), 0, tok0, kz);
+          if (NPROD == 3) ptx::tma_load_3d(base + SM::kKOff + TC_B_BYTES, &P.ops.k_map[x.l][1], bar_qfull(st), 0, tok0, kz);
+        }
+        if (need_ksel) {
+          ptx::tma_load_3d(base + SM::kKselOff, &P.ksel_map[x.l][0], bar_qfull(st), 0, 0, qz);
+          if (NPROD == 3) ptx::tma_load_3d(base + SM::kKselOff + BW_KSEL_BYTES, &P.ksel_map[x.l][1], bar_qfull(st), 0, 0, qz);
+        }
+        prev_hg = x.hg;
+        prev_b = x.b;
+      }
+    }
+  } else if (warp == 1) {
+    // =========================== MMA issuer (one lane) =====================================
+    if (lane == 0) {
+      uint32_t it = 0;
+      bool dk_fresh = true;
+      for (int u = u_begin; u < u_end; ++u, ++it) {
+        const BwUnit x = bw_decode(P, u);
+        const int d = P.ops.d[x.l];
+        const int st = it & 1;
+        const uint32_t qs = base + SM::kQOff + st * SM::kQStage;
+        const uint32_t ks = base + SM::kKOff, ksel = base + SM::kKselOff, dsb = base + SM::kDsOff;
+        ptx::mbar_wait(bar_qfull(st), (it >> 1) & 1u);
+        ptx::tc_fence_after();
+        // ---- S = Q' K^T (256 tokens) and S_sel = Q' K_sel^T (16 tokens)
+        const uint32_t id_S = bw_idesc(TC_BM, TC_BN, 0, 0), id_sel = bw_idesc(TC_BM, BW_SEL, 0, 0);
+        const int nk16 = d / 16;
+        for (int kk = 0; kk < nk16; ++kk) {
+          const uint64_t a_hi = bw_desc(qs + kk * 32, 16, 1024), b_hi = bw_desc(ks + kk * 32, 16, 1024);
+          const uint64_t s_hi = bw_desc(ksel + kk * 32, 16, 1024);
+          if (NPROD == 3) {
+            const uint64_t a_lo = bw_desc(qs + TC_A_BYTES + kk * 32, 16, 1024);
+            const uint64_t b_lo = bw_desc(ks + TC_B_BYTES + kk * 32, 16, 1024);
+            const uint64_t s_lo = bw_desc(ksel + BW_KSEL_BYTES + kk * 32, 16, 1024);
+            ptx::umma_bf16(tm_S, a_hi, b_lo, id_S, kk != 0);
+            ptx::umma_bf16(tm_S, a_lo, b_hi, id_S, 1u);
+            ptx::umma_bf16(tm_S, a_hi, b_hi, id_S, 1u);
+            ptx::umma_bf16(tm_sel, a_hi, s_lo, id_sel, kk != 0);
+            ptx::umma_bf16(tm_sel, a_lo, s_hi, id_sel, 1u);
+            ptx::umma_bf16(tm_sel, a_hi, s_hi, id_sel, 1u);
+          } else {
+            ptx::umma_bf16(tm_S, a_hi, b_hi, id_S, kk != 0);
+            ptx::umma_bf16(tm_sel, a_hi, s_hi, id_sel, kk != 0);
+          }
+        }
+        ptx::umma_commit(bar_sfull);
+        // ---- wait for dS (bf16, [px][tok]) in shared memory
+        ptx::mbar_wait(bar_dsfull, it & 1u);
+        ptx::tc_fence_after();
+        // dQ' (128 px x d) = dS (K-major A, K = 256 tokens) * K_hi (MN-major B: rows = tokens)
+        const uint32_t id_dq = bw_idesc(TC_BM, d, 0, 1);
+        const int nkt = (ntok + 15) / 16;
+        for (int k = 0; k < nkt; ++k)
+          ptx::umma_bf16(tm_dQ, bw_desc(dsb + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024), bw_desc(ks + k * 2048, 16384, 1024),
+                         id_dq, k != 0);
+        // dK (128 tok x d per half) += dS^T (MN-major A: rows = pixels) * Q'_hi (MN-major B: rows = pixels)
+        const uint32_t id_dk = bw_idesc(128, d, 1, 1);
+        for (int mh = 0; mh < n_mh; ++mh)
+          for (int k = 0; k < TC_BM / 16; ++k)
+            ptx::umma_bf16(tm_dK + mh * 64, bw_desc(dsb + mh * 2 * 16384 + k * 2048, 16384, 1024),
+                           bw_desc(qs + k * 2048, 16384, 1024), id_dk, (dk_fresh && k == 0) ? 0u : 1u);
+        ptx::umma_commit(bar_mmadone);
+        ptx::umma_commit(bar_qempty(st));
+        dk_fresh = bw_flush_after(P, u, u_end);
+      }
+    }
+  } else {
+    // =========================== softmax-recompute / dS / drain warps ========================
+    const int quad = warp & 3;                 // TMEM lane quadrant this warp may access
+    const int ch = (warp - 2) >> 2;            // column half of the CTA's 256 tokens
+    const int row = quad * 32 + lane;
+    const int stid = threadIdx.x - 64;         // 0..255
+    const int col0 = ch * 128;
+    const int ncol = max(0, min(128, ntok - col0));
+    const uint32_t lane_off = static_cast<uint32_t>(quad * 32) << 16;
+    const uint32_t dsb = base + SM::kDsOff;
+    uint8_t* ds_ptr = base_ptr + SM::kDsOff;
+    const int R = P.R;
+    uint32_t it = 0;
+    int prev_l = -1, prev_b = -1;
+    for (int u = u_begin; u < u_end; ++u, ++it) {
+      const BwUnit x = bw_decode(P, u);
+      const int d = P.ops.d[x.l], s = P.s[x.l], C = P.C[x.l];
+      const int up = R / s, nj = 5 * up;
+      const float wgt = P.ops.weight[x.l], scale = P.ops.scale[x.l];
+      if (x.l != prev_l || x.b != prev_b) {
+        named_bar_sync(1, TC_SOFTMAX_THREADS);
+        if (x.l != prev_l) {
+          const float ratio = static_cast<float>(s) / R;
+          for (int e = stid; e < s * nj; e += TC_SOFTMAX_THREADS) {
+            const int sx = e / nj, xx = max(0, (sx - 2) * up) + e % nj;
+            float wsum = 0.0f;
+            if (xx < R) {
+              int ix;
+              float w[4];
+              bicubic_coeffs(xx, ratio, &ix, w);
+#pragma unroll
+              for (int a = 0; a < 4; ++a) wsum += (min(max(ix - 1 + a, 0), s - 1) == sx) ? w[a] : 0.0f;
+            }
+            wxt[e] = wsum;
+          }
+        }
+        if (stid < BW_SEL) tok_s[stid] = stid < P.n_idx ? static_cast<int>(P.token_idx[x.b * P.idx_stride + stid]) : -1;
+        named_bar_sync(1, TC_SOFTMAX_THREADS);
+        prev_l = x.l;
+        prev_b = x.b;
+      }
+      const int p = x.tile * TC_BM + row;
+      const float2 ml = reinterpret_cast<const float2*>(P.row_stats)[(static_cast<int64_t>(x.b) * P.ops.total_heads + x.hg) * P.R2 + p];
+      const float m = ml.x, inv_l = 1.0f / ml.y;
+      float dp[BW_SEL];
+#pragma unroll
+      for (int j = 0; j < BW_SEL; ++j)
+        dp[j] = j < P.n_idx ? wgt * __ldg(P.dmaps_sel + (static_cast<int64_t>(x.b) * P.n_idx + j) * P.R2 + p) : 0.0f;
+
+      ptx::mbar_wait(bar_sfull, it & 1u);
+      ptx::tc_fence_after();
+      float delta = 0.0f;
+      {
+        uint32_t sv[BW_SEL];
+        tmem_ld16(tm_sel + lane_off, sv);
+        ptx::tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < BW_SEL; ++j) {
+          const int t = tok_s[j];
+          const float ps = (t >= 0 && t < P.T) ? ptx::ex2(__uint_as_float(sv[j]) - m) * inv_l : 0.0f;
+          delta = fmaf(ps, dp[j], delta);
+          dp[j] *= ps;                          // dp[j] now holds P_sel[j] * dP[j]
+        }
+      }
+      // ---- dS = P * (dP - delta): dense part -P*delta for my 128 columns, then the n_idx corrections
+      const float nd = -delta * inv_l;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t v[32];
+        ptx::tmem_ld32(tm_S + lane_off + col0 + 32 * c, v);
+        ptx::tmem_ld_wait();
+        uint32_t pk[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const float e0 = (32 * c + 2 * j < ncol) ? ptx::ex2(__uint_as_float(v[2 * j]) - m) * nd : 0.0f;
+          const float e1 = (32 * c + 2 * j + 1 < ncol) ? ptx::ex2(__uint_as_float(v[2 * j + 1]) - m) * nd : 0.0f;
+          const __nv_bfloat162 h2 = __floats2bfloat162_rn(e0, e1);
+          pk[j] = *reinterpret_cast<const uint32_t*>(&h2);
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int cc = col0 + 32 * c + 8 * q;
+          const uint32_t off = (cc >> 6) * 16384 + row * 128 + ((((cc & 63) >> 3) ^ (row & 7)) << 4);
+          *reinterpret_cast<uint4*>(ds_ptr + off) = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < BW_SEL; ++j) {
+        const int t = tok_s[j] - tok0;
+        if (j < P.n_idx && t >= col0 && t < col0 + ncol) {
+          const uint32_t off = (t >> 6) * 16384 + row * 128 + ((((t & 63) >> 3) ^ (row & 7)) << 4) + (t & 7) * 2;
+          __nv_bfloat16* e = reinterpret_cast<__nv_bfloat16*>(ds_ptr + off);
+          *e = __float2bfloat16_rn(__bfloat162float(*e) + dp[j]);
+        }
+      }
+      ptx::fence_proxy_async();
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(bar_dsfull);
+
+      // ---- dQ' tile: TMEM -> fp32 staging (aliases the dS tile, free once the MMAs are done)
+      ptx::mbar_wait(bar_mmadone, it & 1u);
+      ptx::tc_fence_after();
+      if (ch * 32 < d) {
+        uint32_t v[32];
+        ptx::tmem_ld32(tm_dQ + lane_off + ch * 32, v);
+        ptx::tmem_ld_wait();
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const int cidx = ch * 8 + q;
+          *reinterpret_cast<float4*>(stg + row * 64 + ((cidx ^ (row & 7)) << 2)) =
+              make_float4(__uint_as_float(v[4 * q]) * scale, __uint_as_float(v[4 * q + 1]) * scale,
+                          __uint_as_float(v[4 * q + 2]) * scale, __uint_as_float(v[4 * q + 3]) * scale);
+        }
+      }
+      ptx::tc_fence_before();
+      named_bar_sync(2, TC_SOFTMAX_THREADS);
+      // ---- adjoint of the bicubic upsample: x-gather from staging, y taps as vector reductions
+      {
+        const int span = R <= TC_BM ? R : TC_BM;
+        const int rows_per_tile = TC_BM / span;
+        const int p0 = x.tile * TC_BM;
+        const int y0 = p0 / R, x0 = p0 % R;
+        const int n_c4 = d >> 2;
+        const int n_out = rows_per_tile * s * n_c4;
+        const float ratio = static_cast<float>(s) / R;
+        float* dq = P.dq[x.l] + static_cast<int64_t>(x.b) * s * s * C + x.head * d;
+        for (int o = stid; o < n_out; o += TC_SOFTMAX_THREADS) {
+          const int c4 = o % n_c4, sx = (o / n_c4) % s, yy = o / (n_c4 * s);
+          const int xlo = max(0, (sx - 2) * up);
+          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+          const int j0 = max(0, x0 - xlo), j1 = min(nj, x0 + span - xlo);
+          for (int j = j0; j < j1; ++j) {
+            const float w = wxt[sx * nj + j];
+            const int r = yy * span + (xlo + j - x0);
+            const float4 t4 = *reinterpret_cast<const float4*>(stg + r * 64 + ((c4 ^ (r & 7)) << 2));
+            acc.x = fmaf(w, t4.x, acc.x);
+            acc.y = fmaf(w, t4.y, acc.y);
+            acc.z = fmaf(w, t4.z, acc.z);
+            acc.w = fmaf(w, t4.w, acc.w);
+          }
+          int iy;
+          float wy[4];
+          bicubic_coeffs(y0 + yy, ratio, &iy, wy);
+#pragma unroll
+          for (int a = 0; a < 4; ++a) {
+            const int sy = min(max(iy - 1 + a, 0), s - 1);
+            red_add_v4(dq + static_cast<int64_t>(sy * s + sx) * C + c4 * 4, wy[a] * acc.x, wy[a] * acc.y, wy[a] * acc.z, wy[a] * acc.w);
+          }
+        }
+      }
+      named_bar_sync(2, TC_SOFTMAX_THREADS);
+      // ---- dK: flush the TMEM accumulator when this head (or image, for a per-image k) is finished
+      if (bw_flush_after(P, u, u_end) && ch < n_mh) {
+        const int t = tok0 + ch * 128 + row;
+        float* dk = P.dk[x.l] + (static_cast<int64_t>(P.ops.k_shared[x.l] ? 0 : x.b) * P.T + t) * C + x.head * d;
+        const float inv = 1.0f / kLog2eBw;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          if (c * 32 < d) {
+            uint32_t v[32];
+            ptx::tmem_ld32(tm_dK + lane_off + ch * 64 + c * 32, v);
+            ptx::tmem_ld_wait();
+            if (t < P.T) {
+#pragma unroll
+              for (int q = 0; q < 8; ++q)
+                if (c * 32 + q * 4 < d)
+                  red_add_v4(dk + c * 32 + q * 4, __uint_as_float(v[4 * q]) * inv, __uint_as_float(v[4 * q + 1]) * inv,
+                             __uint_as_float(v[4 * q + 2]) * inv, __uint_as_float(v[4 * q + 3]) * inv);
+            }
+          }
+        }
+        ptx::tc_fence_before();
+      }
+    }
+  }
+
+  // ---- teardown -------------------------------------------------------------------------------
+  __syncwarp();
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// ==========================================================================================
+// host side
+// ==========================================================================================
+bool attn_map_bwd_tc_supported(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int n_idx) {
+  if (!attn_map_tc_supported(h_layers, n_layers, B, T, R, n_idx)) return false;
+  if (n_idx < 1 || n_idx > BW_SEL || R > 256) return false;
+  if (!((R <= TC_BM && TC_BM % R == 0) || (R % TC_BM == 0))) return false;
+  for (int l = 0; l < n_layers; ++l) {
+    const int d = h_layers[l].C / h_layers[l].heads;
+    if (d > 64 || d % 16 != 0) return false;     // dQ' / dK accumulators are 64 TMEM columns each
+  }
+  return true;
+}
+
+size_t attn_map_bwd_tc_workspace(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int precision) {
+  size_t total = attn_map_tc_workspace(h_layers, n_layers, B, T, R, precision);
+  const int nbuf = precision == SKP_PREC_TC_BF16 ? 1 : 2;
+  for (int l = 0; l < n_layers; ++l)
+    total += nbuf * tc_align_up(static_cast<size_t>(B) * h_layers[l].heads * BW_SEL * (h_layers[l].C / h_layers[l].heads) * 2, 1024);
+  return total + 1024;
+}
+
+template <int NPROD, int NH>
+static int launch_bwd(const BwdParams& P, cudaStream_t st) {
+  using SM = BwSmem<NPROD>;
+  auto kern = attn_map_bwd_tc_kernel<NPROD, NH>;
+  SKP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::kDynamic));
+  kern<<<(::skp::note_launch(), P.n_chunks * NH), TC_THREADS, SM::kDynamic, st>>>(P);
+  SKP_LAUNCH_CHECK();
+  return SKP_OK;
+}
+
+int attn_map_bwd_tc(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, const int64_t* token_idx, int n_idx,
+                    int64_t idx_stride, const float* dmaps_sel, const float* row_stats, int precision, void* workspace,
+                    size_t workspace_bytes, cudaStream_t st) {
+  SKP_REQUIRE(token_idx && dmaps_sel && row_stats, "skp_attn_map_bwd (tcgen05): token_idx, dmaps_sel and row_stats are required");
+  const size_t need = attn_map_bwd_tc_workspace(h_layers, n_layers, B, T, R, precision);
+  if (!workspace || workspace_bytes < need) {
+    set_error("skp_attn_map_bwd: workspace %zu B < required %zu B", workspace_bytes, need);
+    return SKP_ERR_WORKSPACE;
+  }
+  const bool x3 = precision != SKP_PREC_TC_BF16;
+  BwdParams P;
+  memset(&P, 0, sizeof(P));
+  char* ws = nullptr;
+  int rc = tc_prepare(h_layers, n_layers, B, T, R, x3, workspace, st, &P.ops, &ws);
+  if (rc != SKP_OK) return rc;
+  for (int l = 0; l < n_layers; ++l) {
+    const skp_attn_layer& a = h_layers[l];
+    SKP_REQUIRE(a.dq && a.dk, "skp_attn_map_bwd: layer %d has null dq/dk", l);
+    const int d = a.C / a.heads;
+    const size_t bytes = tc_align_up(static_cast<size_t>(B) * a.heads * BW_SEL * d * 2, 1024);
+    __nv_bfloat16* hi = reinterpret_cast<__nv_bfloat16*>(ws); ws += bytes;
+    __nv_bfloat16* lo = nullptr;
+    if (x3) { lo = reinterpret_cast<__nv_bfloat16*>(ws); ws += bytes; }
+    dim3 g(BW_SEL, B);
+    if (x3) bw_prep_ksel_kernel<3><<<(::skp::note_launch(), g), 256, 0, st>>>(a.k, T, a.C, a.heads, a.k_shared, token_idx, n_idx, idx_stride, hi, lo);
+    else bw_prep_ksel_kernel<1><<<(::skp::note_launch(), g), 256, 0, st>>>(a.k, T, a.C, a.heads, a.k_shared, token_idx, n_idx, idx_stride, hi, lo);
+    SKP_LAUNCH_CHECK();
+    rc = tc_encode_map(&P.ksel_map[l][0], hi, d, BW_SEL, B * a.heads, BW_SEL);
+    if (rc == SKP_OK && x3) rc = tc_encode_map(&P.ksel_map[l][1], lo, d, BW_SEL, B * a.heads, BW_SEL);
+    if (rc != SKP_OK) return rc;
+    P.dq[l] = a.dq; P.dk[l] = a.dk; P.s[l] = a.s; P.C[l] = a.C;
+  }
+  P.B = B; P.T = T; P.R = R; P.R2 = R * R; P.n_idx = n_idx; P.tiles = R * R / TC_BM;
+  P.idx_stride = idx_stride; P.token_idx = token_idx; P.dmaps_sel = dmaps_sel; P.row_stats = row_stats;
+  P.n_units = P.ops.total_heads * B * P.tiles;
+  const int nh = T > TC_BN ? 2 : 1;
+  P.n_chunks = kNumSMs / nh < P.n_units ? kNumSMs / nh : P.n_units;
+  if (x3) return nh == 2 ? launch_bwd<3, 2>(P, st) : launch_bwd<3, 1>(P, st);
+  return nh == 2 ? launch_bwd<1, 2>(P, st) : launch_bwd<1, 1>(P, st);
+}
+
+}  // namespace skp

@@ -299,28 +299,32 @@ class _AttentionMaps(torch.autograd.Function):
                 stride = token_idx.shape[1]
         t_out = token_idx.shape[-1] if token_idx is not None else T
         maps = torch.empty(B, t_out, R, R, dtype=torch.float32, device=dev)
+        # per (image, head, pixel) softmax statistics (row max, sum exp2): 8 B per row instead of
+        # the reference's T probabilities; the tcgen05 backward consumes them
+        stats = torch.empty(B, sum(heads), R * R, 2, dtype=torch.float32, device=dev)
         arr = _layer_array(qs, ks, heads, scales, weights)
         with _guard(maps):
             ws, nbytes = _workspace(arr, n, B, T, R, prec, dev)
             call("skp_attn_map_fwd", arr, n, B, T, R, ptr(token_idx), t_out if token_idx is not None else 0, stride,
-                 ptr(maps), None, prec, ptr(ws), nbytes, stream_of(maps))
-        ctx.save_for_backward(token_idx, *qs, *ks)
+                 ptr(maps), ptr(stats), prec, ptr(ws), nbytes, stream_of(maps))
+        ctx.save_for_backward(token_idx, stats, *qs, *ks)
         ctx.meta = meta
-        return maps
+        ctx.mark_non_differentiable(stats)
+        return maps, stats
 
     @staticmethod
-    def backward(ctx, g):
+    def backward(ctx, g, _gstats=None):
         heads, scales, weights, R, prec = ctx.meta
         n = len(heads)
-        token_idx = ctx.saved_tensors[0]
-        qs = list(ctx.saved_tensors[1:1 + n])
-        ks = list(ctx.saved_tensors[1 + n:])
+        token_idx, stats = ctx.saved_tensors[0], ctx.saved_tensors[1]
+        qs = list(ctx.saved_tensors[2:2 + n])
+        ks = list(ctx.saved_tensors[2 + n:])
         B, T = qs[0].shape[0], ks[0].shape[1]
         dev = g.device
         g = _f32(g)
         dqs = [torch.zeros_like(q) for q in qs]
         dks = [torch.zeros_like(k) for k in ks]
-        chunk = max(1, min(32, min(q.shape[-1] // h for q, h in zip(qs, heads))))
+        chunk = max(1, min(16, min(q.shape[-1] // h for q, h in zip(qs, heads))))
         arr = _layer_array(qs, ks, heads, scales, weights, dqs, dks)
         if token_idx is not None and token_idx.dim() == 2:
             # per-image ids: the gradient is already compact, (B, n_idx, R, R)
@@ -329,7 +333,7 @@ class _AttentionMaps(torch.autograd.Function):
                 for i in range(0, token_idx.shape[1], chunk):
                     tok = token_idx[:, i:i + chunk].contiguous()
                     dsel = g[:, i:i + chunk].contiguous()
-                    call("skp_attn_map_bwd", arr, n, B, T, R, ptr(tok), tok.shape[1], tok.shape[1], ptr(dsel),
+                    call("skp_attn_map_bwd", arr, n, B, T, R, ptr(tok), tok.shape[1], tok.shape[1], ptr(dsel), ptr(stats),
                          prec, ptr(ws), nbytes, stream_of(g))
             return (None, None, *dqs, *dks)
         # the losses touch K selected planes only (optimize.py:420-424): find them, compact them
@@ -342,11 +346,11 @@ class _AttentionMaps(torch.autograd.Function):
                     sel = live[i:i + chunk]
                     dsel = g.index_select(1, sel).contiguous()
                     call("skp_attn_map_bwd", arr, n, B, T, R, ptr(tok[i:i + chunk].contiguous()), sel.numel(), 0, ptr(dsel),
-                         prec, ptr(ws), nbytes, stream_of(g))
+                         ptr(stats), prec, ptr(ws), nbytes, stream_of(g))
         return (None, None, *dqs, *dks)
 
 
-def _attn_backward_compact(meta, token_idx, g, qs, ks):
+def _attn_backward_compact(meta, token_idx, g, qs, ks, stats=None):
     """dq, dk for a compact gradient g (B, n_idx, R, R) on planes token_idx (n_idx,) or (B, n_idx)."""
     heads, scales, weights, R, prec = meta
     n = len(heads)
@@ -354,7 +358,7 @@ def _attn_backward_compact(meta, token_idx, g, qs, ks):
     g = _f32(g)
     dqs = [torch.zeros_like(q) for q in qs]
     dks = [torch.zeros_like(k) for k in ks]
-    chunk = max(1, min(32, min(q.shape[-1] // h for q, h in zip(qs, heads))))
+    chunk = max(1, min(16, min(q.shape[-1] // h for q, h in zip(qs, heads))))
     arr = _layer_array(qs, ks, heads, scales, weights, dqs, dks)
     per_image = token_idx.dim() == 2
     with _guard(g):
@@ -363,7 +367,7 @@ def _attn_backward_compact(meta, token_idx, g, qs, ks):
             tok = token_idx[..., i:i + chunk].contiguous()
             dsel = g[:, i:i + chunk].contiguous()
             call("skp_attn_map_bwd", arr, n, B, T, R, ptr(tok), tok.shape[-1], tok.shape[-1] if per_image else 0,
-                 ptr(dsel), prec, ptr(ws), nbytes, stream_of(g))
+                 ptr(dsel), ptr(stats), prec, ptr(ws), nbytes, stream_of(g))
     return dqs, dks
 
 
@@ -377,25 +381,27 @@ class _SelectedPlanes(torch.autograd.Function):
     for `attn_map[top_embedding_indices]` (`optimize.py:420-424`)."""
 
     @staticmethod
-    def forward(ctx, meta, token_idx, maps_full, *tensors):
+    def forward(ctx, meta, token_idx, maps_full, stats, *tensors):
         n = len(meta[0])
         qs = [_f32(t) for t in tensors[:n]]
         ks = [_f32(t) for t in tensors[n:]]
         B, K = token_idx.shape
         R = meta[3]
         out = torch.gather(maps_full, 1, token_idx.view(B, K, 1, 1).expand(B, K, R, R))
-        ctx.save_for_backward(token_idx, *qs, *ks)
+        ctx.has_stats = stats is not None
+        ctx.save_for_backward(token_idx, *([stats] if stats is not None else []), *qs, *ks)
         ctx.meta = meta
         return out
 
     @staticmethod
     def backward(ctx, g):
         n = len(ctx.meta[0])
-        token_idx = ctx.saved_tensors[0]
-        qs = list(ctx.saved_tensors[1:1 + n])
-        ks = list(ctx.saved_tensors[1 + n:])
-        dqs, dks = _attn_backward_compact(ctx.meta, token_idx, g, qs, ks)
-        return (None, None, None, *dqs, *dks)
+        saved = list(ctx.saved_tensors)
+        token_idx = saved.pop(0)
+        stats = saved.pop(0) if ctx.has_stats else None
+        qs, ks = saved[:n], saved[n:]
+        dqs, dks = _attn_backward_compact(ctx.meta, token_idx, g, qs, ks, stats)
+        return (None, None, None, None, *dqs, *dks)
 
 
 def _meta(heads, scales, weights, feature_res, precision, n):
@@ -406,21 +412,24 @@ def _meta(heads, scales, weights, feature_res, precision, n):
 
 
 def selected_planes(maps_full: torch.Tensor, token_idx: torch.Tensor, qs, ks, heads, scales, feature_res: int,
-                    weights=None, precision: str = "auto") -> torch.Tensor:
-    """(B, K, R, R) = maps_full[b, token_idx[b]] with gradients flowing to qs / ks (see _SelectedPlanes)."""
+                    weights=None, precision: str = "auto", row_stats: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """(B, K, R, R) = maps_full[b, token_idx[b]] with gradients flowing to qs / ks (see _SelectedPlanes).
+    `row_stats` = the statistics `attention_maps(..., return_stats=True)` returned with `maps_full`."""
     token_idx = token_idx.to(device=maps_full.device, dtype=torch.int64).contiguous()
     return _SelectedPlanes.apply(_meta(heads, scales, weights, feature_res, precision, len(qs)), token_idx,
-                                 maps_full, *qs, *ks)
+                                 maps_full, row_stats, *qs, *ks)
 
 
 def attention_maps(qs: Sequence[torch.Tensor], ks: Sequence[torch.Tensor], heads: Sequence[int], scales: Sequence[float],
                    feature_res: int, token_idx: Optional[torch.Tensor] = None, weights: Optional[Sequence[float]] = None,
-                   precision: str = "auto") -> torch.Tensor:
+                   precision: str = "auto", return_stats: bool = False):
     """qs[l] (B, s_l^2, C_l) low-resolution to_q(x); ks[l] (B or 1, T, C_l) to_k(context).
-    -> (B, T', R, R) with T' = len(token_idx) or T.  Differentiable w.r.t. every q and k."""
+    -> (B, T', R, R) with T' = len(token_idx) or T.  Differentiable w.r.t. every q and k.
+    return_stats: also return the (B, sum heads, R^2, 2) softmax statistics (for `selected_planes`)."""
     n = len(qs)
     if weights is None:
         weights = [1.0 / n] * n
     meta = (tuple(int(h) for h in heads), tuple(float(s) for s in scales), tuple(float(w) for w in weights),
             int(feature_res), _lib.PRECISIONS[precision])
-    return _AttentionMaps.apply(meta, token_idx, *qs, *ks)
+    maps, stats = _AttentionMaps.apply(meta, token_idx, *qs, *ks)
+    return (maps, stats) if return_stats else maps

@@ -137,10 +137,11 @@ def token_opt_losses(ldm, image, transformed_img, context, transform, controller
     qs, ks, heads, scales, R = _layer_args(handles)
     ctrl.reset()
     with torch.no_grad():
-        maps = ops.attention_maps([q.detach() for q in qs], [k.detach() for k in ks], heads, scales, R)   # (2B,T,R,R)
+        maps, stats = ops.attention_maps([q.detach() for q in qs], [k.detach() for k in ks], heads, scales, R,
+                                         return_stats=True)                                              # (2B,T,R,R)
         idx = torch.stack([select_tokens(maps[i], maps[B + i], top_k_strategy, furthest_point_num_samples, top_k,
                                          sigma, num_subjects) for i in range(B)])
-    sel = ops.selected_planes(maps, torch.cat([idx, idx], dim=0), qs, ks, heads, scales, R)               # (2B,K,R,R)
+    sel = ops.selected_planes(maps, torch.cat([idx, idx], dim=0), qs, ks, heads, scales, R, row_stats=stats)   # (2B,K,R,R)
     theta_inv = transform.inverse_theta()
     ar = _arange_like(idx.shape[1], idx)
     sharp, equiv = [], []

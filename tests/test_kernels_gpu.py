@@ -237,3 +237,60 @@ def test_resampling_matches_oracle(ops):
     y = torch.randn(5, 16, 16, generator=g)
     assert torch.allclose(ops.bilinear_upsample(_cu(y), 64).cpu().double(), O.bilinear_upsample(y.double(), 64), atol=1e-6)
     assert torch.equal(ops.bilinear_upsample(_cu(y), 16).cpu(), y)
+
+
+@pytest.mark.parametrize("spec,T,R,B,shared", [
+    ([(4, 64, 4), (8, 32, 2)], 40, 16, 2, True),             # dim_head 16, several pixel rows per tile
+    ([(8, 128, 2), (16, 64, 1)], 300, 32, 2, False),         # dim_head 64, two token halves, per-image k
+])
+def test_attention_maps_backward_tcgen05_matches_oracle_autograd(ops, spec, T, R, B, shared):
+    """tcgen05 backward (bf16 gradient GEMMs, fp32 accumulate): 1e-2 of the gradient's max."""
+    qs, ks, heads, sc = _random_layers(spec, T, B, 5, shared)
+    g = torch.Generator().manual_seed(9)
+    idx = torch.stack([torch.randperm(T, generator=g)[:6] for _ in range(B)])       # per-image token ids
+    w = torch.randn(B, idx.shape[1], R, R, generator=g)
+    q64 = [q.double().requires_grad_(True) for q in qs]
+    k64 = [k.double().requires_grad_(True) for k in ks]
+    loss = 0
+    for b in range(B):
+        m = O.attention_maps_from_qk([q[b] for q in q64], [k[0 if shared else b] for k in k64], heads, sc, R)
+        loss = loss + (m[idx[b]] * w[b].double()).sum()
+    grads = torch.autograd.grad(loss, q64 + k64)
+    qc = [_cu(q).requires_grad_(True) for q in qs]
+    kc = [_cu(k).requires_grad_(True) for k in ks]
+    with torch.no_grad():
+        full, stats = ops.attention_maps([q.detach() for q in qc], [k.detach() for k in kc], heads, sc, R, return_stats=True)
+    sel = ops.selected_planes(full, _cu(idx), qc, kc, heads, sc, R, row_stats=stats)
+    (sel * _cu(w)).sum().backward()
+    for got, want in zip([t.grad for t in qc + kc], grads):
+        scale = float(want.abs().max())
+        assert torch.isfinite(got).all()
+        assert (got.cpu().double() - want).abs().max().item() <= 1e-2 * scale
+    # and the CUDA-core backward (no statistics passed) agrees on the same problem
+    qd = [_cu(q).requires_grad_(True) for q in qs]
+    kd = [_cu(k).requires_grad_(True) for k in ks]
+    sel2 = ops.selected_planes(full, _cu(idx), qd, kd, heads, sc, R, precision="simt_f32")
+    (sel2 * _cu(w)).sum().backward()
+    for a, b_ in zip([t.grad for t in qc + kc], [t.grad for t in qd + kd]):
+        assert (a - b_).abs().max().item() <= 1e-2 * float(b_.abs().max())
+
+
+def test_backward_full_size_tcgen05_vs_cuda_core(ops):
+    """SD-2.1 head shape (d=64) at T=500, R=128 on a reduced channel count: tcgen05 vs fp32 CUDA cores."""
+    spec = [(16, 256, 4), (32, 128, 2)]
+    qs, ks, heads, sc = _random_layers(spec, 500, 2, 13, True)
+    g = torch.Generator().manual_seed(2)
+    idx = torch.stack([torch.randperm(500, generator=g)[:10] for _ in range(2)])
+    w = torch.randn(2, 10, 128, 128, generator=g)
+    grads = []
+    for prec in ("auto", "simt_f32"):
+        qc = [_cu(q).requires_grad_(True) for q in qs]
+        kc = [_cu(k).requires_grad_(True) for k in ks]
+        with torch.no_grad():
+            full, stats = ops.attention_maps([q.detach() for q in qc], [k.detach() for k in kc], heads, sc, 128, return_stats=True)
+        sel = ops.selected_planes(full, _cu(idx), qc, kc, heads, sc, 128, precision=prec, row_stats=stats if prec == "auto" else None)
+        (sel * _cu(w)).sum().backward()
+        grads.append([t.grad for t in qc + kc])
+    for a, b_ in zip(*grads):
+        assert torch.isfinite(a).all()
+        assert (a - b_).abs().max().item() <= 1e-2 * float(b_.abs().max())
