@@ -89,6 +89,71 @@ __global__ void tc_prep_q_kernel(const float* __restrict__ q, int s, int C, int 
   }
 }
 
+// Row-wise separable version of the above for s != R: one CTA = (output row y, image b, 256-channel
+// chunk).  Phase 1: the 4 source rows are combined with the y weights into shared memory
+// (s x 256 fp32); phase 2: every output pixel of the row is 4 shared-memory taps.  ~4.5 FMA per
+// output instead of 20, all global reads and writes coalesced (bf16x2 stores, 128 B per warp).
+constexpr int PREP_CH = 256;     // channels per CTA (128 threads x 2)
+template <int NPROD>
+__global__ void __launch_bounds__(128)
+tc_prep_q_rows_kernel(const float* __restrict__ q, int s, int C, int heads, int R, float mult,
+                      __nv_bfloat16* __restrict__ hi, __nv_bfloat16* __restrict__ lo) {
+  extern __shared__ float yc[];                 // [s][PREP_CH]
+  __shared__ float wxs[256 * 4];
+  __shared__ int ixs[256];
+  const int oy = blockIdx.x, b = blockIdx.y;
+  const int c = blockIdx.z * PREP_CH + threadIdx.x * 2;
+  const int d = C / heads, R2 = R * R;
+  const float ratio = static_cast<float>(s) / R;
+  for (int x = threadIdx.x; x < R; x += blockDim.x) {
+    int ix;
+    float w[4];
+    bicubic_coeffs(x, ratio, &ix, w);
+    ixs[x] = ix;
+    wxs[4 * x] = w[0]; wxs[4 * x + 1] = w[1]; wxs[4 * x + 2] = w[2]; wxs[4 * x + 3] = w[3];
+  }
+  if (c < C) {
+    int iy;
+    float wy[4];
+    bicubic_coeffs(oy, ratio, &iy, wy);
+    const float* src = q + static_cast<int64_t>(b) * s * s * C + c;
+    for (int sx = 0; sx < s; ++sx) {
+      float2 acc = make_float2(0.f, 0.f);
+#pragma unroll
+      for (int a = 0; a < 4; ++a) {
+        const int yy = min(max(iy - 1 + a, 0), s - 1);
+        const float2 t = __ldg(reinterpret_cast<const float2*>(src + static_cast<int64_t>(yy * s + sx) * C));
+        acc.x = fmaf(wy[a], t.x, acc.x);
+        acc.y = fmaf(wy[a], t.y, acc.y);
+      }
+      *reinterpret_cast<float2*>(yc + sx * PREP_CH + threadIdx.x * 2) = make_float2(acc.x * mult, acc.y * mult);
+    }
+  }
+  __syncthreads();
+  if (c >= C) return;
+  const int head = c / d, dd = c % d;
+  const int64_t o0 = ((static_cast<int64_t>(b) * heads + head) * R2 + static_cast<int64_t>(oy) * R) * d + dd;
+  for (int x = 0; x < R; ++x) {
+    const int ix = ixs[x];
+    float2 v = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int xx = min(max(ix - 1 + e, 0), s - 1);
+      const float w = wxs[4 * x + e];
+      const float2 t = *reinterpret_cast<const float2*>(yc + xx * PREP_CH + threadIdx.x * 2);
+      v.x = fmaf(w, t.x, v.x);
+      v.y = fmaf(w, t.y, v.y);
+    }
+    const int64_t o = o0 + static_cast<int64_t>(x) * d;
+    const __nv_bfloat16 hx = __float2bfloat16_rn(v.x), hy = __float2bfloat16_rn(v.y);
+    *reinterpret_cast<__nv_bfloat162*>(hi + o) = __halves2bfloat162(hx, hy);
+    if (NPROD == 3) {
+      *reinterpret_cast<__nv_bfloat162*>(lo + o) =
+          __halves2bfloat162(__float2bfloat16_rn(v.x - __bfloat162float(hx)), __float2bfloat16_rn(v.y - __bfloat162float(hy)));
+    }
+  }
+}
+
 // k (Bk, T, C) fp32 -> bf16 hi (+lo) laid out [bk*h + head][token][d]
 template <int NPROD>
 __global__ void tc_prep_k_kernel(const float* __restrict__ k, int T, int C, int heads, __nv_bfloat16* __restrict__ hi,
@@ -129,8 +194,13 @@ struct TcSmem {
   static constexpr int kDynamic = kTotal + 1024;                       // slack for manual 1024 B alignment
 };
 
+// 12 warps = 3 warpgroups: warpgroup 0 = {TMA producer, MMA issuer, 2 idle warps} gives its registers
+// back (setmaxnreg.dec), warpgroups 1-2 = 8 softmax warps take them (setmaxnreg.inc): the 128 fp32
+// accumulators + two in-flight TMEM chunks per thread do not fit the 168 registers a 384-thread CTA starts with.
+constexpr int FW_THREADS = 384;
+constexpr int FW_SOFTMAX_WARP0 = 4;
 template <int NPROD, int NSPLIT, bool SELECT>
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __launch_bounds__(FW_THREADS, 1)
 attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
   using SM = TcSmem<NPROD>;
   extern __shared__ uint8_t smem_raw[];
@@ -163,7 +233,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
     for (int i = 0; i < 2; ++i) {
       ptx::mbar_init(bar_tfull(i), 1);
       ptx::mbar_init(bar_tempty(i), TC_SOFTMAX_THREADS);
-      ptx::mbar_init(bar_xfull(i), TC_SOFTMAX_THREADS * NSPLIT);
+      ptx::mbar_init(bar_xfull(i), TC_SOFTMAX_THREADS);
     }
     ptx::fence_barrier_init();
   }
@@ -178,7 +248,9 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
 
-  if (warp == 0) {
+  if (warp < FW_SOFTMAX_WARP0) {
+    ptx::setmaxnreg_dec<56>();
+    if (warp == 0) {
     // =========================== TMA producer (one lane) ===================================
     if (lane == 0) {
       for (int l = 0; l < P.ops.n_layers; ++l) {
@@ -251,10 +323,12 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
         }
       }
     }
+    }
   } else {
+    ptx::setmaxnreg_inc<224>();
     // =========================== softmax / accumulate warps =================================
     const int quad = warp & 3;                 // TMEM lane quadrant this warp may access
-    const int ch = (warp - 2) >> 2;            // column half of the CTA's 256 tokens
+    const int ch = (warp - FW_SOFTMAX_WARP0) >> 2;   // column half of the CTA's 256 tokens
     const int row = quad * 32 + lane;
     const int col0 = ch * 128;
     const int ncol = max(0, min(128, P.T - (tok0 + col0)));
@@ -274,51 +348,73 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
         ptx::mbar_wait(bar_tfull(buf), par);
         ptx::tc_fence_after();
         const uint32_t taddr = t_lane + buf * TC_BN + col0;
-        uint32_t v[32];
-        // ---- pass A: row max over my columns
+        uint32_t v[2][16];
+        const int nch = (ncol + 15) >> 4;          // 16-column chunks I own (warp-uniform)
+        // ---- pass A: row max over my columns (TMEM loads software-pipelined one chunk ahead)
         float m = -INFINITY;
+        if (nch > 0) ptx::tmem_ld16(taddr, v[0]);
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          if (ncol > 32 * c) {
-            ptx::tmem_ld32(taddr + 32 * c, v);
+        for (int c = 0; c < 8; ++c) {
+          if (c < nch) {
             ptx::tmem_ld_wait();
+            if (c + 1 < nch) ptx::tmem_ld16(taddr + 16 * (c + 1), v[(c + 1) & 1]);
+            if (ncol >= 16 * (c + 1)) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (32 * c + j < ncol) m = fmaxf(m, __uint_as_float(v[j]));
+              for (int j = 0; j < 16; j += 2) m = ptx::max3(m, __uint_as_float(v[c & 1][j]), __uint_as_float(v[c & 1][j + 1]));
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j)
+                if (16 * c + j < ncol) m = fmaxf(m, __uint_as_float(v[c & 1][j]));
+            }
           }
         }
         // ---- pass B: exponentials (parked back in TMEM) and their sum
         float sum = 0.0f;
+        if (nch > 0) ptx::tmem_ld16(taddr, v[0]);
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          if (ncol > 32 * c) {
-            ptx::tmem_ld32(taddr + 32 * c, v);
+        for (int c = 0; c < 8; ++c) {
+          if (c < nch) {
             ptx::tmem_ld_wait();
+            if (c + 1 < nch) ptx::tmem_ld16(taddr + 16 * (c + 1), v[(c + 1) & 1]);
+            if (ncol >= 16 * (c + 1)) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const float e = (32 * c + j < ncol) ? ptx::ex2(__uint_as_float(v[j]) - m) : 0.0f;
-              sum += e;
-              v[j] = __float_as_uint(e);
+              for (int j = 0; j < 16; ++j) {
+                const float e = ptx::ex2(__uint_as_float(v[c & 1][j]) - m);
+                sum += e;
+                v[c & 1][j] = __float_as_uint(e);
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                const float e = (16 * c + j < ncol) ? ptx::ex2(__uint_as_float(v[c & 1][j]) - m) : 0.0f;
+                sum += e;
+                v[c & 1][j] = __float_as_uint(e);
+              }
             }
-            if (!SELECT) ptx::tmem_st32(taddr + 32 * c, v);
+            if (!SELECT) {
+              ptx::tmem_st16(taddr + 16 * c, v[c & 1]);
+              if (c + 2 < nch) ptx::tmem_st_wait();     // v[c & 1] is the target of the load issued next iteration
+            }
           }
         }
         if (!SELECT) ptx::tmem_st_wait();
-        // ---- exchange (max, sum) with the other column half and the other CTAs of the cluster
+        // ---- exchange (max, sum) with the other column half and the other CTAs of the cluster.
+        // Local slot: plain store + arrive.  Remote slot: st.async, which completes bytes on the
+        // peer's mbarrier itself (no cluster-scope release fence, no L1 invalidate on the waiter).
         {
-          const uint32_t slot = base + SM::kStatsOff + ((buf * 4 + part) * TC_BM + row) * 8;
-          if (NSPLIT == 1) {
-            stats[(buf * 4 + part) * TC_BM + row] = make_float2(m, sum);
-            ptx::mbar_arrive(bar_xfull(buf));
-            ptx::mbar_wait(bar_xfull(buf), par);
-          } else {
+          const int sidx = (buf * 4 + part) * TC_BM + row;
+          stats[sidx] = make_float2(m, sum);
+          if (NSPLIT > 1) {
+            const uint32_t slot = base + SM::kStatsOff + sidx * 8;
 #pragma unroll
-            for (uint32_t dst = 0; dst < static_cast<uint32_t>(NSPLIT); ++dst) {
-              ptx::st_cluster_v2(ptx::mapa(slot, dst), m, sum);
-              ptx::mbar_arrive_cluster(ptx::mapa(bar_xfull(buf), dst));
-            }
-            ptx::mbar_wait_cluster(bar_xfull(buf), par);
+            for (uint32_t dst = 0; dst < static_cast<uint32_t>(NSPLIT); ++dst)
+              if (dst != cta_rank) ptx::st_async_v2(ptx::mapa(slot, dst), m, sum, ptx::mapa(bar_xfull(buf), dst));
+            if (warp == FW_SOFTMAX_WARP0 && lane == 0) ptx::mbar_arrive_expect_tx(bar_xfull(buf), (NSPLIT - 1) * TC_SOFTMAX_THREADS * 8);
+            else ptx::mbar_arrive(bar_xfull(buf));
+          } else {
+            ptx::mbar_arrive(bar_xfull(buf));
           }
+          ptx::mbar_wait(bar_xfull(buf), par);
         }
         float mg = -INFINITY;
 #pragma unroll
@@ -335,13 +431,14 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
         const float cf = ncol > 0 ? wgt * ptx::ex2(m - mg) / total : 0.0f;
         // ---- pass C: accumulate weight/heads * P
         if (!SELECT) {
+          if (nch > 0) ptx::tmem_ld16(taddr, v[0]);
 #pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            if (ncol > 32 * c) {
-              ptx::tmem_ld32(taddr + 32 * c, v);
+          for (int c = 0; c < 8; ++c) {
+            if (c < nch) {
               ptx::tmem_ld_wait();
+              if (c + 1 < nch) ptx::tmem_ld16(taddr + 16 * (c + 1), v[(c + 1) & 1]);
 #pragma unroll
-              for (int j = 0; j < 32; ++j) acc[32 * c + j] = fmaf(cf, __uint_as_float(v[j]), acc[32 * c + j]);
+              for (int j = 0; j < 16; ++j) acc[16 * c + j] = fmaf(cf, __uint_as_float(v[c & 1][j]), acc[16 * c + j]);
             }
           }
         } else {
@@ -459,7 +556,7 @@ static int launch_tc(const TcParams& P, int B, int R2, cudaStream_t st) {
   SKP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::kDynamic));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(static_cast<unsigned>(R2 / TC_BM * NSPLIT), static_cast<unsigned>(B), 1);
-  cfg.blockDim = dim3(TC_THREADS, 1, 1);
+  cfg.blockDim = dim3(FW_THREADS, 1, 1);
   cfg.dynamicSmemBytes = SM::kDynamic;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
@@ -494,11 +591,24 @@ int tc_prepare(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R
     if (x3) { k_lo = reinterpret_cast<__nv_bfloat16*>(ws); ws += kbytes; }
     const float mult = a.scale * 1.4426950408889634f;
     dim3 gq(R2, B), gk(T, Bk);
+    const bool rows = a.s != R && R <= 256 && a.s <= 64 && (a.C / a.heads) % 2 == 0;
+    dim3 gr(R, B, (a.C + PREP_CH - 1) / PREP_CH);
+    const size_t rsm = static_cast<size_t>(a.s) * PREP_CH * sizeof(float);
     if (x3) {
-      tc_prep_q_kernel<3><<<(::skp::note_launch(), gq), 256, 0, st>>>(a.q, a.s, a.C, a.heads, R, mult, q_hi, q_lo);
+      if (rows) {
+        SKP_CUDA(cudaFuncSetAttribute(tc_prep_q_rows_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * PREP_CH * 4));
+        tc_prep_q_rows_kernel<3><<<(::skp::note_launch(), gr), 128, rsm, st>>>(a.q, a.s, a.C, a.heads, R, mult, q_hi, q_lo);
+      } else {
+        tc_prep_q_kernel<3><<<(::skp::note_launch(), gq), 256, 0, st>>>(a.q, a.s, a.C, a.heads, R, mult, q_hi, q_lo);
+      }
       tc_prep_k_kernel<3><<<(::skp::note_launch(), gk), 256, 0, st>>>(a.k, T, a.C, a.heads, k_hi, k_lo);
     } else {
-      tc_prep_q_kernel<1><<<(::skp::note_launch(), gq), 256, 0, st>>>(a.q, a.s, a.C, a.heads, R, mult, q_hi, q_lo);
+      if (rows) {
+        SKP_CUDA(cudaFuncSetAttribute(tc_prep_q_rows_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * PREP_CH * 4));
+        tc_prep_q_rows_kernel<1><<<(::skp::note_launch(), gr), 128, rsm, st>>>(a.q, a.s, a.C, a.heads, R, mult, q_hi, q_lo);
+      } else {
+        tc_prep_q_kernel<1><<<(::skp::note_launch(), gq), 256, 0, st>>>(a.q, a.s, a.C, a.heads, R, mult, q_hi, q_lo);
+      }
       tc_prep_k_kernel<1><<<(::skp::note_launch(), gk), 256, 0, st>>>(a.k, T, a.C, a.heads, k_hi, k_lo);
     }
     SKP_LAUNCH_CHECK();

@@ -92,16 +92,6 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 __device__ __forceinline__ void named_bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-      : "r"(taddr)
-      : "memory");
-}
-
 struct BwUnit {
   int l, head, hg, b, tile;
 };
@@ -318,7 +308,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       float delta = 0.0f;
       {
         uint32_t sv[BW_SEL];
-        tmem_ld16(tm_sel + lane_off, sv);
+        ptx::tmem_ld16(tm_sel + lane_off, sv);
         ptx::tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < BW_SEL; ++j) {
