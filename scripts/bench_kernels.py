@@ -1,0 +1,38 @@
+"""Kernel-only timing of the attention-map forward / backward C-ABI calls at BASELINE shapes
+(SD-2.1-base capture set, T=500, R=128, B images).  python scripts/bench_kernels.py [B] [precision]"""
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from stablekeypoints_b200 import ops, _lib
+
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 8
+prec = sys.argv[2] if len(sys.argv) > 2 else "auto"
+dev = "cuda:0"
+spec = [(16, 1280, 20), (16, 1280, 20), (16, 1280, 20), (32, 640, 10)]
+g = torch.Generator().manual_seed(0)
+qs = [(torch.randn(B, s * s, C, generator=g) * 1.5).to(dev).requires_grad_(True) for s, C, h in spec]
+ks = [torch.randn(1, 500, C, generator=g).to(dev).requires_grad_(True) for s, C, h in spec]
+heads = [h for _, _, h in spec]
+sc = [(C // h) ** -0.5 for _, C, h in spec]
+idx = torch.stack([torch.randperm(500, generator=g)[:10] for _ in range(B)]).to(dev)
+w = torch.randn(B, 10, 128, 128, generator=g).to(dev)
+
+
+def run():
+    with torch.no_grad():
+        full, stats = ops.attention_maps([q.detach() for q in qs], [k.detach() for k in ks], heads, sc, 128, precision=prec, return_stats=True)
+    sel = ops.selected_planes(full, idx, qs, ks, heads, sc, 128, precision=prec, row_stats=stats)
+    (sel * w).sum().backward()
+
+
+for _ in range(3):
+    run()
+_lib.timing_start()
+for _ in range(10):
+    run()
+t = _lib.timing_summary()
+flops = 2 * 128 * 128 * 500 * (3 * 1280 + 640) * B
+for k, v in t.items():
+    ms = v["ms"] / v["calls"]
+    mult = 1 if "fwd" in k else 2
+    print(f"{k}: {ms:.3f} ms/call  ({ms / B * 1e3:.0f} us/image)  {mult * flops / ms / 1e9:.1f} TFLOP/s algorithmic")

@@ -16,6 +16,8 @@
 //   dq   += U^T dQ'             (adjoint of the bicubic upsample, separable: x-gather through
 //                                shared memory, y taps as red.global.add.v4.f32)
 // No cluster, no cross-CTA exchange: the two token halves only meet in the global reductions.
+#include <cstdlib>
+
 #include "attn_tc.cuh"
 
 namespace skp {
@@ -25,6 +27,7 @@ constexpr int BW_KSEL_BYTES = BW_SEL * 128;   // 16 rows x 128 B
 constexpr int BW_DS_BYTES = TC_BM * TC_BN * 2;   // 64 KB: dS tile, 4 slabs of [128 px][64 tok] bf16
 constexpr int BW_WXT_FLOATS = 5 * 256;        // x-adjoint table: s * (5 * R/s) = 5 R floats, R <= 256
 constexpr float kLog2eBw = 1.4426950408889634f;
+constexpr int BW_STG_LD = 68;          // fp32 staging row pitch (64 + 4): conflict-free float4 stores with lane = row
 
 struct BwdParams {
   TcOperands ops;
@@ -37,6 +40,8 @@ struct BwdParams {
   const int64_t* token_idx;
   const float* dmaps_sel;                   // (B, n_idx, R2)
   const float* row_stats;                   // (B, total_heads, R2, 2)
+  unsigned long long* prof;                 // SKP_BWD_DBG & 8: per-phase cycle counters of CTA 0
+  int dbg;                                  // SKP_BWD_DBG bits (profiling experiments only): 1 no reductions, 2 no adjoint, 4 no drain
 };
 
 // k_sel[(b*h + head)][j][dd] = k[bk][token_idx[b][j]][head*d + dd]  (rows j >= n_idx are zero)
@@ -120,8 +125,11 @@ __device__ __forceinline__ bool bw_flush_after(const BwdParams& P, int u, int u_
   return (u - hg * per_head) / P.tiles != (u + 1 - hg * per_head) / P.tiles;
 }
 
+// 12 warps = 3 warpgroups: {TMA, MMA, 2 idle} shrink to 56 registers, the 8 softmax warps grow to 224
+constexpr int BW_THREADS = 384;
+constexpr int BW_SOFTMAX_WARP0 = 4;
 template <int NPROD, int NH>
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __launch_bounds__(BW_THREADS, 1)
 attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
   using SM = BwSmem<NPROD>;
   extern __shared__ uint8_t smem_raw[];
@@ -167,6 +175,8 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
   const uint32_t tmem_base = *tmem_ptr;
   const uint32_t tm_S = tmem_base, tm_dQ = tmem_base + 256, tm_dK = tmem_base + 320, tm_sel = tmem_base + 448;
 
+  if (warp < BW_SOFTMAX_WARP0) {
+  ptx::setmaxnreg_dec<56>();
   if (warp == 0) {
     // =========================== TMA producer (one lane) ===================================
     if (lane == 0) {
@@ -210,8 +220,10 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         const int st = it & 1;
         const uint32_t qs = base + SM::kQOff + st * SM::kQStage;
         const uint32_t ks = base + SM::kKOff, ksel = base + SM::kKselOff, dsb = base + SM::kDsOff;
+        long long c0 = clock64();
         ptx::mbar_wait(bar_qfull(st), (it >> 1) & 1u);
         ptx::tc_fence_after();
+        if (P.prof && blockIdx.x == 0) atomicAdd(P.prof + 0, clock64() - c0);
         // ---- S = Q' K^T (256 tokens) and S_sel = Q' K_sel^T (16 tokens)
         const uint32_t id_S = bw_idesc(TC_BM, TC_BN, 0, 0), id_sel = bw_idesc(TC_BM, BW_SEL, 0, 0);
         const int nk16 = d / 16;
@@ -235,8 +247,10 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         }
         ptx::umma_commit(bar_sfull);
         // ---- wait for dS (bf16, [px][tok]) in shared memory
+        c0 = clock64();
         ptx::mbar_wait(bar_dsfull, it & 1u);
         ptx::tc_fence_after();
+        if (P.prof && blockIdx.x == 0) atomicAdd(P.prof + 1, clock64() - c0);
         // dQ' (128 px x d) = dS (K-major A, K = 256 tokens) * K_hi (MN-major B: rows = tokens)
         const uint32_t id_dq = bw_idesc(TC_BM, d, 0, 1);
         const int nkt = (ntok + 15) / 16;
@@ -254,12 +268,14 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         dk_fresh = bw_flush_after(P, u, u_end);
       }
     }
+  }
   } else {
+    ptx::setmaxnreg_inc<224>();
     // =========================== softmax-recompute / dS / drain warps ========================
     const int quad = warp & 3;                 // TMEM lane quadrant this warp may access
-    const int ch = (warp - 2) >> 2;            // column half of the CTA's 256 tokens
+    const int ch = (warp - BW_SOFTMAX_WARP0) >> 2;   // column half of the CTA's 256 tokens
     const int row = quad * 32 + lane;
-    const int stid = threadIdx.x - 64;         // 0..255
+    const int stid = threadIdx.x - BW_SOFTMAX_WARP0 * 32;   // 0..255
     const int col0 = ch * 128;
     const int ncol = max(0, min(128, ntok - col0));
     const uint32_t lane_off = static_cast<uint32_t>(quad * 32) << 16;
@@ -268,6 +284,16 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
     const int R = P.R;
     uint32_t it = 0;
     int prev_l = -1, prev_b = -1;
+    float2 nx_ml = make_float2(0.f, 1.f);
+    float nx_dp[BW_SEL];
+    auto load_row = [&](int uu, float2& ml, float (&dpr)[BW_SEL]) {
+      const BwUnit y = bw_decode(P, uu);
+      const int pp = y.tile * TC_BM + row;
+      ml = __ldg(reinterpret_cast<const float2*>(P.row_stats) + (static_cast<int64_t>(y.b) * P.ops.total_heads + y.hg) * P.R2 + pp);
+#pragma unroll
+      for (int j = 0; j < BW_SEL; ++j)
+        dpr[j] = j < P.n_idx ? __ldg(P.dmaps_sel + (static_cast<int64_t>(y.b) * P.n_idx + j) * P.R2 + pp) : 0.0f;
+    };
     for (int u = u_begin; u < u_end; ++u, ++it) {
       const BwUnit x = bw_decode(P, u);
       const int d = P.ops.d[x.l], s = P.s[x.l], C = P.C[x.l];
@@ -295,16 +321,21 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         prev_l = x.l;
         prev_b = x.b;
       }
-      const int p = x.tile * TC_BM + row;
-      const float2 ml = reinterpret_cast<const float2*>(P.row_stats)[(static_cast<int64_t>(x.b) * P.ops.total_heads + x.hg) * P.R2 + p];
-      const float m = ml.x, inv_l = 1.0f / ml.y;
+      // (m, l) and the n_idx upstream gradients of this row were fetched one unit ahead (nx_*): a unit
+      // is too short to hide a DRAM round trip behind itself
+      if (u == u_begin) load_row(u, nx_ml, nx_dp);
+      const float m = nx_ml.x, inv_l = 1.0f / nx_ml.y;
       float dp[BW_SEL];
 #pragma unroll
-      for (int j = 0; j < BW_SEL; ++j)
-        dp[j] = j < P.n_idx ? wgt * __ldg(P.dmaps_sel + (static_cast<int64_t>(x.b) * P.n_idx + j) * P.R2 + p) : 0.0f;
+      for (int j = 0; j < BW_SEL; ++j) dp[j] = wgt * nx_dp[j];
+      if (u + 1 < u_end) load_row(u + 1, nx_ml, nx_dp);
 
+      const bool pr = P.prof && blockIdx.x == 0 && stid == 0;
+      long long c1 = clock64();
       ptx::mbar_wait(bar_sfull, it & 1u);
       ptx::tc_fence_after();
+      if (pr) P.prof[2] += clock64() - c1;
+      c1 = clock64();
       float delta = 0.0f;
       {
         uint32_t sv[BW_SEL];
@@ -320,24 +351,32 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       }
       // ---- dS = P * (dP - delta): dense part -P*delta for my 128 columns, then the n_idx corrections
       const float nd = -delta * inv_l;
+      {
+        uint32_t v[2][32];
+        const bool full = ncol == 128;
+        ptx::tmem_ld32(tm_S + lane_off + col0, v[0]);
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        uint32_t v[32];
-        ptx::tmem_ld32(tm_S + lane_off + col0 + 32 * c, v);
-        ptx::tmem_ld_wait();
-        uint32_t pk[16];
+        for (int c = 0; c < 4; ++c) {
+          ptx::tmem_ld_wait();
+          if (c < 3) ptx::tmem_ld32(tm_S + lane_off + col0 + 32 * (c + 1), v[(c + 1) & 1]);
+          uint32_t pk[16];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const float e0 = (32 * c + 2 * j < ncol) ? ptx::ex2(__uint_as_float(v[2 * j]) - m) * nd : 0.0f;
-          const float e1 = (32 * c + 2 * j + 1 < ncol) ? ptx::ex2(__uint_as_float(v[2 * j + 1]) - m) * nd : 0.0f;
-          const __nv_bfloat162 h2 = __floats2bfloat162_rn(e0, e1);
-          pk[j] = *reinterpret_cast<const uint32_t*>(&h2);
-        }
+          for (int j = 0; j < 16; ++j) {
+            float e0 = ptx::ex2(__uint_as_float(v[c & 1][2 * j]) - m) * nd;
+            float e1 = ptx::ex2(__uint_as_float(v[c & 1][2 * j + 1]) - m) * nd;
+            if (!full) {
+              e0 = (32 * c + 2 * j < ncol) ? e0 : 0.0f;
+              e1 = (32 * c + 2 * j + 1 < ncol) ? e1 : 0.0f;
+            }
+            const __nv_bfloat162 h2 = __floats2bfloat162_rn(e0, e1);
+            pk[j] = *reinterpret_cast<const uint32_t*>(&h2);
+          }
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int cc = col0 + 32 * c + 8 * q;
-          const uint32_t off = (cc >> 6) * 16384 + row * 128 + ((((cc & 63) >> 3) ^ (row & 7)) << 4);
-          *reinterpret_cast<uint4*>(ds_ptr + off) = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+          for (int q = 0; q < 4; ++q) {
+            const int cc = col0 + 32 * c + 8 * q;
+            const uint32_t off = (cc >> 6) * 16384 + row * 128 + ((((cc & 63) >> 3) ^ (row & 7)) << 4);
+            *reinterpret_cast<uint4*>(ds_ptr + off) = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+          }
         }
       }
 #pragma unroll
@@ -349,21 +388,27 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
           *e = __float2bfloat16_rn(__bfloat162float(*e) + dp[j]);
         }
       }
+      if (pr) P.prof[3] += clock64() - c1;
+      c1 = clock64();
       ptx::fence_proxy_async();
       ptx::tc_fence_before();
       ptx::mbar_arrive(bar_dsfull);
+      if (pr) P.prof[4] += clock64() - c1;
+      c1 = clock64();
 
       // ---- dQ' tile: TMEM -> fp32 staging (aliases the dS tile, free once the MMAs are done)
       ptx::mbar_wait(bar_mmadone, it & 1u);
       ptx::tc_fence_after();
-      if (ch * 32 < d) {
+      if (pr) P.prof[5] += clock64() - c1;
+      c1 = clock64();
+      if (ch * 32 < d && !(P.dbg & 4)) {
         uint32_t v[32];
         ptx::tmem_ld32(tm_dQ + lane_off + ch * 32, v);
         ptx::tmem_ld_wait();
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
           const int cidx = ch * 8 + q;
-          *reinterpret_cast<float4*>(stg + row * 64 + ((cidx ^ (row & 7)) << 2)) =
+          *reinterpret_cast<float4*>(stg + row * BW_STG_LD + (cidx << 2)) =
               make_float4(__uint_as_float(v[4 * q]) * scale, __uint_as_float(v[4 * q + 1]) * scale,
                           __uint_as_float(v[4 * q + 2]) * scale, __uint_as_float(v[4 * q + 3]) * scale);
         }
@@ -380,31 +425,65 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         const int n_out = rows_per_tile * s * n_c4;
         const float ratio = static_cast<float>(s) / R;
         float* dq = P.dq[x.l] + static_cast<int64_t>(x.b) * s * s * C + x.head * d;
-        for (int o = stid; o < n_out; o += TC_SOFTMAX_THREADS) {
+        for (int o = stid; o < ((P.dbg & 2) ? 0 : n_out); o += TC_SOFTMAX_THREADS) {
           const int c4 = o % n_c4, sx = (o / n_c4) % s, yy = o / (n_c4 * s);
           const int xlo = max(0, (sx - 2) * up);
-          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+          // taps outside the tile's x span get weight 0 and a clamped (valid) row: fixed trip count,
+          // four independent accumulators so the shared-memory loads pipeline
+          float4 a4[4];
+#pragma unroll
+          for (int g = 0; g < 4; ++g) a4[g] = make_float4(0.f, 0.f, 0.f, 0.f);
           const int j0 = max(0, x0 - xlo), j1 = min(nj, x0 + span - xlo);
-          for (int j = j0; j < j1; ++j) {
-            const float w = wxt[sx * nj + j];
-            const int r = yy * span + (xlo + j - x0);
-            const float4 t4 = *reinterpret_cast<const float4*>(stg + r * 64 + ((c4 ^ (r & 7)) << 2));
-            acc.x = fmaf(w, t4.x, acc.x);
-            acc.y = fmaf(w, t4.y, acc.y);
-            acc.z = fmaf(w, t4.z, acc.z);
-            acc.w = fmaf(w, t4.w, acc.w);
+          const float* wrow = wxt + sx * nj;
+          if (span == R && R == TC_BM) {
+            // one whole image row per tile: every tap of the table is inside the tile (taps past the row
+            // end have weight 0 and read finite bytes of the dS area), addresses are base + immediates
+            const float4* src = reinterpret_cast<const float4*>(stg) + xlo * (BW_STG_LD / 4) + c4;
+#pragma unroll 2
+            for (int jb = 0; jb < nj; jb += 4) {
+#pragma unroll
+              for (int g = 0; g < 4; ++g) {
+                const float w = wrow[jb + g];
+                const float4 t4 = src[(jb + g) * (BW_STG_LD / 4)];
+                a4[g].x = fmaf(w, t4.x, a4[g].x);
+                a4[g].y = fmaf(w, t4.y, a4[g].y);
+                a4[g].z = fmaf(w, t4.z, a4[g].z);
+                a4[g].w = fmaf(w, t4.w, a4[g].w);
+              }
+            }
+          } else {
+            for (int jb = 0; jb < nj; jb += 4) {
+#pragma unroll
+              for (int g = 0; g < 4; ++g) {
+                const int j = jb + g;
+                const bool ok = j >= j0 && j < j1;
+                const float w = ok ? wrow[j] : 0.0f;
+                const int r = yy * span + min(max(xlo + j - x0, 0), span - 1);
+                const float4 t4 = *reinterpret_cast<const float4*>(stg + r * BW_STG_LD + (c4 << 2));
+                a4[g].x = fmaf(w, t4.x, a4[g].x);
+                a4[g].y = fmaf(w, t4.y, a4[g].y);
+                a4[g].z = fmaf(w, t4.z, a4[g].z);
+                a4[g].w = fmaf(w, t4.w, a4[g].w);
+              }
+            }
           }
+          float4 acc;
+          acc.x = (a4[0].x + a4[1].x) + (a4[2].x + a4[3].x);
+          acc.y = (a4[0].y + a4[1].y) + (a4[2].y + a4[3].y);
+          acc.z = (a4[0].z + a4[1].z) + (a4[2].z + a4[3].z);
+          acc.w = (a4[0].w + a4[1].w) + (a4[2].w + a4[3].w);
           int iy;
           float wy[4];
           bicubic_coeffs(y0 + yy, ratio, &iy, wy);
 #pragma unroll
           for (int a = 0; a < 4; ++a) {
             const int sy = min(max(iy - 1 + a, 0), s - 1);
-            red_add_v4(dq + static_cast<int64_t>(sy * s + sx) * C + c4 * 4, wy[a] * acc.x, wy[a] * acc.y, wy[a] * acc.z, wy[a] * acc.w);
+            if (!(P.dbg & 1)) red_add_v4(dq + static_cast<int64_t>(sy * s + sx) * C + c4 * 4, wy[a] * acc.x, wy[a] * acc.y, wy[a] * acc.z, wy[a] * acc.w);
           }
         }
       }
       named_bar_sync(2, TC_SOFTMAX_THREADS);
+      if (pr) { P.prof[6] += clock64() - c1; P.prof[7] += 1; }
       // ---- dK: flush the TMEM accumulator when this head (or image, for a per-image k) is finished
       if (bw_flush_after(P, u, u_end) && ch < n_mh) {
         const int t = tok0 + ch * 128 + row;
@@ -467,7 +546,7 @@ static int launch_bwd(const BwdParams& P, cudaStream_t st) {
   using SM = BwSmem<NPROD>;
   auto kern = attn_map_bwd_tc_kernel<NPROD, NH>;
   SKP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::kDynamic));
-  kern<<<(::skp::note_launch(), P.n_chunks * NH), TC_THREADS, SM::kDynamic, st>>>(P);
+  kern<<<(::skp::note_launch(), P.n_chunks * NH), BW_THREADS, SM::kDynamic, st>>>(P);
   SKP_LAUNCH_CHECK();
   return SKP_OK;
 }
@@ -507,10 +586,26 @@ int attn_map_bwd_tc(const skp_attn_layer* h_layers, int n_layers, int B, int T, 
   P.B = B; P.T = T; P.R = R; P.R2 = R * R; P.n_idx = n_idx; P.tiles = R * R / TC_BM;
   P.idx_stride = idx_stride; P.token_idx = token_idx; P.dmaps_sel = dmaps_sel; P.row_stats = row_stats;
   P.n_units = P.ops.total_heads * B * P.tiles;
+  if (const char* e = getenv("SKP_BWD_DBG")) P.dbg = atoi(e);
+  static unsigned long long* d_prof = nullptr;
+  if (P.dbg & 8) {
+    if (!d_prof) cudaMalloc(&d_prof, 64);
+    cudaMemsetAsync(d_prof, 0, 64, st);
+    P.prof = d_prof;
+  }
   const int nh = T > TC_BN ? 2 : 1;
   P.n_chunks = kNumSMs / nh < P.n_units ? kNumSMs / nh : P.n_units;
-  if (x3) return nh == 2 ? launch_bwd<3, 2>(P, st) : launch_bwd<3, 1>(P, st);
-  return nh == 2 ? launch_bwd<1, 2>(P, st) : launch_bwd<1, 1>(P, st);
+  if (x3) rc = nh == 2 ? launch_bwd<3, 2>(P, st) : launch_bwd<3, 1>(P, st);
+  else rc = nh == 2 ? launch_bwd<1, 2>(P, st) : launch_bwd<1, 1>(P, st);
+  if (P.dbg & 8) {
+    unsigned long long h[8];
+    cudaStreamSynchronize(st);
+    cudaMemcpy(h, d_prof, 64, cudaMemcpyDeviceToHost);
+    const double n = h[7] ? static_cast<double>(h[7]) : 1.0;
+    fprintf(stderr, "[bwd prof, cycles/unit over %llu units] mma: wait q_full %.0f, wait ds_full %.0f | softmax: wait s_full %.0f, dS %.0f, "
+            "fence+arrive %.0f, wait mma_done %.0f, drain+adjoint %.0f\n", h[7], h[0] / n, h[1] / n, h[2] / n, h[3] / n, h[4] / n, h[5] / n, h[6] / n);
+  }
+  return rc;
 }
 
 }  // namespace skp
