@@ -185,20 +185,33 @@ struct TcSmem {
   static constexpr int kStages = NPROD == 3 ? 2 : 4;
   static constexpr int kStageBytes = (NPROD == 3 ? 2 : 1) * (TC_A_BYTES + TC_B_BYTES);
   static constexpr int kTiles = kStages * kStageBytes;                 // 192 KB either way
-  static constexpr int kBarOff = kTiles;                               // full[], empty[], tfull[2], tempty[2], xfull[2]
-  static constexpr int kNumBars = 2 * kStages + 6;
+  static constexpr int kBarOff = kTiles;                               // full[], empty[], tfull[2][2], tempty[2][2], xfull[2]
+  static constexpr int kNumBars = 2 * kStages + 10;
   static constexpr int kTmemPtrOff = kBarOff + 8 * kNumBars;
   static constexpr int kTokOff = kTmemPtrOff + 8;                      // int tok[TC_MAX_SEL]
-  static constexpr int kStatsOff = kTokOff + 4 * TC_MAX_SEL;           // float2 stats[2 buf][4 part][128 row]
-  static constexpr int kTotal = kStatsOff + 2 * 4 * TC_BM * 8;
+  static constexpr int kStatsOff = kTokOff + 4 * TC_MAX_SEL;           // float2 stats[2 buf][8 part][128 row]
+  static constexpr int kTotal = kStatsOff + 2 * 8 * TC_BM * 8;
   static constexpr int kDynamic = kTotal + 1024;                       // slack for manual 1024 B alignment
 };
 
-// 12 warps = 3 warpgroups: warpgroup 0 = {TMA producer, MMA issuer, 2 idle warps} gives its registers
-// back (setmaxnreg.dec), warpgroups 1-2 = 8 softmax warps take them (setmaxnreg.inc): the 128 fp32
-// accumulators + two in-flight TMEM chunks per thread do not fit the 168 registers a 384-thread CTA starts with.
-constexpr int FW_THREADS = 384;
+// 2^d for an integer-valued d <= 0 (or -inf), flushed to 0 below 2^-126, without MUFU: the integer lands in the
+// low mantissa bits of d + 1.5 * 2^23 and is shifted into the exponent field.
+__device__ __forceinline__ float pow2_int(float d) {
+  const int bits = __float_as_int(fmaxf(d, -127.0f) + 12582912.0f);
+  return __int_as_float((bits << 23) + 0x3f800000);
+}
+
+// 20 warps = 5 warpgroups: warpgroup 0 = {TMA producer, MMA issuer, 2 idle warps} gives registers back
+// (setmaxnreg.dec), warpgroups 1-4 = 16 softmax warps take them (setmaxnreg.inc): 64 fp32 accumulators + one
+// 32-column TMEM chunk per thread.  The softmax side is latency bound (dependent FMNMX / FADD chains, MUFU and
+// tcgen05.ld round trips), so it runs four warps per scheduler rather than two wide ones.
 constexpr int FW_SOFTMAX_WARP0 = 4;
+constexpr int FW_PARTS = 4;                                   // column quarters per CTA
+constexpr int FW_MAX_PARTS = 2 * FW_PARTS;                    // parts of a cluster of two
+constexpr int FW_QCOLS = TC_BN / FW_PARTS;                    // 64 tokens per thread
+constexpr int FW_SOFTMAX_THREADS = 128 * FW_PARTS;            // 16 warps
+constexpr int FW_THREADS = 32 * FW_SOFTMAX_WARP0 + FW_SOFTMAX_THREADS;   // 640
+constexpr int FW_SOFTMAX_REGS = 112;   // 128*32 + 512*112 == 640*96: setmaxnreg.inc only draws from what .dec released
 template <int NPROD, int NSPLIT, bool SELECT>
 __global__ void __launch_bounds__(FW_THREADS, 1)
 attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
@@ -217,9 +230,10 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
 
   auto bar_full = [&](int s) { return base + SM::kBarOff + 8u * s; };
   auto bar_empty = [&](int s) { return base + SM::kBarOff + 8u * (SM::kStages + s); };
-  auto bar_tfull = [&](int i) { return base + SM::kBarOff + 8u * (2 * SM::kStages + i); };
-  auto bar_tempty = [&](int i) { return base + SM::kBarOff + 8u * (2 * SM::kStages + 2 + i); };
-  auto bar_xfull = [&](int i) { return base + SM::kBarOff + 8u * (2 * SM::kStages + 4 + i); };
+  // TMEM buffers are handed over in column halves: tfull/tempty[buffer][half]
+  auto bar_tfull = [&](int i, int hf) { return base + SM::kBarOff + 8u * (2 * SM::kStages + 2 * i + hf); };
+  auto bar_tempty = [&](int i, int hf) { return base + SM::kBarOff + 8u * (2 * SM::kStages + 4 + 2 * i + hf); };
+  auto bar_xfull = [&](int i) { return base + SM::kBarOff + 8u * (2 * SM::kStages + 8 + i); };
   volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(base_ptr + SM::kTmemPtrOff);
   int* tok_s = reinterpret_cast<int*>(base_ptr + SM::kTokOff);
   float2* stats = reinterpret_cast<float2*>(base_ptr + SM::kStatsOff);
@@ -231,9 +245,11 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
       ptx::mbar_init(bar_empty(s), 1);
     }
     for (int i = 0; i < 2; ++i) {
-      ptx::mbar_init(bar_tfull(i), 1);
-      ptx::mbar_init(bar_tempty(i), TC_SOFTMAX_THREADS);
-      ptx::mbar_init(bar_xfull(i), TC_SOFTMAX_THREADS);
+      for (int hf = 0; hf < 2; ++hf) {
+        ptx::mbar_init(bar_tfull(i, hf), 1);
+        ptx::mbar_init(bar_tempty(i, hf), FW_SOFTMAX_THREADS / 2);
+      }
+      ptx::mbar_init(bar_xfull(i), FW_SOFTMAX_THREADS);
     }
     ptx::fence_barrier_init();
   }
@@ -249,7 +265,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
   const uint32_t tmem_base = *tmem_ptr;
 
   if (warp < FW_SOFTMAX_WARP0) {
-    ptx::setmaxnreg_dec<56>();
+    ptx::setmaxnreg_dec<32>();
     if (warp == 0) {
     // =========================== TMA producer (one lane) ===================================
     if (lane == 0) {
@@ -287,180 +303,212 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
   } else if (warp == 1) {
     // =========================== MMA issuer (one lane) =====================================
     if (lane == 0) {
-      constexpr uint32_t idesc = ptx::umma_idesc_bf16(TC_BM, TC_BN);
+      // Each unit is issued as two N = 128 column halves with their own barriers: the softmax warps of
+      // half 1 start ~half a unit's MMA time after those of half 0 and stay out of phase with them, so
+      // one group's MUFU-bound exponentials overlap the other's max / accumulate passes.
+      constexpr uint32_t idesc = ptx::umma_idesc_bf16(TC_BM, TC_BN / 2);
+      constexpr uint32_t kHalfB = (TC_BN / 2) * 128;     // byte offset of token row 128 in a K tile
       uint32_t it = 0, u = 0;
       for (int l = 0; l < P.ops.n_layers; ++l) {
         const int h = P.ops.heads[l], d = P.ops.d[l];
         const int nkb = (d + TC_BK - 1) / TC_BK;
         for (int head = 0; head < h; ++head, ++u) {
           const uint32_t buf = u & 1u;
-          ptx::mbar_wait(bar_tempty(buf), ((u >> 1) & 1u) ^ 1u);   // softmax drained this TMEM buffer
-          ptx::tc_fence_after();
-          const uint32_t d_tmem = tmem_base + buf * TC_BN;
           for (int kb = 0; kb < nkb; ++kb, ++it) {
             const int s = it % SM::kStages;
             ptx::mbar_wait(bar_full(s), (it / SM::kStages) & 1u);
             ptx::tc_fence_after();
             const uint32_t st = base + s * SM::kStageBytes;
             const int nk16 = (min(TC_BK, d - kb * TC_BK) + 15) / 16;
-            for (int kk = 0; kk < nk16; ++kk) {
-              const uint64_t a_hi = ptx::umma_desc_sw128(st + kk * 32);
-              const uint64_t b_hi = ptx::umma_desc_sw128(st + TC_A_BYTES + kk * 32);
-              const uint32_t first = (kb | kk) != 0;
-              if (NPROD == 3) {
-                const uint64_t a_lo = ptx::umma_desc_sw128(st + TC_A_BYTES + TC_B_BYTES + kk * 32);
-                const uint64_t b_lo = ptx::umma_desc_sw128(st + 2 * TC_A_BYTES + TC_B_BYTES + kk * 32);
-                ptx::umma_bf16(d_tmem, a_hi, b_lo, idesc, first);
-                ptx::umma_bf16(d_tmem, a_lo, b_hi, idesc, 1u);
-                ptx::umma_bf16(d_tmem, a_hi, b_hi, idesc, 1u);
-              } else {
-                ptx::umma_bf16(d_tmem, a_hi, b_hi, idesc, first);
+            for (int hf = 0; hf < 2; ++hf) {
+              if (kb == 0) {
+                ptx::mbar_wait(bar_tempty(buf, hf), ((u >> 1) & 1u) ^ 1u);   // softmax drained this half buffer
+                ptx::tc_fence_after();
               }
+              const uint32_t d_tmem = tmem_base + buf * TC_BN + hf * (TC_BN / 2);
+              for (int kk = 0; kk < nk16; ++kk) {
+                const uint64_t a_hi = ptx::umma_desc_sw128(st + kk * 32);
+                const uint64_t b_hi = ptx::umma_desc_sw128(st + TC_A_BYTES + hf * kHalfB + kk * 32);
+                const uint32_t first = (kb | kk) != 0;
+                if (NPROD == 3) {
+                  const uint64_t a_lo = ptx::umma_desc_sw128(st + TC_A_BYTES + TC_B_BYTES + kk * 32);
+                  const uint64_t b_lo = ptx::umma_desc_sw128(st + 2 * TC_A_BYTES + TC_B_BYTES + hf * kHalfB + kk * 32);
+                  ptx::umma_bf16(d_tmem, a_hi, b_lo, idesc, first);
+                  ptx::umma_bf16(d_tmem, a_lo, b_hi, idesc, 1u);
+                  ptx::umma_bf16(d_tmem, a_hi, b_hi, idesc, 1u);
+                } else {
+                  ptx::umma_bf16(d_tmem, a_hi, b_hi, idesc, first);
+                }
+              }
+              if (kb == nkb - 1) ptx::umma_commit(bar_tfull(buf, hf));   // this half's logits are in TMEM
             }
             ptx::umma_commit(bar_empty(s));      // smem slot free once these MMAs retire
           }
-          ptx::umma_commit(bar_tfull(buf));      // logits of this (layer, head) are in TMEM
         }
       }
     }
     }
   } else {
-    ptx::setmaxnreg_inc<224>();
+    ptx::setmaxnreg_inc<FW_SOFTMAX_REGS>();
     // =========================== softmax / accumulate warps =================================
+    // Thread = (pixel row, 64-token quarter of the CTA's 256 tokens): four warps per scheduler hide the
+    // MUFU / TMEM latencies of each other.  Per unit u = (layer, head) the order is
+    //   A(u): row max of my columns  ->  C(u-1): normalise + accumulate the PREVIOUS unit  ->  B(u): exponentials,
+    // so the statistics exchange of unit u-1 (posted at the end of the previous iteration) has pass A to
+    // land, and the MMAs of unit u+1 (which need the buffer C(u-1) frees) run under pass B.
     const int quad = warp & 3;                 // TMEM lane quadrant this warp may access
-    const int ch = (warp - FW_SOFTMAX_WARP0) >> 2;   // column half of the CTA's 256 tokens
+    const int qt = (warp - FW_SOFTMAX_WARP0) >> 2;   // column quarter
     const int row = quad * 32 + lane;
-    const int col0 = ch * 128;
-    const int ncol = max(0, min(128, P.T - (tok0 + col0)));
+    const int col0 = qt * FW_QCOLS;
+    const int ncol = max(0, min(FW_QCOLS, P.T - (tok0 + col0)));
     const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
-    const int part = static_cast<int>(cta_rank) * 2 + ch;
-    constexpr int NPART = 2 * NSPLIT;
-    float acc[SELECT ? TC_MAX_SEL : 128];
+    const int hf = qt >> 1;                    // column half (hand-over unit of the TMEM buffers)
+    const int part = static_cast<int>(cta_rank) * FW_PARTS + qt;
+    constexpr int NPART = FW_PARTS * NSPLIT;
+    constexpr int NCH = FW_QCOLS / 32;
+    float acc[SELECT ? TC_MAX_SEL : FW_QCOLS];
 #pragma unroll
-    for (int j = 0; j < (SELECT ? TC_MAX_SEL : 128); ++j) acc[j] = 0.0f;
+    for (int j = 0; j < (SELECT ? TC_MAX_SEL : FW_QCOLS); ++j) acc[j] = 0.0f;
+
+    // normalise + accumulate unit uu, whose exponentials this thread parked in TMEM one iteration ago
+    auto pass_c = [&](uint32_t uu, float m_own, float wgt_u) {
+      const uint32_t buf = uu & 1u, par = (uu >> 1) & 1u;
+      const uint32_t taddr = t_lane + buf * TC_BN + col0;
+      ptx::mbar_wait(bar_xfull(buf), par);
+      float mg = -INFINITY;
+#pragma unroll
+      for (int q = 0; q < NPART; ++q) mg = fmaxf(mg, stats[(buf * FW_MAX_PARTS + q) * TC_BM + row].x);
+      float total = 0.0f;
+#pragma unroll
+      for (int q = 0; q < NPART; ++q) {
+        const float2 sq = stats[(buf * FW_MAX_PARTS + q) * TC_BM + row];
+        total += sq.y * pow2_int(sq.x - mg);
+      }
+      if (P.row_stats != nullptr && part == 0)
+        reinterpret_cast<float2*>(P.row_stats)[(static_cast<int64_t>(b) * P.ops.total_heads + uu) * P.R2 + p0 + row] =
+            make_float2(mg, total);
+      const float cf = ncol > 0 ? __fdividef(wgt_u * pow2_int(m_own - mg), total) : 0.0f;
+      if (!SELECT) {
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+          if (32 * c < ncol) {
+            uint32_t v[32];
+            ptx::tmem_ld32(taddr + 32 * c, v);
+            ptx::tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) acc[32 * c + j] = fmaf(cf, __uint_as_float(v[j]), acc[32 * c + j]);
+          }
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < TC_MAX_SEL; ++j) {
+          const int t = tok_s[j] - tok0 - col0;   // warp-uniform
+          if (j < P.n_idx && t >= 0 && t < ncol) {
+            const uint32_t ev = ptx::tmem_ld1(taddr + t);
+            ptx::tmem_ld_wait();
+            acc[j] = fmaf(cf, __uint_as_float(ev), acc[j]);
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(bar_tempty(buf, hf));
+    };
 
     uint32_t u = 0;
+    float m_prev = 0.0f, wgt_prev = 0.0f;
     for (int l = 0; l < P.ops.n_layers; ++l) {
       const int h = P.ops.heads[l];
       const float wgt = P.ops.weight[l];
       for (int head = 0; head < h; ++head, ++u) {
         const uint32_t buf = u & 1u, par = (u >> 1) & 1u;
-        ptx::mbar_wait(bar_tfull(buf), par);
+        ptx::mbar_wait(bar_tfull(buf, hf), par);
         ptx::tc_fence_after();
         const uint32_t taddr = t_lane + buf * TC_BN + col0;
-        uint32_t v[2][16];
-        const int nch = (ncol + 15) >> 4;          // 16-column chunks I own (warp-uniform)
-        // ---- pass A: row max over my columns (TMEM loads software-pipelined one chunk ahead)
-        float m = -INFINITY;
-        if (nch > 0) ptx::tmem_ld16(taddr, v[0]);
+        // ---- pass A: row max over my columns (four independent chains)
+        float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
 #pragma unroll
-        for (int c = 0; c < 8; ++c) {
-          if (c < nch) {
+        for (int c = 0; c < NCH; ++c) {
+          if (32 * c < ncol) {
+            uint32_t v[32];
+            ptx::tmem_ld32(taddr + 32 * c, v);
             ptx::tmem_ld_wait();
-            if (c + 1 < nch) ptx::tmem_ld16(taddr + 16 * (c + 1), v[(c + 1) & 1]);
-            if (ncol >= 16 * (c + 1)) {
+            if (ncol >= 32 * (c + 1)) {
 #pragma unroll
-              for (int j = 0; j < 16; j += 2) m = ptx::max3(m, __uint_as_float(v[c & 1][j]), __uint_as_float(v[c & 1][j + 1]));
+              for (int j = 0; j < 32; j += 8) {
+                m0 = ptx::max3(m0, __uint_as_float(v[j]), __uint_as_float(v[j + 1]));
+                m1 = ptx::max3(m1, __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+                m2 = ptx::max3(m2, __uint_as_float(v[j + 4]), __uint_as_float(v[j + 5]));
+                m3 = ptx::max3(m3, __uint_as_float(v[j + 6]), __uint_as_float(v[j + 7]));
+              }
             } else {
 #pragma unroll
-              for (int j = 0; j < 16; ++j)
-                if (16 * c + j < ncol) m = fmaxf(m, __uint_as_float(v[c & 1][j]));
+              for (int j = 0; j < 32; ++j)
+                if (32 * c + j < ncol) m0 = fmaxf(m0, __uint_as_float(v[j]));
             }
           }
         }
+        // Rounded up to an integer: any m >= the true max stabilises the exponentials equally well, and
+        // integer-valued maxima make every rescale 2^(m_part - m_row) an exponent-field add, not a MUFU.
+        const float m = ceilf(fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)));
+        // ---- pass C of the previous unit
+        if (u > 0) pass_c(u - 1, m_prev, wgt_prev);
         // ---- pass B: exponentials (parked back in TMEM) and their sum
-        float sum = 0.0f;
-        if (nch > 0) ptx::tmem_ld16(taddr, v[0]);
+        float s0 = 0.0f, s1 = 0.0f, s2 = 0.0f, s3 = 0.0f;
 #pragma unroll
-        for (int c = 0; c < 8; ++c) {
-          if (c < nch) {
+        for (int c = 0; c < NCH; ++c) {
+          if (32 * c < ncol) {
+            uint32_t v[32];
+            ptx::tmem_ld32(taddr + 32 * c, v);
             ptx::tmem_ld_wait();
-            if (c + 1 < nch) ptx::tmem_ld16(taddr + 16 * (c + 1), v[(c + 1) & 1]);
-            if (ncol >= 16 * (c + 1)) {
+            if (ncol >= 32 * (c + 1)) {
 #pragma unroll
-              for (int j = 0; j < 16; ++j) {
-                const float e = ptx::ex2(__uint_as_float(v[c & 1][j]) - m);
-                sum += e;
-                v[c & 1][j] = __float_as_uint(e);
+              for (int j = 0; j < 32; j += 4) {
+                const float e0 = ptx::ex2(__uint_as_float(v[j]) - m), e1 = ptx::ex2(__uint_as_float(v[j + 1]) - m);
+                const float e2 = ptx::ex2(__uint_as_float(v[j + 2]) - m), e3 = ptx::ex2(__uint_as_float(v[j + 3]) - m);
+                s0 += e0; s1 += e1; s2 += e2; s3 += e3;
+                v[j] = __float_as_uint(e0); v[j + 1] = __float_as_uint(e1);
+                v[j + 2] = __float_as_uint(e2); v[j + 3] = __float_as_uint(e3);
               }
             } else {
 #pragma unroll
-              for (int j = 0; j < 16; ++j) {
-                const float e = (16 * c + j < ncol) ? ptx::ex2(__uint_as_float(v[c & 1][j]) - m) : 0.0f;
-                sum += e;
-                v[c & 1][j] = __float_as_uint(e);
+              for (int j = 0; j < 32; ++j) {
+                const float e = (32 * c + j < ncol) ? ptx::ex2(__uint_as_float(v[j]) - m) : 0.0f;
+                s0 += e;
+                v[j] = __float_as_uint(e);
               }
             }
-            if (!SELECT) {
-              ptx::tmem_st16(taddr + 16 * c, v[c & 1]);
-              if (c + 2 < nch) ptx::tmem_st_wait();     // v[c & 1] is the target of the load issued next iteration
-            }
+            ptx::tmem_st32(taddr + 32 * c, v);
           }
         }
-        if (!SELECT) ptx::tmem_st_wait();
-        // ---- exchange (max, sum) with the other column half and the other CTAs of the cluster.
-        // Local slot: plain store + arrive.  Remote slot: st.async, which completes bytes on the
-        // peer's mbarrier itself (no cluster-scope release fence, no L1 invalidate on the waiter).
+        const float sum = (s0 + s1) + (s2 + s3);
+        ptx::tmem_st_wait();
+        // ---- post (max, sum) to every column part of the cluster.  Local slot: plain store + arrive.
+        // Remote slot: st.async, which completes bytes on the peer's mbarrier itself (no cluster-scope
+        // release fence, no L1 invalidate on the waiter).
         {
-          const int sidx = (buf * 4 + part) * TC_BM + row;
+          const int sidx = (buf * FW_MAX_PARTS + part) * TC_BM + row;
           stats[sidx] = make_float2(m, sum);
           if (NSPLIT > 1) {
             const uint32_t slot = base + SM::kStatsOff + sidx * 8;
 #pragma unroll
             for (uint32_t dst = 0; dst < static_cast<uint32_t>(NSPLIT); ++dst)
               if (dst != cta_rank) ptx::st_async_v2(ptx::mapa(slot, dst), m, sum, ptx::mapa(bar_xfull(buf), dst));
-            if (warp == FW_SOFTMAX_WARP0 && lane == 0) ptx::mbar_arrive_expect_tx(bar_xfull(buf), (NSPLIT - 1) * TC_SOFTMAX_THREADS * 8);
+            if (warp == FW_SOFTMAX_WARP0 && lane == 0) ptx::mbar_arrive_expect_tx(bar_xfull(buf), (NSPLIT - 1) * FW_SOFTMAX_THREADS * 8);
             else ptx::mbar_arrive(bar_xfull(buf));
           } else {
             ptx::mbar_arrive(bar_xfull(buf));
           }
-          ptx::mbar_wait(bar_xfull(buf), par);
         }
-        float mg = -INFINITY;
-#pragma unroll
-        for (int q = 0; q < NPART; ++q) mg = fmaxf(mg, stats[(buf * 4 + q) * TC_BM + row].x);
-        float total = 0.0f;
-#pragma unroll
-        for (int q = 0; q < NPART; ++q) {
-          const float2 sq = stats[(buf * 4 + q) * TC_BM + row];
-          total += sq.y * ptx::ex2(sq.x - mg);
-        }
-        if (P.row_stats != nullptr && part == 0)
-          reinterpret_cast<float2*>(P.row_stats)[(static_cast<int64_t>(b) * P.ops.total_heads + u) * P.R2 + p0 + row] =
-              make_float2(mg, total);
-        const float cf = ncol > 0 ? wgt * ptx::ex2(m - mg) / total : 0.0f;
-        // ---- pass C: accumulate weight/heads * P
-        if (!SELECT) {
-          if (nch > 0) ptx::tmem_ld16(taddr, v[0]);
-#pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            if (c < nch) {
-              ptx::tmem_ld_wait();
-              if (c + 1 < nch) ptx::tmem_ld16(taddr + 16 * (c + 1), v[(c + 1) & 1]);
-#pragma unroll
-              for (int j = 0; j < 16; ++j) acc[16 * c + j] = fmaf(cf, __uint_as_float(v[c & 1][j]), acc[16 * c + j]);
-            }
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < TC_MAX_SEL; ++j) {
-            const int t = tok_s[j] - tok0 - col0;   // warp-uniform
-            if (j < P.n_idx && t >= 0 && t < ncol) {
-              const uint32_t sv = ptx::tmem_ld1(taddr + t);
-              ptx::tmem_ld_wait();
-              acc[j] = fmaf(cf, ptx::ex2(__uint_as_float(sv) - m), acc[j]);
-            }
-          }
-        }
-        ptx::tc_fence_before();
-        ptx::mbar_arrive(bar_tempty(buf));
+        m_prev = m;
+        wgt_prev = wgt;
       }
     }
+    if (u > 0) pass_c(u - 1, m_prev, wgt_prev);
     // ---- write-out: lanes hold consecutive pixels -> 128 B coalesced stores per token
     if (!SELECT) {
       float* out = P.maps + (static_cast<int64_t>(b) * P.T + tok0 + col0) * P.R2 + p0 + row;
 #pragma unroll
-      for (int j = 0; j < 128; ++j)
+      for (int j = 0; j < FW_QCOLS; ++j)
         if (j < ncol) out[static_cast<int64_t>(j) * P.R2] = acc[j];
     } else {
 #pragma unroll
