@@ -211,6 +211,7 @@ constexpr int FW_MAX_PARTS = 2 * FW_PARTS;                    // parts of a clus
 constexpr int FW_QCOLS = TC_BN / FW_PARTS;                    // 64 tokens per thread
 constexpr int FW_SOFTMAX_THREADS = 128 * FW_PARTS;            // 16 warps
 constexpr int FW_THREADS = 32 * FW_SOFTMAX_WARP0 + FW_SOFTMAX_THREADS;   // 640
+constexpr int FW_NH = 1;                                      // column groups a TMEM buffer is handed over in (1 or 2)
 constexpr int FW_SOFTMAX_REGS = 112;   // 128*32 + 512*112 == 640*96: setmaxnreg.inc only draws from what .dec released
 template <int NPROD, int NSPLIT, bool SELECT>
 __global__ void __launch_bounds__(FW_THREADS, 1)
@@ -247,7 +248,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
     for (int i = 0; i < 2; ++i) {
       for (int hf = 0; hf < 2; ++hf) {
         ptx::mbar_init(bar_tfull(i, hf), 1);
-        ptx::mbar_init(bar_tempty(i, hf), FW_SOFTMAX_THREADS / 2);
+        ptx::mbar_init(bar_tempty(i, hf), FW_SOFTMAX_THREADS / FW_NH);
       }
       ptx::mbar_init(bar_xfull(i), FW_SOFTMAX_THREADS);
     }
@@ -303,11 +304,12 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
   } else if (warp == 1) {
     // =========================== MMA issuer (one lane) =====================================
     if (lane == 0) {
-      // Each unit is issued as two N = 128 column halves with their own barriers: the softmax warps of
-      // half 1 start ~half a unit's MMA time after those of half 0 and stay out of phase with them, so
-      // one group's MUFU-bound exponentials overlap the other's max / accumulate passes.
-      constexpr uint32_t idesc = ptx::umma_idesc_bf16(TC_BM, TC_BN / 2);
-      constexpr uint32_t kHalfB = (TC_BN / 2) * 128;     // byte offset of token row 128 in a K tile
+      // FW_NH = 2 hands each buffer over as two N = 128 column halves with their own barriers (two softmax
+      // groups half a unit out of phase).  Measured on B200: an SS-mode M=128 K=16 MMA costs ~130 cycles
+      // whether N is 128 or 256 (the A tile is re-read from shared memory each time), so halving N doubles
+      // the tensor time per unit (3400 vs 1700 cycles) and the stagger buys nothing: one N = 256 hand-over.
+      constexpr uint32_t idesc = ptx::umma_idesc_bf16(TC_BM, TC_BN / FW_NH);
+      constexpr uint32_t kHalfB = (TC_BN / FW_NH) * 128;     // byte offset of the second group's first token row in a K tile
       uint32_t it = 0, u = 0;
       for (int l = 0; l < P.ops.n_layers; ++l) {
         const int h = P.ops.heads[l], d = P.ops.d[l];
@@ -320,12 +322,12 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
             ptx::tc_fence_after();
             const uint32_t st = base + s * SM::kStageBytes;
             const int nk16 = (min(TC_BK, d - kb * TC_BK) + 15) / 16;
-            for (int hf = 0; hf < 2; ++hf) {
+            for (int hf = 0; hf < FW_NH; ++hf) {
               if (kb == 0) {
                 ptx::mbar_wait(bar_tempty(buf, hf), ((u >> 1) & 1u) ^ 1u);   // softmax drained this half buffer
                 ptx::tc_fence_after();
               }
-              const uint32_t d_tmem = tmem_base + buf * TC_BN + hf * (TC_BN / 2);
+              const uint32_t d_tmem = tmem_base + buf * TC_BN + hf * (TC_BN / FW_NH);
               for (int kk = 0; kk < nk16; ++kk) {
                 const uint64_t a_hi = ptx::umma_desc_sw128(st + kk * 32);
                 const uint64_t b_hi = ptx::umma_desc_sw128(st + TC_A_BYTES + hf * kHalfB + kk * 32);
@@ -362,7 +364,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
     const int col0 = qt * FW_QCOLS;
     const int ncol = max(0, min(FW_QCOLS, P.T - (tok0 + col0)));
     const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
-    const int hf = qt >> 1;                    // column half (hand-over unit of the TMEM buffers)
+    const int hf = qt / (FW_PARTS / FW_NH);    // hand-over group of the TMEM buffers
     const int part = static_cast<int>(cta_rank) * FW_PARTS + qt;
     constexpr int NPART = FW_PARTS * NSPLIT;
     constexpr int NCH = FW_QCOLS / 32;
