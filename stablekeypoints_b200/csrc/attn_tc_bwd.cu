@@ -125,6 +125,25 @@ __device__ __forceinline__ bool bw_flush_after(const BwdParams& P, int u, int u_
   return (u - hg * per_head) / P.tiles != (u + 1 - hg * per_head) / P.tiles;
 }
 
+// Units are walked in order, so after the first decode the (layer, head, image, tile) tuple is advanced
+// incrementally: the integer divisions of bw_decode were ~1.5k cycles of dependent latency per unit.
+__device__ __forceinline__ BwUnit bw_next(const BwdParams& P, BwUnit x) {
+  if (++x.tile == P.tiles) {
+    x.tile = 0;
+    if (++x.b == P.B) {
+      x.b = 0;
+      ++x.hg;
+      if (x.l + 1 < P.ops.n_layers && x.hg >= P.ops.head_base[x.l + 1]) ++x.l;
+      x.head = x.hg - P.ops.head_base[x.l];
+    }
+  }
+  return x;
+}
+// same predicate as bw_flush_after, from the current and the next tuple
+__device__ __forceinline__ bool bw_flush_between(const BwdParams& P, const BwUnit& x, const BwUnit& nx, bool last) {
+  return last || nx.hg != x.hg || (!P.ops.k_shared[x.l] && nx.b != x.b);
+}
+
 // 12 warps = 3 warpgroups: {TMA, MMA, 2 idle} shrink to 56 registers, the 8 softmax warps grow to 224
 constexpr int BW_THREADS = 384;
 constexpr int BW_SOFTMAX_WARP0 = 4;
@@ -182,8 +201,8 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
     if (lane == 0) {
       int prev_hg = -1, prev_b = -1;
       uint32_t it = 0;
-      for (int u = u_begin; u < u_end; ++u, ++it) {
-        const BwUnit x = bw_decode(P, u);
+      BwUnit x = bw_decode(P, u_begin);
+      for (int u = u_begin; u < u_end; ++u, ++it, x = bw_next(P, x)) {
         const int h = P.ops.heads[x.l];
         const int st = it & 1;
         ptx::mbar_wait(bar_qempty(st), ((it >> 1) & 1u) ^ 1u);
@@ -214,8 +233,10 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
     if (lane == 0) {
       uint32_t it = 0;
       bool dk_fresh = true;
+      long long pf_q = 0, pf_ds = 0, pf_is = 0, pf_id = 0;      // profiler (SKP_BWD_DBG & 8), kept in registers
+      BwUnit x = bw_decode(P, u_begin);
       for (int u = u_begin; u < u_end; ++u, ++it) {
-        const BwUnit x = bw_decode(P, u);
+        const BwUnit nxu = bw_next(P, x);
         const int d = P.ops.d[x.l];
         const int st = it & 1;
         const uint32_t qs = base + SM::kQOff + st * SM::kQStage;
@@ -223,7 +244,8 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         long long c0 = clock64();
         ptx::mbar_wait(bar_qfull(st), (it >> 1) & 1u);
         ptx::tc_fence_after();
-        if (P.prof && blockIdx.x == 0) atomicAdd(P.prof + 0, clock64() - c0);
+        pf_q += clock64() - c0;
+        c0 = clock64();
         // ---- S = Q' K^T (256 tokens) and S_sel = Q' K_sel^T (16 tokens)
         const uint32_t id_S = bw_idesc(TC_BM, TC_BN, 0, 0), id_sel = bw_idesc(TC_BM, BW_SEL, 0, 0);
         const int nk16 = d / 16;
@@ -246,11 +268,13 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
           }
         }
         ptx::umma_commit(bar_sfull);
+        pf_is += clock64() - c0;
         // ---- wait for dS (bf16, [px][tok]) in shared memory
         c0 = clock64();
         ptx::mbar_wait(bar_dsfull, it & 1u);
         ptx::tc_fence_after();
-        if (P.prof && blockIdx.x == 0) atomicAdd(P.prof + 1, clock64() - c0);
+        pf_ds += clock64() - c0;
+        c0 = clock64();
         // dQ' (128 px x d) = dS (K-major A, K = 256 tokens) * K_hi (MN-major B: rows = tokens)
         const uint32_t id_dq = bw_idesc(TC_BM, d, 0, 1);
         const int nkt = (ntok + 15) / 16;
@@ -265,7 +289,12 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
                            bw_desc(qs + k * 2048, 16384, 1024), id_dk, (dk_fresh && k == 0) ? 0u : 1u);
         ptx::umma_commit(bar_mmadone);
         ptx::umma_commit(bar_qempty(st));
-        dk_fresh = bw_flush_after(P, u, u_end);
+        pf_id += clock64() - c0;
+        dk_fresh = bw_flush_between(P, x, nxu, u + 1 >= u_end);
+        x = nxu;
+      }
+      if (P.prof && blockIdx.x == 0) {
+        P.prof[0] = pf_q; P.prof[1] = pf_ds; P.prof[8] = pf_is; P.prof[9] = pf_id;
       }
     }
   }
@@ -286,18 +315,19 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
     int prev_l = -1, prev_b = -1;
     float2 nx_ml = make_float2(0.f, 1.f);
     float nx_dp[BW_SEL];
-    auto load_row = [&](int uu, float2& ml, float (&dpr)[BW_SEL]) {
-      const BwUnit y = bw_decode(P, uu);
+    auto load_row = [&](const BwUnit& y, float2& ml, float (&dpr)[BW_SEL]) {
       const int pp = y.tile * TC_BM + row;
       ml = __ldg(reinterpret_cast<const float2*>(P.row_stats) + (static_cast<int64_t>(y.b) * P.ops.total_heads + y.hg) * P.R2 + pp);
 #pragma unroll
       for (int j = 0; j < BW_SEL; ++j)
         dpr[j] = j < P.n_idx ? __ldg(P.dmaps_sel + (static_cast<int64_t>(y.b) * P.n_idx + j) * P.R2 + pp) : 0.0f;
     };
-    for (int u = u_begin; u < u_end; ++u, ++it) {
-      const BwUnit x = bw_decode(P, u);
+    long long pf[6] = {0, 0, 0, 0, 0, 0}, c_end = clock64();   // profiler (SKP_BWD_DBG & 8), kept in registers
+    BwUnit x = bw_decode(P, u_begin), nxu = x;
+    for (int u = u_begin; u < u_end; ++u, ++it, x = nxu) {
+      nxu = bw_next(P, x);
       const int d = P.ops.d[x.l], s = P.s[x.l], C = P.C[x.l];
-      const int up = R / s, nj = 5 * up;
+      const int up = ((R & (R - 1)) | (s & (s - 1))) == 0 ? R >> (__ffs(s) - 1) : R / s, nj = 5 * up;
       const float wgt = P.ops.weight[x.l], scale = P.ops.scale[x.l];
       if (x.l != prev_l || x.b != prev_b) {
         named_bar_sync(1, TC_SOFTMAX_THREADS);
@@ -323,18 +353,17 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       }
       // (m, l) and the n_idx upstream gradients of this row were fetched one unit ahead (nx_*): a unit
       // is too short to hide a DRAM round trip behind itself
-      if (u == u_begin) load_row(u, nx_ml, nx_dp);
+      if (u == u_begin) load_row(x, nx_ml, nx_dp);
       const float m = nx_ml.x, inv_l = 1.0f / nx_ml.y;
       float dp[BW_SEL];
 #pragma unroll
       for (int j = 0; j < BW_SEL; ++j) dp[j] = wgt * nx_dp[j];
-      if (u + 1 < u_end) load_row(u + 1, nx_ml, nx_dp);
 
-      const bool pr = P.prof && blockIdx.x == 0 && stid == 0;
       long long c1 = clock64();
+      pf[5] += c1 - c_end;                      // loop top: decode, prefetch issue, table rebuilds
       ptx::mbar_wait(bar_sfull, it & 1u);
       ptx::tc_fence_after();
-      if (pr) P.prof[2] += clock64() - c1;
+      pf[0] += clock64() - c1;
       c1 = clock64();
       float delta = 0.0f;
       {
@@ -388,18 +417,21 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
           *e = __float2bfloat16_rn(__bfloat162float(*e) + dp[j]);
         }
       }
-      if (pr) P.prof[3] += clock64() - c1;
+      pf[1] += clock64() - c1;
       c1 = clock64();
       ptx::fence_proxy_async();
       ptx::tc_fence_before();
       ptx::mbar_arrive(bar_dsfull);
-      if (pr) P.prof[4] += clock64() - c1;
+      pf[2] += clock64() - c1;
       c1 = clock64();
 
+      // next unit's row statistics / upstream gradients: issued here, where this thread would only spin
+      // on the dQ/dK MMAs, they are back long before the next loop top
+      if (u + 1 < u_end && !(P.dbg & 16)) load_row(nxu, nx_ml, nx_dp);
       // ---- dQ' tile: TMEM -> fp32 staging (aliases the dS tile, free once the MMAs are done)
       ptx::mbar_wait(bar_mmadone, it & 1u);
       ptx::tc_fence_after();
-      if (pr) P.prof[5] += clock64() - c1;
+      pf[3] += clock64() - c1;
       c1 = clock64();
       if (ch * 32 < d && !(P.dbg & 4)) {
         uint32_t v[32];
@@ -420,13 +452,18 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         const int span = R <= TC_BM ? R : TC_BM;
         const int rows_per_tile = TC_BM / span;
         const int p0 = x.tile * TC_BM;
-        const int y0 = p0 / R, x0 = p0 % R;
+        // R, s and d/4 are powers of two for every supported model: shifts instead of ~150-cycle divisions
+        const bool p2 = ((R & (R - 1)) | (s & (s - 1)) | ((d >> 2) & ((d >> 2) - 1))) == 0;
+        const int lg_c4 = __ffs(d >> 2) - 1, lg_s = __ffs(s) - 1;
+        const int y0 = p2 ? p0 >> (__ffs(R) - 1) : p0 / R, x0 = p2 ? p0 & (R - 1) : p0 % R;
         const int n_c4 = d >> 2;
         const int n_out = rows_per_tile * s * n_c4;
         const float ratio = static_cast<float>(s) / R;
         float* dq = P.dq[x.l] + static_cast<int64_t>(x.b) * s * s * C + x.head * d;
         for (int o = stid; o < ((P.dbg & 2) ? 0 : n_out); o += TC_SOFTMAX_THREADS) {
-          const int c4 = o % n_c4, sx = (o / n_c4) % s, yy = o / (n_c4 * s);
+          const int c4 = p2 ? o & (n_c4 - 1) : o % n_c4;
+          const int sx = p2 ? (o >> lg_c4) & (s - 1) : (o / n_c4) % s;
+          const int yy = p2 ? o >> (lg_c4 + lg_s) : o / (n_c4 * s);
           const int xlo = max(0, (sx - 2) * up);
           // taps outside the tile's x span get weight 0 and a clamped (valid) row: fixed trip count,
           // four independent accumulators so the shared-memory loads pipeline
@@ -483,9 +520,10 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         }
       }
       named_bar_sync(2, TC_SOFTMAX_THREADS);
-      if (pr) { P.prof[6] += clock64() - c1; P.prof[7] += 1; }
+      pf[4] += clock64() - c1;
+      c_end = clock64();
       // ---- dK: flush the TMEM accumulator when this head (or image, for a per-image k) is finished
-      if (bw_flush_after(P, u, u_end) && ch < n_mh) {
+      if (bw_flush_between(P, x, nxu, u + 1 >= u_end) && ch < n_mh) {
         const int t = tok0 + ch * 128 + row;
         float* dk = P.dk[x.l] + (static_cast<int64_t>(P.ops.k_shared[x.l] ? 0 : x.b) * P.T + t) * C + x.head * d;
         const float inv = 1.0f / kLog2eBw;
@@ -506,6 +544,11 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         }
         ptx::tc_fence_before();
       }
+    }
+    if (P.prof && blockIdx.x == 0 && stid == 0) {
+      for (int i = 0; i < 5; ++i) P.prof[2 + i] = pf[i];
+      P.prof[7] = it;
+      P.prof[10] = pf[5];
     }
   }
 
@@ -589,8 +632,8 @@ int attn_map_bwd_tc(const skp_attn_layer* h_layers, int n_layers, int B, int T, 
   if (const char* e = getenv("SKP_BWD_DBG")) P.dbg = atoi(e);
   static unsigned long long* d_prof = nullptr;
   if (P.dbg & 8) {
-    if (!d_prof) cudaMalloc(&d_prof, 64);
-    cudaMemsetAsync(d_prof, 0, 64, st);
+    if (!d_prof) cudaMalloc(&d_prof, 128);
+    cudaMemsetAsync(d_prof, 0, 128, st);
     P.prof = d_prof;
   }
   const int nh = T > TC_BN ? 2 : 1;
@@ -598,12 +641,13 @@ int attn_map_bwd_tc(const skp_attn_layer* h_layers, int n_layers, int B, int T, 
   if (x3) rc = nh == 2 ? launch_bwd<3, 2>(P, st) : launch_bwd<3, 1>(P, st);
   else rc = nh == 2 ? launch_bwd<1, 2>(P, st) : launch_bwd<1, 1>(P, st);
   if (P.dbg & 8) {
-    unsigned long long h[8];
+    unsigned long long h[16];
     cudaStreamSynchronize(st);
-    cudaMemcpy(h, d_prof, 64, cudaMemcpyDeviceToHost);
+    cudaMemcpy(h, d_prof, 128, cudaMemcpyDeviceToHost);
     const double n = h[7] ? static_cast<double>(h[7]) : 1.0;
-    fprintf(stderr, "[bwd prof, cycles/unit over %llu units] mma: wait q_full %.0f, wait ds_full %.0f | softmax: wait s_full %.0f, dS %.0f, "
-            "fence+arrive %.0f, wait mma_done %.0f, drain+adjoint %.0f\n", h[7], h[0] / n, h[1] / n, h[2] / n, h[3] / n, h[4] / n, h[5] / n, h[6] / n);
+    fprintf(stderr, "[bwd prof, cycles/unit over %llu units] mma: wait q_full %.0f, issue S %.0f, wait ds_full %.0f, issue dQ/dK %.0f | softmax: loop top %.0f, "
+            "wait s_full %.0f, dS %.0f, fence+arrive %.0f, wait mma_done %.0f, drain+adjoint %.0f\n", h[7], h[0] / n, h[8] / n, h[1] / n, h[9] / n,
+            h[10] / n, h[2] / n, h[3] / n, h[4] / n, h[5] / n, h[6] / n);
   }
   return rc;
 }
