@@ -134,6 +134,22 @@ def make_pool(cfg, rank: int) -> torch.Tensor:
     return torch.stack([ds[i]["img"] for i in range(len(ds))])
 
 
+def ncu_dram_bytes(profile: str, images: int):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch from a committed `ncu --set full` summary under
+    profiles/ (captured at 8 images per launch; the traffic is proportional to the images).  None if absent."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", profile)
+    if not os.path.exists(path):
+        return None
+    mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    total = 0.0
+    for ln in open(path):
+        for key in ("dram__bytes_read.sum = ", "dram__bytes_write.sum = "):
+            if ln.startswith(key):
+                val, unit = ln[len(key):].split()[:2]
+                total += float(val) * mult[unit]
+    return total * images / 8.0 if total else None
+
+
 def attn_algorithmic_flops(cfg_model: str, T: int, R: int, n_layers: int = 4) -> float:
     """2 * R^2 * T * sum_l C_l per image over the captured layers."""
     from stablekeypoints_b200.sd_standin import unet_config
@@ -289,16 +305,27 @@ def ours(args):
     value = units_per_step * args.steps / (ms / 1e3)
     e2e = units_per_step * args.steps / (ms2 / 1e3)
     tm = launches["timing"]
-    # ---- roofline of the dominant kernel of OUR path: the fused attention-map forward ---------
+    # ---- roofline of the dominant kernel of OUR path: the fused attention-map backward in the token
+    # optimisation (it moves 2x the forward's algorithmic FLOPs), the forward in extraction -----------
     imgs_per_call = (2 * args.images_per_pass) if args.workload == "optimize" else cfg["n_aug"]
-    fwd = tm.get("skp_attn_map_fwd", {"calls": 0, "ms": 0.0})
-    flops_call = attn_algorithmic_flops(cfg["model"], cfg["T"], cfg["R"], len(cfg["layers"])) * imgs_per_call
-    ach = flops_call * fwd["calls"] / (fwd["ms"] / 1e3) / 1e12 if fwd["ms"] > 0 else None
+    flops_fwd = attn_algorithmic_flops(cfg["model"], cfg["T"], cfg["R"], len(cfg["layers"])) * imgs_per_call
     peak = peaks["bf16_tflops_sustained"]
-    roofline = {"kernel": "skp_attn_map_fwd (prep + attn_map_fwd_tc_kernel, bf16x3 on tcgen05)", "bound": "tensor",
-                "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": (ach / peak) if ach else None,
-                "peak_source": f"{peaks['source']} bf16 dense, sustained", "traffic": None,
-                "ms_per_launch": fwd["ms"] / max(1, fwd["calls"]), "algorithmic_flops_per_launch": flops_call}
+
+    def roof(symbol, label, flops_call, profile):
+        t = tm.get(symbol, {"calls": 0, "ms": 0.0})
+        ach = flops_call * t["calls"] / (t["ms"] / 1e3) / 1e12 if t["ms"] > 0 else None
+        return {"kernel": label, "bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
+                "frac": (ach / peak) if ach else None, "peak_source": f"{peaks['source']} bf16 dense, sustained",
+                "traffic": ncu_dram_bytes(profile, imgs_per_call), "traffic_source": f"profiles/{profile} (ncu --set full, "
+                "dram read+write of the main kernel at 8 images/launch, scaled to this launch's images)",
+                "ms_per_launch": t["ms"] / max(1, t["calls"]), "algorithmic_flops_per_launch": flops_call,
+                "ms_per_step": t["ms"] / args.steps}
+
+    r_fwd = roof("skp_attn_map_fwd", "skp_attn_map_fwd (operand prep + attn_map_fwd_tc_kernel, bf16x3 on tcgen05)",
+                 flops_fwd, "r1c_fwd_tc_full.txt")
+    r_bwd = roof("skp_attn_map_bwd", "skp_attn_map_bwd (attn_map_bwd_tc_kernel: recompute + dQ/dK on tcgen05, bicubic adjoint)",
+                 2.0 * flops_fwd, "r1c_bwd_tc_full.txt")
+    roofline, roofline_other = (r_bwd, r_fwd) if r_bwd["ms_per_step"] > r_fwd["ms_per_step"] else (r_fwd, r_bwd)
     total_kernel_ms = sum(v["ms"] for v in tm.values())
     kernels = {k: {"calls": v["calls"], "ms_per_step": v["ms"] / args.steps} for k, v in sorted(tm.items())}
     line = {
@@ -317,7 +344,7 @@ def ours(args):
         "e2e": {"value": e2e, "unit": unit, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms2 / args.steps},
         "gpu_launches": launches["k1"] - launches["k0"], "abi_calls": launches["c1"] - launches["c0"],
-        "roofline": roofline, "kernels": kernels, "own_kernel_ms_per_step": total_kernel_ms / args.steps,
+        "roofline": roofline, "roofline_second_kernel": roofline_other, "kernels": kernels, "own_kernel_ms_per_step": total_kernel_ms / args.steps,
         "clocks": launches.get("clocks"),
     }
     if not args.no_cpu_baseline and world == 1:
