@@ -25,7 +25,7 @@ namespace skp {
 constexpr int BW_SEL = 16;            // selected tokens per launch (UMMA N of the S_sel product)
 constexpr int BW_KSEL_BYTES = BW_SEL * 128;   // 16 rows x 128 B
 constexpr int BW_DS_BYTES = TC_BM * TC_BN * 2;   // 64 KB: dS tile, 4 slabs of [128 px][64 tok] bf16
-constexpr int BW_WXT_FLOATS = 5 * 256;        // x-adjoint table: s * (5 * R/s) = 5 R floats, R <= 256
+constexpr int BW_WXT_FLOATS = 8 * 256;        // x-adjoint table: s rows of 5 R/s taps padded to a multiple of 4 (<= 8 R/s... R <= 256)
 constexpr float kLog2eBw = 1.4426950408889634f;
 constexpr int BW_STG_LD = 68;          // fp32 staging row pitch (64 + 4): conflict-free float4 stores with lane = row
 
@@ -328,15 +328,16 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       nxu = bw_next(P, x);
       const int d = P.ops.d[x.l], s = P.s[x.l], C = P.C[x.l];
       const int up = ((R & (R - 1)) | (s & (s - 1))) == 0 ? R >> (__ffs(s) - 1) : R / s, nj = 5 * up;
+      const int njp = (nj + 3) & ~3;            // table row pitch: the gather loops run in groups of four taps
       const float wgt = P.ops.weight[x.l], scale = P.ops.scale[x.l];
       if (x.l != prev_l || x.b != prev_b) {
         named_bar_sync(1, TC_SOFTMAX_THREADS);
         if (x.l != prev_l) {
           const float ratio = static_cast<float>(s) / R;
-          for (int e = stid; e < s * nj; e += TC_SOFTMAX_THREADS) {
-            const int sx = e / nj, xx = max(0, (sx - 2) * up) + e % nj;
+          for (int e = stid; e < s * njp; e += TC_SOFTMAX_THREADS) {
+            const int sx = e / njp, jj = e % njp, xx = max(0, (sx - 2) * up) + jj;
             float wsum = 0.0f;
-            if (xx < R) {
+            if (jj < nj && xx < R) {
               int ix;
               float w[4];
               bicubic_coeffs(xx, ratio, &ix, w);
@@ -471,7 +472,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
 #pragma unroll
           for (int g = 0; g < 4; ++g) a4[g] = make_float4(0.f, 0.f, 0.f, 0.f);
           const int j0 = max(0, x0 - xlo), j1 = min(nj, x0 + span - xlo);
-          const float* wrow = wxt + sx * nj;
+          const float* wrow = wxt + sx * njp;
           if (span == R && R == TC_BM) {
             // one whole image row per tile: every tap of the table is inside the tile (taps past the row
             // end have weight 0 and read finite bytes of the dS area), addresses are base + immediates

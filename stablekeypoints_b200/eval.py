@@ -7,6 +7,7 @@ Reference lines replaced:
   find_k_max_pixels / mask_radius   eval.py:62-111
   pixel_from_weighted_avg           eval.py:113-155
   run_image_with_context_augmented  eval.py:197-355
+  swap_points / evaluate            eval.py:360-539   (metrics: SURVEY.md §8(f) rank 2)
 """
 from __future__ import annotations
 
@@ -50,6 +51,18 @@ def pixel_from_weighted_avg(heatmaps: torch.Tensor, distance: float = 5) -> torc
 
 
 @torch.no_grad()
+def find_corresponding_points(maps: torch.Tensor, num_points: int = 10):
+    """`eval.py:159-195` (unused by `main`): rank tokens by their pixel-softmax entropy summed over the
+    images, keep the `num_points` lowest, return their argmax pixels per image and the token ids.
+    maps (num_images, num_tokens, h, w) -> ((num_images, num_points, 2), (num_points,) int64).
+    Entropies and argmaxes come from `skp_plane_stats` / `skp_plane_argmax`, the ranking from `skp_rank_ascending`."""
+    ni, nt, h, w = maps.shape
+    _, ent, _ = ops.plane_stats(maps.reshape(ni * nt, h, w), want_kl=False, want_entropy=True)
+    order = ops.rank_ascending(ent.reshape(ni, nt).sum(dim=0), int(num_points))
+    chosen = maps[:, order].reshape(ni * order.numel(), h, w).contiguous()
+    return find_max_pixel(chosen).reshape(ni, order.numel(), 2), order
+
+
 def run_image_with_context_augmented(
     ldm,
     image,
@@ -106,3 +119,106 @@ def run_image_with_context_augmented(
             upsample_res=-1, device=device, controllers=controllers, indices=indices, noise=nz)   # (G,K,R,R)
         ops.tta_accumulate(maps, transform.inverse_theta(), sum_samples, num_samples)
     return ops.tta_finalize(sum_samples, num_samples)
+
+
+# --------------------------------------------------------------------------------------
+# evaluation (`eval.py:360-539`)
+# --------------------------------------------------------------------------------------
+_H36M_PAIRS = ((1, 6), (2, 7), (3, 8), (4, 9), (5, 10), (17, 25), (18, 26), (19, 27), (20, 28), (21, 28), (22, 30), (23, 31))
+
+
+def swap_points(points: torch.Tensor) -> torch.Tensor:
+    """Left/right relabelling of Human3.6M keypoints, points (B, N, D) (`eval.py:360-371`; the table,
+    including its (21, 28) entry, is the reference's)."""
+    perm = list(range(points.shape[1]))
+    for a, b in _H36M_PAIRS:
+        perm[a] = b
+        perm[b] = a
+    return points[:, perm, :]
+
+
+def keypoint_error(estimated_kpts: torch.Tensor, gt_kpts: torch.Tensor, evaluation_method: str = "inter_eye_distance",
+                   visible: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Per-image error of `evaluate` (`eval.py:469-510`) for (n, 2) regressed / annotated keypoints in [0, 1]."""
+    if evaluation_method in ("mean_average_error", "pck"):
+        estimated_kpts, gt_kpts = estimated_kpts * 256, gt_kpts * 256
+    l2 = (estimated_kpts - gt_kpts).norm(dim=-1)
+    if evaluation_method == "inter_eye_distance":
+        return (l2 / torch.sqrt(((gt_kpts[0] - gt_kpts[1]) ** 2).sum(dim=-1))).mean()
+    if evaluation_method in ("visible", "mean_average_error"):
+        vis = torch.ones_like(l2) if visible is None else visible.to(l2)
+        err = (l2 * vis).sum()
+        return err / vis.sum() if evaluation_method == "visible" else err
+    if evaluation_method == "pck":
+        return (l2 < 6).float().mean()
+    if evaluation_method == "orientation_invariant":
+        swapped = (swap_points(estimated_kpts[None])[0] - gt_kpts).norm(dim=-1).mean()
+        return torch.minimum(l2.mean(), swapped) * 128
+    raise NotImplementedError(evaluation_method)
+
+
+@torch.no_grad()
+def evaluate(
+    ldm,
+    context,
+    indices,
+    regressor,
+    device="cuda",
+    from_where=["down_cross", "mid_cross", "up_cross"],
+    upsample_res=32,
+    layers=[0, 1, 2, 3, 4, 5],
+    noise_level=-1,
+    num_tokens=1000,
+    augment_degrees=30,
+    augment_scale=(0.9, 1.1),
+    augment_translate=(0.1, 0.1),
+    augmentation_iterations=20,
+    dataset_loc="~",
+    save_folder="outputs",
+    wandb_log=False,
+    visualize=False,
+    dataset_name="celeba_aligned",
+    evaluation_method="inter_eye_distance",
+    controllers=None,
+    num_gpus=1,
+    max_loc_strategy="argmax",
+    validation=False,
+    dataset=None,
+    log_fn=print,
+):
+    """`eval.py:374-539`: TTA extraction -> readout -> linear regressor -> dataset metric, per test
+    image; writes `all_errors.pt` into `save_folder` like the reference and returns the (N,) errors.
+    Images are sharded across ranks, one all_gather of the scalar errors at the end."""
+    import os
+    from . import distributed as dist_
+    from .optimize import _make_dataset
+
+    world, rank = dist_.world_size(), dist_.rank()
+    dataset = _make_dataset(dataset_name, dataset_loc, dataset)
+    n = len(dataset)
+    per = (n + world - 1) // world
+    regressor = torch.as_tensor(regressor).to(device=device, dtype=torch.float32)
+    errs = []
+    for i in dist_.shard_range(n, rank, world):
+        sample = dataset[i]
+        maps = run_image_with_context_augmented(
+            ldm, sample["img"], context, torch.as_tensor(indices).cpu(), device=device, from_where=from_where,
+            layers=layers, noise_level=noise_level, augmentation_iterations=augmentation_iterations,
+            augment_degrees=augment_degrees, augment_scale=augment_scale, augment_translate=augment_translate,
+            controllers=controllers, num_gpus=num_gpus, save_folder=save_folder)
+        kp = (find_max_pixel(maps) if max_loc_strategy == "argmax" else pixel_from_weighted_avg(maps)) / 512.0
+        est = (((kp.reshape(1, -1) - 0.5) @ regressor) + 0.5).reshape(-1, 2)
+        gt = torch.as_tensor(sample["kpts"]).to(device=device, dtype=torch.float32)
+        vis = torch.as_tensor(sample["visibility"]).to(device) if "visibility" in sample else None
+        errs.append(keypoint_error(est, gt, evaluation_method, vis))
+    t = torch.stack(errs) if errs else torch.zeros(0, device=device)
+    if world > 1:
+        t = torch.cat([t, torch.zeros(per - t.shape[0], device=device)])
+        t = dist_.interleave_shards(dist_.all_gather_cat(t), n)
+    all_errors = t.cpu()
+    if rank == 0:
+        if log_fn:
+            log_fn(f"mean distance: {float(all_errors.mean()) if n else float('nan'):.6f} over {n} images ({evaluation_method})")
+        os.makedirs(save_folder, exist_ok=True)
+        torch.save(all_errors, os.path.join(save_folder, "all_errors.pt"))
+    return all_errors

@@ -133,3 +133,65 @@ def precompute_all_keypoints(
         return dist_.interleave_shards(dist_.all_gather_cat(t), n)
 
     return _gather(src), _gather(tgt), (_gather(vis) if vis else None)
+
+
+# --------------------------------------------------------------------------------------
+# linear regressors from unsupervised to annotated keypoints (`keypoint_regressor.py:227-299`)
+# Closed-form least squares in fp64 on the tensors' own device; (N, 2K) -> (N, 2n), both
+# centred at 0.5 like the reference.  Accept numpy arrays or tensors, return what they were given.
+# --------------------------------------------------------------------------------------
+def _as64(a):
+    was_numpy = not torch.is_tensor(a)
+    return torch.as_tensor(a).to(torch.float64), was_numpy
+
+
+def _back(w: torch.Tensor, was_numpy: bool):
+    return w.cpu().numpy() if was_numpy else w
+
+
+def _lstsq_pinv(x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+    return torch.linalg.pinv(x.T @ x) @ x.T @ y
+
+
+def return_regressor(X, Y):
+    """`W = pinv(X^T X) X^T Y` on X - 0.5, Y - 0.5 (`keypoint_regressor.py:256-266`)."""
+    x, np_in = _as64(X)
+    y, _ = _as64(Y)
+    return _back(_lstsq_pinv(x - 0.5, y.to(x.device) - 0.5), np_in)
+
+
+def return_regressor_visible(X, Y, visible):
+    """One least-squares problem per output column over the rows where that column is visible
+    (`keypoint_regressor.py:227-253`)."""
+    x, np_in = _as64(X)
+    y, _ = _as64(Y)
+    v, _ = _as64(visible)
+    x, y, v = x - 0.5, y.to(x.device) - 0.5, v.to(x.device)
+    w = torch.zeros(x.shape[1], y.shape[1], dtype=torch.float64, device=x.device)
+    for j in range(y.shape[1]):
+        rows = torch.nonzero(v[:, j] == 1).flatten()
+        w[:, j] = _lstsq_pinv(x[rows], y[rows, j])
+    return _back(w, np_in)
+
+
+def return_regressor_human36m(X, Y):
+    """Least squares with the Human3.6M left/right label swap: refit until at most 10 samples are
+    closer to their mirrored annotation than to the given one (`keypoint_regressor.py:269-299`)."""
+    from .eval import swap_points
+    x, np_in = _as64(X)
+    y, _ = _as64(Y)
+    x, y = x - 0.5, (y.to(x.device) - 0.5).clone()
+    proj = torch.linalg.inv(x.T @ x) @ x.T
+    while True:
+        w = proj @ y
+        pred = x @ w
+        n = x.shape[0]
+        dist = (pred - y).reshape(n, -1, 2).norm(dim=2).mean(dim=1)
+        swapped = swap_points(y.reshape(n, -1, 2)).reshape(n, -1)
+        swapped_dist = (pred - swapped).reshape(n, -1, 2).norm(dim=2).mean(dim=1)
+        should_swap = dist > swapped_dist
+        if int(should_swap.sum()) > 10:
+            y[should_swap] = swapped[should_swap]
+        else:
+            break
+    return _back(w, np_in)

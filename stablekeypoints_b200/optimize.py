@@ -104,6 +104,53 @@ def sharpening_loss(attn_map, sigma=1.0, temperature=1e1, device="cuda", num_sub
 # --------------------------------------------------------------------------------------
 # token optimisation (`optimize.py:269-475`)
 # --------------------------------------------------------------------------------------
+# --------------------------------------------------------------------------------------
+# helpers the reference defines but never calls from `main` (`optimize.py:82-135, 209-266`;
+# SURVEY.md §8(a) row 19).  Kept for API completeness; plain differentiable tensor algebra on
+# the caller's device, not part of the measured path.
+# --------------------------------------------------------------------------------------
+def create_gaussian_kernel(size: int, sigma: float) -> torch.Tensor:
+    """Normalised (size, size) Gaussian, centre at size // 2 (`optimize.py:82-103`)."""
+    assert size % 2 == 1, "Size must be odd"
+    r = torch.arange(size, dtype=torch.float32) - size // 2
+    k = torch.exp(-(r[:, None] ** 2 + r[None, :] ** 2) / (2 * sigma ** 2))
+    return k / k.sum()
+
+
+def gaussian_loss(attn_map, kernel_size=5, sigma=1.0, temperature=1e-4):
+    """`optimize.py:106-135`: MSE between the map and its own temperature pixel-softmax (gradient
+    stopped).  The reference also blurs that softmax with a 5x5 Gaussian and max-normalises it, then
+    does not use the result (`:120-132`); the blur is therefore not computed here."""
+    t = attn_map.shape[0]
+    probs = torch.softmax(attn_map.reshape(t, -1) / temperature, dim=1).detach().reshape(attn_map.shape)
+    return torch.nn.functional.mse_loss(attn_map, probs)
+
+
+def _normalised(heatmaps):
+    return heatmaps / (heatmaps.sum(dim=(1, 2), keepdim=True) + 1e-6)
+
+
+def variance_loss(heatmaps):
+    """Mean over planes of the spatial standard deviation of the normalised heat-map (`optimize.py:209-241`)."""
+    _, m, n = heatmaps.shape
+    p = _normalised(heatmaps)
+    x = torch.arange(m, device=heatmaps.device, dtype=torch.float32).view(1, m, 1)
+    y = torch.arange(n, device=heatmaps.device, dtype=torch.float32).view(1, 1, n)
+    xm = (x * p).sum(dim=(1, 2), keepdim=True)
+    ym = (y * p).sum(dim=(1, 2), keepdim=True)
+    return torch.sqrt((p * ((x - xm) ** 2 + (y - ym) ** 2)).sum(dim=(1, 2))).mean()
+
+
+def differentiable_argmax(heatmaps):
+    """Soft-argmax `sum(coord * v) / (sum(v) + 1e-6)` -> (N, 2) as (row, col), no half-pixel offset
+    (`optimize.py:244-266`).  The readout used by the live path is `eval.pixel_from_weighted_avg`."""
+    _, m, n = heatmaps.shape
+    p = _normalised(heatmaps)
+    x = torch.arange(m, device=heatmaps.device, dtype=torch.float32).view(1, m, 1)
+    y = torch.arange(n, device=heatmaps.device, dtype=torch.float32).view(1, 1, n)
+    return torch.stack([(x * p).sum(dim=(1, 2)), (y * p).sum(dim=(1, 2))], dim=1)
+
+
 def select_tokens(attn_map, attn_map_transformed, top_k_strategy, furthest_point_num_samples, top_k, sigma, num_subjects):
     """Candidate ranking on the image's maps + furthest-point sampling on the transformed image's
     maps (`optimize.py:405-418`) -> (top_k,) int64 on the maps' device, no host sync."""
