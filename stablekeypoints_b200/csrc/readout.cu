@@ -72,6 +72,21 @@ __device__ unsigned long long block_masked_argmax(const float* __restrict__ p, i
                                                   unsigned long long* scratch) {
   unsigned long long best = 0ull;
   const int n = H * W;
+  if (d.n == 0 && (n & 3) == 0 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) {
+    // no disc yet (the first, usually only, subject): 16-byte loads, no per-pixel row/column arithmetic
+    const float4* p4 = reinterpret_cast<const float4*>(p);
+    for (int i = threadIdx.x; i < (n >> 2); i += blockDim.x) {
+      const float4 v = __ldg(p4 + i);
+      const uint32_t b = static_cast<uint32_t>(i) << 2;
+      unsigned long long k0 = argmax_key(v.x, b), k1 = argmax_key(v.y, b + 1);
+      unsigned long long k2 = argmax_key(v.z, b + 2), k3 = argmax_key(v.w, b + 3);
+      k0 = k0 > k1 ? k0 : k1;
+      k2 = k2 > k3 ? k2 : k3;
+      k0 = k0 > k2 ? k0 : k2;
+      best = best > k0 ? best : k0;
+    }
+    return block_max_u64(best, scratch);
+  }
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
     float v = p[i];
     if (d.n) v = disc_masked(v, i / W, i % W, d);
@@ -170,9 +185,11 @@ __global__ void plane_stats_kernel(const float* __restrict__ maps, int H, int W,
   d.n = 0;
   d.rad2 = static_cast<float>((0.05 * static_cast<double>(H)) * (0.05 * static_cast<double>(H)));
   float cr[8], cc[8];
+  uint32_t first_idx = 0;
   for (int s = 0; s < num_subjects; ++s) {
     unsigned long long key = block_masked_argmax(p, H, W, d, scratch);
     uint32_t idx = argmax_key_index(key);
+    if (s == 0) first_idx = idx;
     if (s == 0 && argmax_out && threadIdx.x == 0) argmax_out[blockIdx.x] = idx;
     float r = static_cast<float>(idx / W) + 0.5f, c = static_cast<float>(idx % W) + 0.5f;
     d.r[d.n] = r;
@@ -182,48 +199,70 @@ __global__ void plane_stats_kernel(const float* __restrict__ maps, int H, int W,
     cc[s] = __fmul_rn(__fdiv_rn(c, static_cast<float>(H)), static_cast<float>(H));
     __syncthreads();
   }
-  // plane max (unmasked) for the pixel softmax
-  float mx = -INFINITY;
-  for (int i = threadIdx.x; i < n; i += blockDim.x) mx = fmaxf(mx, p[i]);
-  mx = block_max(mx, fscratch);
+  // Plane max for the pixel softmax = the value at the first (unmasked) argmax.  Everything else is ONE more pass
+  // over the plane (L1/L2-resident after the argmax pass), fp32 per element, fp64 accumulators:
+  //   s0 = sum e^(x-mx), s1 = sum e^(x-mx) (x-mx)                      -> entropy = log s0 - s1/s0
+  //   a = gaussian/S + eps, z = sum a, A = sum a log a, Bv = sum a (x-mx)
+  //   KL(target || softmax) = sum (a/z) (log(a/z) - (x - mx - log s0)) = (A - Bv)/z - log z + log s0
+  // (the per-pixel double-precision log and division of the textbook form were 17x slower than the loads).
+  const float mx = p[first_idx];
   const float inv2s2 = 1.0f / (2.0f * sigma * sigma);
   const float invS = 1.0f / static_cast<float>(num_subjects);
-  double s0 = 0.0, s1 = 0.0, z = 0.0;
-  for (int i = threadIdx.x; i < n; i += blockDim.x) {
-    float v = p[i] - mx;
-    float e = expf(v);
-    s0 += e;
-    s1 += static_cast<double>(e) * v;
-    if (kl_out) {
-      float rr = static_cast<float>(i / W) + 0.5f, cx = static_cast<float>(i % W) + 0.5f;
+  const bool want_kl = kl_out != nullptr;
+  const bool wp2 = (W & (W - 1)) == 0;
+  const int lgw = __ffs(W) - 1;
+  double s0 = 0.0, s1 = 0.0, z = 0.0, A = 0.0, Bv = 0.0;
+  // per-pixel terms in fp32; the four pixels of a 16-byte load are summed in fp32 (a 3-add tree) and enter the fp64
+  // accumulators once per vector: the float->double conversions (XU pipe, 16/clk/SM) were the bottleneck
+  struct Terms { float e, ev, a, alog, av; };
+  auto pixel = [&](float x, float rr, float cx) -> Terms {      // rr, cx: pixel centre (row + 0.5, col + 0.5)
+    Terms t;
+    const float v = x - mx;
+    t.e = expf(v);
+    t.ev = t.e * v;
+    t.a = t.alog = t.av = 0.0f;
+    if (want_kl) {
       float g = 0.0f;
       for (int s = 0; s < num_subjects; ++s) {
-        float dc = cx - cc[s], dr = rr - cr[s];
+        const float dc = cx - cc[s], dr = rr - cr[s];
         g += expf(-(dc * dc + dr * dr) * inv2s2);
       }
-      z += static_cast<double>(g * invS + eps);
+      t.a = g * invS + eps;
+      t.alog = t.a * logf(t.a);
+      t.av = t.a * v;
+    }
+    return t;
+  };
+  if ((n & 3) == 0 && (W & 3) == 0 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) {
+    const float4* p4 = reinterpret_cast<const float4*>(p);
+    for (int i4 = threadIdx.x; i4 < (n >> 2); i4 += blockDim.x) {
+      const float4 x = __ldg(p4 + i4);
+      const int i = i4 << 2;
+      const int row = wp2 ? i >> lgw : i / W, col = wp2 ? i & (W - 1) : i - row * W;   // W % 4 == 0: one row per vector
+      const float rr = static_cast<float>(row) + 0.5f, cx = static_cast<float>(col) + 0.5f;   // integers + 0.5: exact in fp32
+      const Terms t0 = pixel(x.x, rr, cx), t1 = pixel(x.y, rr, cx + 1.0f), t2 = pixel(x.z, rr, cx + 2.0f), t3 = pixel(x.w, rr, cx + 3.0f);
+      s0 += static_cast<double>((t0.e + t1.e) + (t2.e + t3.e));
+      s1 += static_cast<double>((t0.ev + t1.ev) + (t2.ev + t3.ev));
+      if (want_kl) {
+        z += static_cast<double>((t0.a + t1.a) + (t2.a + t3.a));
+        A += static_cast<double>((t0.alog + t1.alog) + (t2.alog + t3.alog));
+        Bv += static_cast<double>((t0.av + t1.av) + (t2.av + t3.av));
+      }
+    }
+  } else {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      const Terms t = pixel(p[i], static_cast<float>(i / W) + 0.5f, static_cast<float>(i % W) + 0.5f);
+      s0 += t.e; s1 += t.ev; z += t.a; A += t.alog; Bv += t.av;
     }
   }
   s0 = block_sum(s0, dscratch);
   s1 = block_sum(s1, dscratch);
   if (ent_out && threadIdx.x == 0) ent_out[blockIdx.x] = static_cast<float>(log(s0) - s1 / s0);
-  if (!kl_out) return;
+  if (!want_kl) return;
   z = block_sum(z, dscratch);
-  const double log_s0 = log(s0);
-  double kl = 0.0;
-  for (int i = threadIdx.x; i < n; i += blockDim.x) {
-    float rr = static_cast<float>(i / W) + 0.5f, cx = static_cast<float>(i % W) + 0.5f;
-    float g = 0.0f;
-    for (int s = 0; s < num_subjects; ++s) {
-      float dc = cx - cc[s], dr = rr - cr[s];
-      g += expf(-(dc * dc + dr * dr) * inv2s2);
-    }
-    double t = static_cast<double>(g * invS + eps) / z;
-    double logp = static_cast<double>(p[i] - mx) - log_s0;
-    kl += t * (log(t) - logp);
-  }
-  kl = block_sum(kl, dscratch);
-  if (threadIdx.x == 0) kl_out[blockIdx.x] = static_cast<float>(kl);
+  A = block_sum(A, dscratch);
+  Bv = block_sum(Bv, dscratch);
+  if (threadIdx.x == 0) kl_out[blockIdx.x] = static_cast<float>((A - Bv) / z - log(z) + log(s0));
 }
 
 __global__ void gaussian_circles_kernel(const float* __restrict__ pos, int S, int N, int size, float sigma, float* out) {
