@@ -194,11 +194,39 @@ struct TcSmem {
   static constexpr int kDynamic = kTotal + 1024;                       // slack for manual 1024 B alignment
 };
 
+// Phase profiler of the softmax warps (diagnostic builds only: nvcc -DSKP_FWD_PROF): cycles per phase averaged
+// over the units of one CTA, printed by a few warps of blocks (0..1, 0).
+#ifdef SKP_FWD_PROF
+#define FW_PROF_DECL long long pf_t = clock64(), pf_acc[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+#define FW_PROF(i) { const long long pf_n = clock64(); pf_acc[i] += pf_n - pf_t; pf_t = pf_n; }
+#else
+#define FW_PROF_DECL
+#define FW_PROF(i)
+#endif
+
 // 2^d for an integer-valued d <= 0 (or -inf), flushed to 0 below 2^-126, without MUFU: the integer lands in the
 // low mantissa bits of d + 1.5 * 2^23 and is shifted into the exponent field.
 __device__ __forceinline__ float pow2_int(float d) {
   const int bits = __float_as_int(fmaxf(d, -127.0f) + 12582912.0f);
   return __int_as_float((bits << 23) + 0x3f800000);
+}
+
+// 2^x for x <= 0 on the FMA / ALU pipes instead of MUFU (pass B is MUFU-bound at 16 ex2/clk/SM while the FMA pipe idles,
+// so every FW_POLY_EVERY-th exponential goes this way): round-to-nearest split x = n + f via the 1.5 * 2^23 trick,
+// degree-5 interpolant of 2^f on [-0.5, 0.5] (max relative error 2.4e-7 in fp32 Horner, the same 2 ulp class as
+// ex2.approx), n added into the exponent field.  Inputs below -126 clamp to 2^-126 (~1e-38; they would flush to 0).
+constexpr int FW_POLY_EVERY = 4;
+__device__ __forceinline__ float exp2_poly(float x) {
+  x = fmaxf(x, -126.0f);
+  const float t = x + 12582912.0f;
+  const float f = x - (t - 12582912.0f);
+  float p = 0.0013390863314270973f;
+  p = fmaf(p, f, 0.009676031768321991f);
+  p = fmaf(p, f, 0.055503569543361664f);
+  p = fmaf(p, f, 0.2402210682630539f);
+  p = fmaf(p, f, 0.6931471824645996f);
+  p = fmaf(p, f, 1.0000001192092896f);
+  return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
 }
 
 // 20 warps = 5 warpgroups: warpgroup 0 = {TMA producer, MMA issuer, 2 idle warps} gives registers back
@@ -373,10 +401,12 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
     for (int j = 0; j < (SELECT ? TC_MAX_SEL : FW_QCOLS); ++j) acc[j] = 0.0f;
 
     // normalise + accumulate unit uu, whose exponentials this thread parked in TMEM one iteration ago
+    FW_PROF_DECL
     auto pass_c = [&](uint32_t uu, float m_own, float wgt_u) {
       const uint32_t buf = uu & 1u, par = (uu >> 1) & 1u;
       const uint32_t taddr = t_lane + buf * TC_BN + col0;
       ptx::mbar_wait(bar_xfull(buf), par);
+      FW_PROF(3)
       float mg = -INFINITY;
 #pragma unroll
       for (int q = 0; q < NPART; ++q) mg = fmaxf(mg, stats[(buf * FW_MAX_PARTS + q) * TC_BM + row].x);
@@ -390,6 +420,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
         reinterpret_cast<float2*>(P.row_stats)[(static_cast<int64_t>(b) * P.ops.total_heads + uu) * P.R2 + p0 + row] =
             make_float2(mg, total);
       const float cf = ncol > 0 ? __fdividef(wgt_u * pow2_int(m_own - mg), total) : 0.0f;
+      FW_PROF(4)
       if (!SELECT) {
 #pragma unroll
         for (int c = 0; c < NCH; ++c) {
@@ -397,8 +428,10 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
             uint32_t v[32];
             ptx::tmem_ld32(taddr + 32 * c, v);
             ptx::tmem_ld_wait();
+            FW_PROF(5)
 #pragma unroll
             for (int j = 0; j < 32; ++j) acc[32 * c + j] = fmaf(cf, __uint_as_float(v[j]), acc[32 * c + j]);
+            FW_PROF(6)
           }
         }
       } else {
@@ -425,6 +458,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
         const uint32_t buf = u & 1u, par = (u >> 1) & 1u;
         ptx::mbar_wait(bar_tfull(buf, hf), par);
         ptx::tc_fence_after();
+        FW_PROF(0)
         const uint32_t taddr = t_lane + buf * TC_BN + col0;
         // ---- pass A: row max over my columns (four independent chains)
         float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
@@ -434,6 +468,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
             uint32_t v[32];
             ptx::tmem_ld32(taddr + 32 * c, v);
             ptx::tmem_ld_wait();
+            FW_PROF(1)
             if (ncol >= 32 * (c + 1)) {
 #pragma unroll
               for (int j = 0; j < 32; j += 8) {
@@ -452,6 +487,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
         // Rounded up to an integer: any m >= the true max stabilises the exponentials equally well, and
         // integer-valued maxima make every rescale 2^(m_part - m_row) an exponent-field add, not a MUFU.
         const float m = ceilf(fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)));
+        FW_PROF(2)
         // ---- pass C of the previous unit
         if (u > 0) pass_c(u - 1, m_prev, wgt_prev);
         // ---- pass B: exponentials (parked back in TMEM) and their sum
@@ -462,11 +498,13 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
             uint32_t v[32];
             ptx::tmem_ld32(taddr + 32 * c, v);
             ptx::tmem_ld_wait();
+            FW_PROF(7)
             if (ncol >= 32 * (c + 1)) {
 #pragma unroll
               for (int j = 0; j < 32; j += 4) {
                 const float e0 = ptx::ex2(__uint_as_float(v[j]) - m), e1 = ptx::ex2(__uint_as_float(v[j + 1]) - m);
-                const float e2 = ptx::ex2(__uint_as_float(v[j + 2]) - m), e3 = ptx::ex2(__uint_as_float(v[j + 3]) - m);
+                const float e2 = ptx::ex2(__uint_as_float(v[j + 2]) - m);
+                const float e3 = FW_POLY_EVERY == 4 ? exp2_poly(__uint_as_float(v[j + 3]) - m) : ptx::ex2(__uint_as_float(v[j + 3]) - m);
                 s0 += e0; s1 += e1; s2 += e2; s3 += e3;
                 v[j] = __float_as_uint(e0); v[j + 1] = __float_as_uint(e1);
                 v[j + 2] = __float_as_uint(e2); v[j + 3] = __float_as_uint(e3);
@@ -479,11 +517,13 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
                 v[j] = __float_as_uint(e);
               }
             }
+            FW_PROF(8)
             ptx::tmem_st32(taddr + 32 * c, v);
           }
         }
         const float sum = (s0 + s1) + (s2 + s3);
         ptx::tmem_st_wait();
+        FW_PROF(9)
         // ---- post (max, sum) to every column part of the cluster.  Local slot: plain store + arrive.
         // Remote slot: st.async, which completes bytes on the peer's mbarrier itself (no cluster-scope
         // release fence, no L1 invalidate on the waiter).
@@ -503,8 +543,15 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
         }
         m_prev = m;
         wgt_prev = wgt;
+        FW_PROF(10)
       }
     }
+#ifdef SKP_FWD_PROF
+    if (blockIdx.x < 2 && blockIdx.y == 0 && lane == 0 && (warp & 3) == 0)
+      printf("cta %d warp %2d: wait_mma %lld | A ld %lld cmp %lld | wait_x %lld comb %lld | C ld %lld fma %lld (+arrive in next) | B ld %lld cmp %lld st+wait %lld | post %lld\n",
+             blockIdx.x, warp, pf_acc[0] / u, pf_acc[1] / u, pf_acc[2] / u, pf_acc[3] / u, pf_acc[4] / u, pf_acc[5] / u, pf_acc[6] / u,
+             pf_acc[7] / u, pf_acc[8] / u, pf_acc[9] / u, pf_acc[10] / u);
+#endif
     if (u > 0) pass_c(u - 1, m_prev, wgt_prev);
     // ---- write-out: lanes hold consecutive pixels -> 128 B coalesced stores per token
     if (!SELECT) {
