@@ -15,6 +15,16 @@ KEYS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "sm__inst_executed_pipe_tmem", "smsp__inst_executed.sum", "lts__t_sector_hit_rate.pct", "sm__cycles_active.avg"]
 
 
+def own_kernel_names():
+    """__global__ function names of stablekeypoints_b200/csrc/*.cu (ncu prints kernel names without the namespace)."""
+    import glob, os, re
+    root = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "stablekeypoints_b200", "csrc")
+    names = set()
+    for f in glob.glob(os.path.join(root, "*.cu")):
+        names.update(re.findall(r"(\w+_kernel)\s*\(", open(f).read()))
+    return names
+
+
 def launches(path):
     lines = [l for l in open(path) if not l.startswith("==")]
     agg = collections.OrderedDict()
@@ -28,9 +38,18 @@ def launches(path):
         a[0] += 1
         a[1] += v
     tot = sum(a[1] for a in agg.values())
-    print(f"# {path}: per-kernel device time of the library's kernels (ncu, cold-cache, serialised: compare SHARES)")
-    for k, (n, t) in sorted(agg.items(), key=lambda x: -x[1][1]):
-        print(f"{k[:72]:72s} n={n:4d} total={t / 1e3:10.3f} ms  avg={t / n:11.1f} us  share={t / tot * 100:5.1f}%")
+    ours = {k: a for k, a in agg.items() if any(n in k for n in own_kernel_names())}
+    t_ours = sum(a[1] for a in ours.values())
+    print(f"# {path}: per-kernel device time (ncu, cold-cache, serialised: compare SHARES)")
+    print(f"# all launches: {sum(a[0] for a in agg.values())} kernels, {tot / 1e3:.1f} ms; this library's kernels: "
+          f"{sum(a[0] for a in ours.values())} launches, {t_ours / 1e3:.1f} ms = {100 * t_ours / tot:.1f} % of the device time")
+    print("# --- this library")
+    for k, (n, t) in sorted(ours.items(), key=lambda x: -x[1][1]):
+        print(f"{k[:72]:72s} n={n:5d} total={t / 1e3:10.3f} ms  avg={t / n:11.1f} us  share={t / tot * 100:5.1f}%")
+    print("# --- everything else (stock PyTorch trunk), top 20")
+    rest = [(k, a) for k, a in agg.items() if k not in ours]
+    for k, (n, t) in sorted(rest, key=lambda x: -x[1][1])[:20]:
+        print(f"{k[:72]:72s} n={n:5d} total={t / 1e3:10.3f} ms  avg={t / n:11.1f} us  share={t / tot * 100:5.1f}%")
 
 
 def full(path):

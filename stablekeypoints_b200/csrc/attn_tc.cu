@@ -215,7 +215,7 @@ __device__ __forceinline__ float pow2_int(float d) {
 // so every FW_POLY_EVERY-th exponential goes this way): round-to-nearest split x = n + f via the 1.5 * 2^23 trick,
 // degree-5 interpolant of 2^f on [-0.5, 0.5] (max relative error 2.4e-7 in fp32 Horner, the same 2 ulp class as
 // ex2.approx), n added into the exponent field.  Inputs below -126 clamp to 2^-126 (~1e-38; they would flush to 0).
-constexpr int FW_POLY_EVERY = 4;
+constexpr int FW_POLY_EVERY = 0;     // 4 = every fourth exponential; measured neutral (the kernel is issue-slot bound: 12 vs 3 instructions)
 __device__ __forceinline__ float exp2_poly(float x) {
   x = fmaxf(x, -126.0f);
   const float t = x + 12582912.0f;
@@ -316,7 +316,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
           for (int kb = 0; kb < nkb; ++kb, ++it) {
             const int s = it % SM::kStages;
             const uint32_t ph = (it / SM::kStages) & 1u;
-            ptx::mbar_wait(bar_empty(s), ph ^ 1u);
+            ptx::mbar_wait_hint(bar_empty(s), ph ^ 1u, 2000u);
             ptx::mbar_arrive_expect_tx(bar_full(s), SM::kStageBytes);
             const uint32_t st = base + s * SM::kStageBytes;
             ptx::tma_load_3d(st, &P.ops.q_map[l][0], bar_full(s), kb * TC_BK, p0, qz);
@@ -346,13 +346,13 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
           const uint32_t buf = u & 1u;
           for (int kb = 0; kb < nkb; ++kb, ++it) {
             const int s = it % SM::kStages;
-            ptx::mbar_wait(bar_full(s), (it / SM::kStages) & 1u);
+            ptx::mbar_wait_hint(bar_full(s), (it / SM::kStages) & 1u, 2000u);
             ptx::tc_fence_after();
             const uint32_t st = base + s * SM::kStageBytes;
             const int nk16 = (min(TC_BK, d - kb * TC_BK) + 15) / 16;
             for (int hf = 0; hf < FW_NH; ++hf) {
               if (kb == 0) {
-                ptx::mbar_wait(bar_tempty(buf, hf), ((u >> 1) & 1u) ^ 1u);   // softmax drained this half buffer
+                ptx::mbar_wait_hint(bar_tempty(buf, hf), ((u >> 1) & 1u) ^ 1u, 2000u);   // softmax drained this half buffer
                 ptx::tc_fence_after();
               }
               const uint32_t d_tmem = tmem_base + buf * TC_BN + hf * (TC_BN / FW_NH);
@@ -405,7 +405,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
     auto pass_c = [&](uint32_t uu, float m_own, float wgt_u) {
       const uint32_t buf = uu & 1u, par = (uu >> 1) & 1u;
       const uint32_t taddr = t_lane + buf * TC_BN + col0;
-      ptx::mbar_wait(bar_xfull(buf), par);
+      ptx::mbar_wait_hint(bar_xfull(buf), par, 500u);
       FW_PROF(3)
       float mg = -INFINITY;
 #pragma unroll
@@ -456,7 +456,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
       const float wgt = P.ops.weight[l];
       for (int head = 0; head < h; ++head, ++u) {
         const uint32_t buf = u & 1u, par = (u >> 1) & 1u;
-        ptx::mbar_wait(bar_tfull(buf, hf), par);
+        ptx::mbar_wait_hint(bar_tfull(buf, hf), par, 500u);
         ptx::tc_fence_after();
         FW_PROF(0)
         const uint32_t taddr = t_lane + buf * TC_BN + col0;
