@@ -134,17 +134,19 @@ def make_pool(cfg, rank: int) -> torch.Tensor:
     return torch.stack([ds[i]["img"] for i in range(len(ds))])
 
 
-def ncu_dram_bytes(profile: str, images: int):
-    """dram__bytes_read.sum + dram__bytes_write.sum of one launch from a committed `ncu --set full` summary under
-    profiles/ (captured at 8 images per launch; the traffic is proportional to the images).  None if absent."""
+def ncu_dram_bytes(profile: str, kernel: str, images: int):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of `kernel` from a committed `ncu --set full` summary
+    under profiles/ (captured at 8 images per launch; the traffic is proportional to the images).  None if absent."""
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", profile)
     if not os.path.exists(path):
         return None
     mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
-    total = 0.0
+    total, inside = 0.0, False
     for ln in open(path):
+        if ln.startswith("# kernel:"):
+            inside = kernel in ln
         for key in ("dram__bytes_read.sum = ", "dram__bytes_write.sum = "):
-            if ln.startswith(key):
+            if inside and ln.startswith(key):
                 val, unit = ln[len(key):].split()[:2]
                 total += float(val) * mult[unit]
     return total * images / 8.0 if total else None
@@ -311,20 +313,20 @@ def ours(args):
     flops_fwd = attn_algorithmic_flops(cfg["model"], cfg["T"], cfg["R"], len(cfg["layers"])) * imgs_per_call
     peak = peaks["bf16_tflops_sustained"]
 
-    def roof(symbol, label, flops_call, profile):
+    def roof(symbol, label, flops_call, kernel, profile="r1d_attn_tc_full.txt"):
         t = tm.get(symbol, {"calls": 0, "ms": 0.0})
         ach = flops_call * t["calls"] / (t["ms"] / 1e3) / 1e12 if t["ms"] > 0 else None
         return {"kernel": label, "bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
                 "frac": (ach / peak) if ach else None, "peak_source": f"{peaks['source']} bf16 dense, sustained",
-                "traffic": ncu_dram_bytes(profile, imgs_per_call), "traffic_source": f"profiles/{profile} (ncu --set full, "
+                "traffic": ncu_dram_bytes(profile, kernel, imgs_per_call), "traffic_source": f"profiles/{profile} (ncu --set full, "
                 "dram read+write of the main kernel at 8 images/launch, scaled to this launch's images)",
                 "ms_per_launch": t["ms"] / max(1, t["calls"]), "algorithmic_flops_per_launch": flops_call,
                 "ms_per_step": t["ms"] / args.steps}
 
     r_fwd = roof("skp_attn_map_fwd", "skp_attn_map_fwd (operand prep + attn_map_fwd_tc_kernel, bf16x3 on tcgen05)",
-                 flops_fwd, "r1c_fwd_tc_full.txt")
+                 flops_fwd, "attn_map_fwd_tc_kernel")
     r_bwd = roof("skp_attn_map_bwd", "skp_attn_map_bwd (attn_map_bwd_tc_kernel: recompute + dQ/dK on tcgen05, bicubic adjoint)",
-                 2.0 * flops_fwd, "r1c_bwd_tc_full.txt")
+                 2.0 * flops_fwd, "attn_map_bwd_tc_kernel")
     roofline, roofline_other = (r_bwd, r_fwd) if r_bwd["ms_per_step"] > r_fwd["ms_per_step"] else (r_fwd, r_bwd)
     total_kernel_ms = sum(v["ms"] for v in tm.values())
     kernels = {k: {"calls": v["calls"], "ms_per_step": v["ms"] / args.steps} for k, v in sorted(tm.items())}
