@@ -52,6 +52,10 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget-s", type=float, default=150.0, help="wall-clock cap for the CPU legs")
     ap.add_argument("--tiny", action="store_true", help="tiny model/config (harness smoke, not a bench number)")
+    ap.add_argument("--trunk-tf32", action="store_true",
+                    help="INFORMATIONAL, not the reference's precision: let the stock UNet/VAE Linear layers use TF32 tensor cores "
+                         "(torch.backends.cuda.matmul.allow_tf32).  The default keeps the reference's fp32 matmuls; a line produced "
+                         "with this flag says so in `dtype` and `config.trunk_precision`.")
     return ap.parse_args()
 
 
@@ -257,6 +261,7 @@ def ours(args):
     from stablekeypoints_b200 import distributed as D
     rank, local_rank, world = D.init_from_env("nccl")
     torch.cuda.set_device(local_rank)
+    torch.backends.cuda.matmul.allow_tf32 = bool(args.trunk_tf32)     # default False = the reference's fp32 Linear layers
     cfg = dict(WL, **(TINY if args.tiny else {}))
     dev, ldm, controllers, context = setup_ours(args, cfg, local_rank)
     pool_host = make_pool(cfg, rank).pin_memory()
@@ -333,7 +338,8 @@ def ours(args):
     line = {
         "metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32 (Q.K^T as bf16x3 on tcgen05 with fp32 accumulation; UNet trunk stock PyTorch fp32)",
+        "dtype": ("f32 (Q.K^T as bf16x3 on tcgen05 with fp32 accumulation; UNet trunk stock PyTorch fp32)" if not args.trunk_tf32 else
+                  "f32 kernels (Q.K^T as bf16x3 on tcgen05) + TF32 matmuls in the stock UNet trunk [reduced precision, informational run]"),
         "data": "synthetic", "impl": "ours",
         "config": {"workload": ("configs[1] celeba_wild-shaped token optimisation" if args.workload == "optimize"
                                 else "configs[2] extraction sweep (10 augmentations/image, argmax readout)"),
@@ -342,7 +348,8 @@ def ours(args):
                    "batch_size_per_gpu": cfg["batch_size"], "images_per_unet_pass": imgs_per_call,
                    "step": ("one optimiser step = 4 image-iterations per GPU (reference batch_size=4); value counts "
                             "batch-4 step equivalents over all GPUs" if args.workload == "optimize" else "one image"),
-                   "l2": "inputs larger than L2: each step streams >1 GB of activations", "tiny": bool(args.tiny)},
+                   "l2": "inputs larger than L2: each step streams >1 GB of activations", "tiny": bool(args.tiny),
+                   "trunk_precision": "tf32 matmuls (informational)" if args.trunk_tf32 else "fp32 matmuls, TF32 cuDNN convolutions (PyTorch / reference default)"},
         "e2e": {"value": e2e, "unit": unit, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms2 / args.steps},
         "gpu_launches": launches["k1"] - launches["k0"], "abi_calls": launches["c1"] - launches["c0"],
