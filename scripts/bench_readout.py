@@ -11,7 +11,7 @@ dev = "cuda:0"
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 peak = 6456.5
 try:
-    peak = float(json.load(open(os.path.join(root, "MEASURED_PEAKS.json")))["hbm_gbps"])
+    peak = float(json.load(open(os.path.join(root, "MEASURED_PEAKS.json")))["hbm_gbs"])
 except Exception:
     pass
 

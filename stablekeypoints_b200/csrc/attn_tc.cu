@@ -19,6 +19,8 @@
 //    exchanges (max, sum) with the other column half and the other CTAs of the cluster
 //    through (distributed) shared memory + mbarriers, then accumulates weight * P into 128
 //    fp32 registers.  The (h, R^2, T) probability tensor never exists; the output is written once.
+#include <cstdlib>
+
 #include "attn_tc.cuh"
 
 namespace skp {
@@ -313,17 +315,22 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
         for (int head = 0; head < h; ++head) {
           const int qz = b * h + head;
           const int kz = (P.ops.k_shared[l] ? 0 : b * h) + head;
+          // operand coordinates: (k offset, row, batch) of A and B.  Staged q' / k, or (lr) the interpolation table of
+          // this tile and the window of native-resolution logits it interpolates from
+          const bool lr = P.ops.lr != 0;
+          const int a_row = lr ? 0 : p0, a_z = lr ? tile : qz, b_z = lr ? qz : kz;
+          const int b_k0 = lr ? lr_window_row0(tile, P.ops.win_s[l], P.ops.R, P.ops.win_nr[l]) * P.ops.win_s[l] : 0;
           for (int kb = 0; kb < nkb; ++kb, ++it) {
             const int s = it % SM::kStages;
             const uint32_t ph = (it / SM::kStages) & 1u;
             ptx::mbar_wait_hint(bar_empty(s), ph ^ 1u, 2000u);
             ptx::mbar_arrive_expect_tx(bar_full(s), SM::kStageBytes);
             const uint32_t st = base + s * SM::kStageBytes;
-            ptx::tma_load_3d(st, &P.ops.q_map[l][0], bar_full(s), kb * TC_BK, p0, qz);
-            ptx::tma_load_3d(st + TC_A_BYTES, &P.ops.k_map[l][0], bar_full(s), kb * TC_BK, tok0, kz);
+            ptx::tma_load_3d(st, &P.ops.q_map[l][0], bar_full(s), kb * TC_BK, a_row, a_z);
+            ptx::tma_load_3d(st + TC_A_BYTES, &P.ops.k_map[l][0], bar_full(s), b_k0 + kb * TC_BK, tok0, b_z);
             if (NPROD == 3) {
-              ptx::tma_load_3d(st + TC_A_BYTES + TC_B_BYTES, &P.ops.q_map[l][1], bar_full(s), kb * TC_BK, p0, qz);
-              ptx::tma_load_3d(st + 2 * TC_A_BYTES + TC_B_BYTES, &P.ops.k_map[l][1], bar_full(s), kb * TC_BK, tok0, kz);
+              ptx::tma_load_3d(st + TC_A_BYTES + TC_B_BYTES, &P.ops.q_map[l][1], bar_full(s), kb * TC_BK, a_row, a_z);
+              ptx::tma_load_3d(st + 2 * TC_A_BYTES + TC_B_BYTES, &P.ops.k_map[l][1], bar_full(s), b_k0 + kb * TC_BK, tok0, b_z);
             }
           }
         }
@@ -643,6 +650,10 @@ size_t attn_map_tc_workspace(const skp_attn_layer* h_layers, int n_layers, int B
     total += nbuf * tc_align_up(static_cast<size_t>(B) * R * R * a.C * 2, 1024);
     total += nbuf * tc_align_up(static_cast<size_t>(a.k_shared ? 1 : B) * T * a.C * 2, 1024);
   }
+  if (nbuf == 2 && attn_map_lr_supported(h_layers, n_layers, B, T, R, 0)) {
+    const size_t lr = attn_map_lr_workspace(h_layers, n_layers, B, T, R);
+    total = total > lr ? total : lr;
+  }
   return total + 1024;
 }
 
@@ -735,7 +746,12 @@ int attn_map_fwd_tc(const skp_attn_layer* h_layers, int n_layers, int B, int T, 
   const int R2 = R * R;
   TcParams P;
   memset(&P, 0, sizeof(P));
-  int rc = tc_prepare(h_layers, n_layers, B, T, R, x3, workspace, st, &P.ops, nullptr);
+  // parity mode on shapes whose interpolation windows are narrow: upsample after the logits (attn_tc_lr.cu), no
+  // staged q'.  SKP_FWD_LR=0 keeps the staged-operand path (A/B measurements, cross-checks).
+  static const bool lr_enabled = !(getenv("SKP_FWD_LR") && atoi(getenv("SKP_FWD_LR")) == 0);
+  const bool lr = x3 && lr_enabled && attn_map_lr_supported(h_layers, n_layers, B, T, R, token_idx ? n_idx : 0);
+  int rc = lr ? tc_prepare_lr(h_layers, n_layers, B, T, R, workspace, st, &P.ops, nullptr)
+              : tc_prepare(h_layers, n_layers, B, T, R, x3, workspace, st, &P.ops, nullptr);
   if (rc != SKP_OK) return rc;
   P.T = T; P.R2 = R2;
   P.n_idx = token_idx ? n_idx : 0;

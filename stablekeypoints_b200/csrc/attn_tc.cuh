@@ -29,7 +29,29 @@ struct TcOperands {
   float weight[TC_MAX_LAYERS];           // layer weight / heads
   float scale[TC_MAX_LAYERS];
   int n_layers, total_heads;
+  // "upsample after the logits" mode (attn_tc_lr.cu): q_map = interpolation tables W [tile][128 px][d[l] taps],
+  // k_map = native-resolution logits s_low [b*h + head][token][s*s]; the B tile of (tile, kb) starts at source pixel
+  // lr_window_row0(tile) * s + 64 kb
+  int lr, R;
+  int win_s[TC_MAX_LAYERS], win_nr[TC_MAX_LAYERS];
 };
+
+// window of source rows [r0, r0 + nr) a 128-pixel tile of the R x R output interpolates from (s x s source)
+struct LrGeom {
+  int nr, kw;   // rows in the window; taps per tile = nr * s rounded up to a multiple of 64
+};
+__device__ __host__ __forceinline__ int lr_window_row0(int tile, int s, int R, int nr) {
+  int ia;
+  float w[4];
+  bicubic_coeffs(tile * TC_BM / R, static_cast<float>(s) / R, &ia, w);
+  const int lo = ia - 1 > 0 ? ia - 1 : 0;
+  return lo < s - nr ? lo : s - nr;
+}
+LrGeom lr_geometry(int s, int R);
+bool attn_map_lr_supported(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int n_idx);
+size_t attn_map_lr_workspace(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R);
+int tc_prepare_lr(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, void* workspace, cudaStream_t st,
+                  TcOperands* out, char** ws_end);
 
 bool attn_map_tc_supported(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int n_idx);
 size_t attn_map_tc_workspace(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int precision);

@@ -265,6 +265,135 @@ __global__ void plane_stats_kernel(const float* __restrict__ maps, int H, int W,
   if (threadIdx.x == 0) kl_out[blockIdx.x] = static_cast<float>((A - Bv) / z - log(z) + log(s0));
 }
 
+// Register-resident single-subject version for planes of exactly 512 * 4 * VPT pixels (64^2, 128^2, ...): every thread
+// loads its VPT 16-byte vectors ONCE (all loads in flight before the first use: the plane crosses HBM once), takes the
+// argmax and the softmax sums from registers (fp32 inside a thread, fp64 across threads), and all sums share one block
+// reduction.  The Gaussian target only needs evaluating near the argmax: once exp(-d^2 / 2 sigma^2) < eps * 2^-25 the
+// fp32 sum g + eps rounds to eps exactly, so everything outside a small window contributes closed-form terms.
+constexpr int PS_THREADS = 512;
+__device__ __forceinline__ float ps_ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+template <int VPT, bool KL>
+__global__ void __launch_bounds__(PS_THREADS, 2)
+plane_stats_reg_kernel(const float* __restrict__ maps, int W, float sigma, float eps, float* kl_out, float* ent_out,
+                       int64_t* argmax_out) {
+  __shared__ unsigned long long scratch[32];
+  __shared__ double dsum[6][PS_THREADS / 32];
+  constexpr int n = PS_THREADS * 4 * VPT;
+  const float4* p4 = reinterpret_cast<const float4*>(maps + static_cast<int64_t>(blockIdx.x) * n);
+  float4 x[VPT];
+#pragma unroll
+  for (int k = 0; k < VPT; ++k) x[k] = __ldg(p4 + threadIdx.x + k * PS_THREADS);
+  // per-thread argmax on plain float compares (elements are visited in increasing flat index, so a strict '>' keeps
+  // the first maximum; a NaN beats everything that is not already a NaN), one 64-bit key per thread for the block
+  float bv = x[0].x;
+  uint32_t bi = static_cast<uint32_t>(threadIdx.x) << 2;
+#pragma unroll
+  for (int k = 0; k < VPT; ++k) {
+    const uint32_t b = static_cast<uint32_t>(threadIdx.x + k * PS_THREADS) << 2;
+    const float xv[4] = {x[k].x, x[k].y, x[k].z, x[k].w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const bool upd = (xv[j] > bv) || (xv[j] != xv[j] && bv == bv);
+      bv = upd ? xv[j] : bv;
+      bi = upd ? b + j : bi;
+    }
+  }
+  unsigned long long best = argmax_key(bv, bi);
+  best = block_max_u64(best, scratch);
+  const uint32_t idx = argmax_key_index(best);
+  if (argmax_out && threadIdx.x == 0) argmax_out[blockIdx.x] = idx;
+  if (!KL && !ent_out) return;
+  const float mx = argmax_key_value(best);
+  const int lgw = __ffs(W) - 1;             // W is a power of two on this path
+  const int H = n >> lgw;
+  // centre in pixel units exactly as the reference forms it: ((k + 0.5) / H) * size with size == H
+  const float cr = __fmul_rn(__fdiv_rn(static_cast<float>(idx >> lgw) + 0.5f, static_cast<float>(H)), static_cast<float>(H));
+  const float cc = __fmul_rn(__fdiv_rn(static_cast<float>(idx & (W - 1)) + 0.5f, static_cast<float>(H)), static_cast<float>(H));
+  const float inv2s2 = 1.0f / (2.0f * sigma * sigma);
+  // all pixels: s0 = sum e^v, s1 = sum e^v v, sv = sum v (v = x - max).  fp32 inside a thread (32 * VPT/8 terms), fp64 across
+  float s0f = 0.0f, s1f = 0.0f, svf = 0.0f;
+#pragma unroll
+  for (int k = 0; k < VPT; ++k) {
+    const float xv[4] = {x[k].x, x[k].y, x[k].z, x[k].w};
+    float v[4], e[4], ev[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      v[j] = xv[j] - mx;
+      // exp(v) as ex2 of a two-term product v * log2(e) (hi + lo): the argument carries ~2^-30 relative error,
+      // the result the 2 ulp of ex2.approx -- the same class as expf at a third of the instructions
+      e[j] = ps_ex2(fmaf(v[j], 1.925963033500011e-8f, v[j] * 1.4426950216293335f));
+      ev[j] = e[j] * v[j];
+    }
+    s0f += (e[0] + e[1]) + (e[2] + e[3]);
+    s1f += (ev[0] + ev[1]) + (ev[2] + ev[3]);
+    if (KL) svf += (v[0] + v[1]) + (v[2] + v[3]);
+  }
+  double s0 = static_cast<double>(s0f), s1 = static_cast<double>(s1f), sv = static_cast<double>(svf);
+  // KL: with a = gaussian + eps,  z = sum a,  A = sum a log a,  Bv = sum a v.  Outside a square of half-width `rad`
+  // around the argmax a == eps exactly, so those pixels contribute eps * (count), eps log eps * (count) and eps * sum v;
+  // the <= (2 rad + 3)^2 window pixels are re-read (L1-resident: this CTA just loaded them) and get the full expf / logf.
+  double z = 0.0, A = 0.0, Bv = 0.0;
+  if (KL) {
+    const float far_thr = eps > 0.0f ? -logf(eps) + 17.6f : 1e30f;     // exp(-far_thr) < eps * 2^-25
+    const int rad = static_cast<int>(fminf(ceilf(sqrtf(far_thr / inv2s2)), 65536.0f)) + 1;   // +1: the centre is (k + 0.5) up to rounding
+    const int r_c = static_cast<int>(idx >> lgw), c_c = static_cast<int>(idx & (W - 1));
+    const int rlo = max(0, r_c - rad), rhi = min(H - 1, r_c + rad), clo = max(0, c_c - rad), chi = min(W - 1, c_c + rad);
+    const int bw = chi - clo + 1, bn = (rhi - rlo + 1) * bw;
+    const float* pl = maps + static_cast<int64_t>(blockIdx.x) * n;
+    for (int i = threadIdx.x; i < bn; i += PS_THREADS) {
+      const int r = rlo + i / bw, c = clo + i % bw;
+      const float v = __ldg(pl + (r << lgw) + c) - mx;
+      const float dr = (static_cast<float>(r) + 0.5f) - cr, dc = (static_cast<float>(c) + 0.5f) - cc;
+      const float a = expf(-(dc * dc + dr * dr) * inv2s2) + eps;       // g * (1 / num_subjects) with one subject
+      z += static_cast<double>(a);
+      A += static_cast<double>(a * logf(a));
+      Bv += static_cast<double>(a * v) - static_cast<double>(eps) * static_cast<double>(v);
+    }
+    if (threadIdx.x == 0) {
+      const double nfar = static_cast<double>(n - bn);
+      z += nfar * static_cast<double>(eps);
+      A += nfar * static_cast<double>(eps * logf(eps));
+    }
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  s0 = warp_sum(s0);
+  s1 = warp_sum(s1);
+  if (KL) {
+    sv = warp_sum(sv);
+    z = warp_sum(z);
+    A = warp_sum(A);
+    Bv = warp_sum(Bv);
+  }
+  if (lane == 0) {
+    dsum[0][warp] = s0; dsum[1][warp] = s1;
+    if (KL) { dsum[2][warp] = z; dsum[3][warp] = A; dsum[4][warp] = Bv; dsum[5][warp] = sv; }
+  }
+  __syncthreads();
+  if (warp == 0) {
+    double r[6];
+#pragma unroll
+    for (int q = 0; q < (KL ? 6 : 2); ++q) r[q] = warp_sum(lane < PS_THREADS / 32 ? dsum[q][lane] : 0.0);
+    if (lane == 0) {
+      if (ent_out) ent_out[blockIdx.x] = static_cast<float>(log(r[0]) - r[1] / r[0]);
+      if (KL) {
+        const double bv = r[4] + static_cast<double>(eps) * r[5];       // sum a v over the whole plane
+        kl_out[blockIdx.x] = static_cast<float>((r[3] - bv) / r[2] - log(r[2]) + log(r[0]));
+      }
+    }
+  }
+}
+
+template <int VPT>
+static void launch_plane_stats_reg(const float* maps, int N, int W, float sigma, float eps, float* kl, float* ent,
+                                   int64_t* am, cudaStream_t st) {
+  if (kl) plane_stats_reg_kernel<VPT, true><<<(::skp::note_launch(), N), PS_THREADS, 0, st>>>(maps, W, sigma, eps, kl, ent, am);
+  else plane_stats_reg_kernel<VPT, false><<<(::skp::note_launch(), N), PS_THREADS, 0, st>>>(maps, W, sigma, eps, kl, ent, am);
+}
+
 __global__ void gaussian_circles_kernel(const float* __restrict__ pos, int S, int N, int size, float sigma, float* out) {
   const int n = blockIdx.y;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -544,6 +673,22 @@ extern "C" int skp_plane_stats(const float* maps, int N, int H, int W, float sig
                                float* kl, float* entropy, int64_t* argmax_out, void* stream) {
   SKP_REQUIRE(maps && N > 0 && H > 0 && W > 0 && num_subjects >= 1 && num_subjects <= 8, "skp_plane_stats: bad arguments");
   SKP_REQUIRE(kl || entropy || argmax_out, "skp_plane_stats: no output requested");
+  const int64_t n = static_cast<int64_t>(H) * W;
+  if (num_subjects == 1 && (W & (W - 1)) == 0 && (reinterpret_cast<uintptr_t>(maps) & 15) == 0) {
+    cudaStream_t st = as_stream(stream);
+    bool done = true;
+    switch (n) {
+      case PS_THREADS * 4 * 1: launch_plane_stats_reg<1>(maps, N, W, sigma, epsilon, kl, entropy, argmax_out, st); break;
+      case PS_THREADS * 4 * 2: launch_plane_stats_reg<2>(maps, N, W, sigma, epsilon, kl, entropy, argmax_out, st); break;
+      case PS_THREADS * 4 * 4: launch_plane_stats_reg<4>(maps, N, W, sigma, epsilon, kl, entropy, argmax_out, st); break;
+      case PS_THREADS * 4 * 8: launch_plane_stats_reg<8>(maps, N, W, sigma, epsilon, kl, entropy, argmax_out, st); break;
+      default: done = false;
+    }
+    if (done) {
+      SKP_LAUNCH_CHECK();
+      return SKP_OK;
+    }
+  }
   plane_stats_kernel<<<(::skp::note_launch(), N), 512, 0, as_stream(stream)>>>(maps, H, W, sigma, epsilon, num_subjects, kl, entropy, argmax_out);
   SKP_LAUNCH_CHECK();
   return SKP_OK;

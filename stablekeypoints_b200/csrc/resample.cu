@@ -34,6 +34,28 @@ __global__ void __launch_bounds__(256) bilinear_upsample_vec4_kernel(const float
   const float* p = in + static_cast<int64_t>(n) * h * w;
   float4* o = reinterpret_cast<float4*>(out + (static_cast<int64_t>(n) * H + ybase) * W);
   const float ry = static_cast<float>(h) / H, rx = static_cast<float>(w) / W;
+  if (blockDim.x % w4 == 0) {
+    // every thread keeps one column group for all its rows: the x taps / weights are computed once
+    const int x4 = threadIdx.x % w4, ystep = blockDim.x / w4;
+    int x0[4], x1[4];
+    float lx[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) bilinear_coeffs(4 * x4 + j, rx, w, &x0[j], &x1[j], &lx[j]);
+    for (int yy = threadIdx.x / w4; yy < rows; yy += ystep) {
+      int y0, y1;
+      float ly;
+      bilinear_coeffs(ybase + yy, ry, h, &y0, &y1, &ly);
+      const float* r0 = p + y0 * w;
+      const float* r1 = p + y1 * w;
+      float v[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        v[j] = (1.0f - ly) * ((1.0f - lx[j]) * __ldg(r0 + x0[j]) + lx[j] * __ldg(r0 + x1[j])) +
+               ly * ((1.0f - lx[j]) * __ldg(r1 + x0[j]) + lx[j] * __ldg(r1 + x1[j]));
+      o[yy * w4 + x4] = make_float4(v[0], v[1], v[2], v[3]);
+    }
+    return;
+  }
   for (int i = threadIdx.x; i < rows * w4; i += blockDim.x) {
     const int yy = i / w4, x4 = i - yy * w4;
     int y0, y1;

@@ -165,6 +165,27 @@ def test_readout_and_selection_golden(ops):
     assert np.array_equal(got.cpu().numpy(), d["ref_fps48"])
 
 
+def test_plane_stats_register_path_matches_oracle_and_two_pass_kernel(ops):
+    """Planes of 512*4*VPT pixels with one subject take the register-resident single-pass kernel; the same data at a
+    16-byte-misaligned address takes the two-pass kernel.  Both against the fp64 oracle (ptp_utils.py:86-112, 165-187)."""
+    g = torch.Generator().manual_seed(5)
+    for hw in (32, 64, 128):        # 64x32 (VPT 1), 64^2 (VPT 2), 128^2 (VPT 8)
+        h, w = (64, 32) if hw == 32 else (hw, hw)
+        m = torch.rand(12, h, w, generator=g) * 4.0
+        m[3, h - 1, w - 1] = 9.0      # peak in a corner: Gaussian window clipped by the border
+        m[4, 0, 0] = 9.0
+        kl64 = O.gaussian_kl(m, 2.0, 1e-5, 1, dtype=torch.float64) if h == w else None
+        ent64 = O.pixel_entropy(m, dtype=torch.float64)
+        flat = torch.empty(m.numel() + 1, device=DEV)
+        flat[1:] = _cu(m).reshape(-1)
+        for name, mm in (("register", _cu(m)), ("two-pass", flat[1:].view(12, h, w))):
+            kl, ent, am = ops.plane_stats(mm, sigma=2.0, epsilon=1e-5, want_kl=h == w, want_entropy=True, want_argmax=True)
+            assert torch.equal(am.cpu(), torch.argmax(m.reshape(12, -1), -1)), name
+            assert torch.allclose(ent.cpu().double(), ent64, rtol=1e-6), name
+            if kl64 is not None:
+                assert torch.allclose(kl.cpu().double(), kl64, rtol=1e-4), name
+
+
 def test_readout_edge_cases(ops):
     t = torch.zeros(3, 16, 16)
     t[0, 3, 4] = 1; t[0, 5, 1] = 1            # tie: first flat index wins
