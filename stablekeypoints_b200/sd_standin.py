@@ -59,9 +59,11 @@ class CrossAttention(nn.Module):
         b, n, _ = x.shape
         h = self.heads
         ctx = x if context is None else context
+        if context is not None and b > 1 and context.stride(0) == 0:
+            ctx = context[:1]       # context.expand(B, -1, -1) (`ptp_utils.py:229`): project the one context once
         q = self.to_q(x).view(b, n, h, -1).transpose(1, 2)
-        k = self.to_k(ctx).view(ctx.shape[0], ctx.shape[1], h, -1).transpose(1, 2)
-        v = self.to_v(ctx).view(ctx.shape[0], ctx.shape[1], h, -1).transpose(1, 2)
+        k = self.to_k(ctx).view(ctx.shape[0], ctx.shape[1], h, -1).transpose(1, 2).expand(b, -1, -1, -1)
+        v = self.to_v(ctx).view(ctx.shape[0], ctx.shape[1], h, -1).transpose(1, 2).expand(b, -1, -1, -1)
         out = F.scaled_dot_product_attention(q, k, v, scale=self.scale)
         return self.to_out[0](out.transpose(1, 2).reshape(b, n, -1))
 
