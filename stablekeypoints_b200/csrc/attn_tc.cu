@@ -748,7 +748,8 @@ int attn_map_fwd_tc(const skp_attn_layer* h_layers, int n_layers, int B, int T, 
   memset(&P, 0, sizeof(P));
   // parity mode on shapes whose interpolation windows are narrow: upsample after the logits (attn_tc_lr.cu), no
   // staged q'.  SKP_FWD_LR=0 keeps the staged-operand path (A/B measurements, cross-checks).
-  static const bool lr_enabled = !(getenv("SKP_FWD_LR") && atoi(getenv("SKP_FWD_LR")) == 0);
+  const char* lr_env = getenv("SKP_FWD_LR");     // read per call: the tests switch it to cover both paths
+  const bool lr_enabled = !(lr_env && atoi(lr_env) == 0);
   const bool lr = x3 && lr_enabled && attn_map_lr_supported(h_layers, n_layers, B, T, R, token_idx ? n_idx : 0);
   int rc = lr ? tc_prepare_lr(h_layers, n_layers, B, T, R, workspace, st, &P.ops, nullptr)
               : tc_prepare(h_layers, n_layers, B, T, R, x3, workspace, st, &P.ops, nullptr);

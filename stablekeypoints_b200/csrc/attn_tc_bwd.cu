@@ -25,7 +25,7 @@ namespace skp {
 constexpr int BW_SEL = 16;            // selected tokens per launch (UMMA N of the S_sel product)
 constexpr int BW_KSEL_BYTES = BW_SEL * 128;   // 16 rows x 128 B
 constexpr int BW_DS_BYTES = TC_BM * TC_BN * 2;   // 64 KB: dS tile, 4 slabs of [128 px][64 tok] bf16
-constexpr int BW_WXT_FLOATS = 8 * 256;        // x-adjoint table: s rows of 5 R/s taps padded to a multiple of 4 (<= 8 R/s... R <= 256)
+constexpr int BW_WXT_FLOATS = 16 * 256;       // x-adjoint table (s rows of 5 R/s taps padded to a multiple of 4, <= 8 KB), or (LR) the 16 KB W tile
 constexpr float kLog2eBw = 1.4426950408889634f;
 constexpr int BW_STG_LD = 68;          // fp32 staging row pitch (64 + 4): conflict-free float4 stores with lane = row
 
@@ -35,6 +35,13 @@ struct BwdParams {
   float* dq[TC_MAX_LAYERS];                 // (B, s*s, C), accumulated into
   float* dk[TC_MAX_LAYERS];                 // (Bk, T, C), accumulated into
   int s[TC_MAX_LAYERS], C[TC_MAX_LAYERS];
+  // "upsample after the logits" launches (template LR): interpolation tables W hi [tile][128 px][64 taps] and the fp32
+  // accumulator of the native-resolution logit gradient dz[b*h + head][token][s*s] of every layer
+  CUtensorMap w_map[TC_MAX_LAYERS];
+  float* dz[TC_MAX_LAYERS];
+  int wnr[TC_MAX_LAYERS];                   // source rows per window (LrGeom::nr)
+  int ghead[TC_MAX_LAYERS];                 // first head of the layer among ALL captured layers (row_stats index)
+  int heads_all;                            // heads of all captured layers (row_stats stride)
   int B, T, R, R2, n_idx, tiles, n_units, n_chunks;
   int64_t idx_stride;
   const int64_t* token_idx;
@@ -73,7 +80,7 @@ struct BwSmem {
   static constexpr int kKselBytes = (NPROD == 3 ? 2 : 1) * BW_KSEL_BYTES;
   static constexpr int kDsOff = kKselOff + kKselBytes;              // dS tile; aliased by the fp32 dQ' staging
   static constexpr int kWxtOff = kDsOff + BW_DS_BYTES;
-  static constexpr int kBarOff = kWxtOff + BW_WXT_FLOATS * 4;       // q_full[2], q_empty[2], s_full, ds_full, mma_done
+  static constexpr int kBarOff = kWxtOff + BW_WXT_FLOATS * 4;       // q_full[2], q_empty[2], s_full, ds_full, mma_done, w_full
   static constexpr int kTmemPtrOff = kBarOff + 8 * 8;
   static constexpr int kTokOff = kTmemPtrOff + 8;                   // int tok[16]
   static constexpr int kTotal = kTokOff + 4 * BW_SEL;
@@ -139,15 +146,24 @@ __device__ __forceinline__ BwUnit bw_next(const BwdParams& P, BwUnit x) {
   }
   return x;
 }
-// same predicate as bw_flush_after, from the current and the next tuple
+// same predicate as bw_flush_after, from the current and the next tuple.  LR: the accumulator holds the logit gradient
+// of one window of source rows of one (image, head): flush when the next tile interpolates from another window.
+template <bool LR>
 __device__ __forceinline__ bool bw_flush_between(const BwdParams& P, const BwUnit& x, const BwUnit& nx, bool last) {
+  if (LR)
+    return last || nx.hg != x.hg || nx.b != x.b ||
+           lr_window_row0(nx.tile, P.s[x.l], P.R, P.wnr[x.l]) != lr_window_row0(x.tile, P.s[x.l], P.R, P.wnr[x.l]);
   return last || nx.hg != x.hg || (!P.ops.k_shared[x.l] && nx.b != x.b);
 }
 
 // 12 warps = 3 warpgroups: {TMA, MMA, 2 idle} shrink to 56 registers, the 8 softmax warps grow to 224
 constexpr int BW_THREADS = 384;
 constexpr int BW_SOFTMAX_WARP0 = 4;
-template <int NPROD, int NH>
+// LR: "upsample after the logits" gradient.  The dQ' / dK products and the bicubic adjoint are replaced by ONE product
+// dz += dS^T W (tokens x 64 taps, K = 128 pixels; same operand forms as the dK product with the W tile of this pixel
+// tile in place of Q'), accumulated in TMEM over the tiles that share a window of source rows and flushed with vector
+// reductions into dz[b*h + head][token][window]; attn_tc_bwd_lr.cu turns dz into dq / dk at native resolution.
+template <int NPROD, int NH, bool LR>
 __global__ void __launch_bounds__(BW_THREADS, 1)
 attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
   using SM = BwSmem<NPROD>;
@@ -169,6 +185,8 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
   const uint32_t bar_sfull = base + SM::kBarOff + 8u * 4;
   const uint32_t bar_dsfull = base + SM::kBarOff + 8u * 5;
   const uint32_t bar_mmadone = base + SM::kBarOff + 8u * 6;
+  const uint32_t bar_wfull = base + SM::kBarOff + 8u * 7;
+  const uint32_t wtile = base + SM::kWxtOff;
   volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(base_ptr + SM::kTmemPtrOff);
   volatile int* tok_s = reinterpret_cast<volatile int*>(base_ptr + SM::kTokOff);
   float* wxt = reinterpret_cast<float*>(base_ptr + SM::kWxtOff);
@@ -182,6 +200,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
     ptx::mbar_init(bar_sfull, 1);
     ptx::mbar_init(bar_dsfull, TC_SOFTMAX_THREADS);
     ptx::mbar_init(bar_mmadone, 1);
+    ptx::mbar_init(bar_wfull, 1);
     ptx::fence_barrier_init();
   }
   if (warp == 1) {
@@ -223,6 +242,12 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         if (need_ksel) {
           ptx::tma_load_3d(base + SM::kKselOff, &P.ksel_map[x.l][0], bar_qfull(st), 0, 0, qz);
           if (NPROD == 3) ptx::tma_load_3d(base + SM::kKselOff + BW_KSEL_BYTES, &P.ksel_map[x.l][1], bar_qfull(st), 0, 0, qz);
+        }
+        if (LR) {
+          // single W buffer: the dz product of the previous unit must have retired before it is overwritten
+          if (it > 0) ptx::mbar_wait(bar_qempty((it - 1) & 1), ((it - 1) >> 1) & 1u);
+          ptx::mbar_arrive_expect_tx(bar_wfull, TC_A_BYTES);
+          ptx::tma_load_3d(wtile, &P.w_map[x.l], bar_wfull, 0, 0, x.tile);
         }
         prev_hg = x.hg;
         prev_b = x.b;
@@ -275,22 +300,33 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         ptx::tc_fence_after();
         pf_ds += clock64() - c0;
         c0 = clock64();
-        // dQ' (128 px x d) = dS (K-major A, K = 256 tokens) * K_hi (MN-major B: rows = tokens)
-        const uint32_t id_dq = bw_idesc(TC_BM, d, 0, 1);
-        const int nkt = (ntok + 15) / 16;
-        for (int k = 0; k < nkt; ++k)
-          ptx::umma_bf16(tm_dQ, bw_desc(dsb + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024), bw_desc(ks + k * 2048, 16384, 1024),
-                         id_dq, k != 0);
-        // dK (128 tok x d per half) += dS^T (MN-major A: rows = pixels) * Q'_hi (MN-major B: rows = pixels)
-        const uint32_t id_dk = bw_idesc(128, d, 1, 1);
-        for (int mh = 0; mh < n_mh; ++mh)
-          for (int k = 0; k < TC_BM / 16; ++k)
-            ptx::umma_bf16(tm_dK + mh * 64, bw_desc(dsb + mh * 2 * 16384 + k * 2048, 16384, 1024),
-                           bw_desc(qs + k * 2048, 16384, 1024), id_dk, (dk_fresh && k == 0) ? 0u : 1u);
+        if (!LR) {
+          // dQ' (128 px x d) = dS (K-major A, K = 256 tokens) * K_hi (MN-major B: rows = tokens)
+          const uint32_t id_dq = bw_idesc(TC_BM, d, 0, 1);
+          const int nkt = (ntok + 15) / 16;
+          for (int k = 0; k < nkt; ++k)
+            ptx::umma_bf16(tm_dQ, bw_desc(dsb + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024), bw_desc(ks + k * 2048, 16384, 1024),
+                           id_dq, k != 0);
+          // dK (128 tok x d per half) += dS^T (MN-major A: rows = pixels) * Q'_hi (MN-major B: rows = pixels)
+          const uint32_t id_dk = bw_idesc(128, d, 1, 1);
+          for (int mh = 0; mh < n_mh; ++mh)
+            for (int k = 0; k < TC_BM / 16; ++k)
+              ptx::umma_bf16(tm_dK + mh * 64, bw_desc(dsb + mh * 2 * 16384 + k * 2048, 16384, 1024),
+                             bw_desc(qs + k * 2048, 16384, 1024), id_dk, (dk_fresh && k == 0) ? 0u : 1u);
+        } else {
+          // dz (128 tok x 64 taps per half) += dS^T (MN-major A: rows = pixels) * W_hi (MN-major B: rows = pixels)
+          ptx::mbar_wait(bar_wfull, it & 1u);
+          ptx::tc_fence_after();
+          const uint32_t id_dz = bw_idesc(128, TC_BK, 1, 1);
+          for (int mh = 0; mh < n_mh; ++mh)
+            for (int k = 0; k < TC_BM / 16; ++k)
+              ptx::umma_bf16(tm_dK + mh * 64, bw_desc(dsb + mh * 2 * 16384 + k * 2048, 16384, 1024),
+                             bw_desc(wtile + k * 2048, 16384, 1024), id_dz, (dk_fresh && k == 0) ? 0u : 1u);
+        }
         ptx::umma_commit(bar_mmadone);
         ptx::umma_commit(bar_qempty(st));
         pf_id += clock64() - c0;
-        dk_fresh = bw_flush_between(P, x, nxu, u + 1 >= u_end);
+        dk_fresh = bw_flush_between<LR>(P, x, nxu, u + 1 >= u_end);
         x = nxu;
       }
       if (P.prof && blockIdx.x == 0) {
@@ -317,7 +353,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
     float nx_dp[BW_SEL];
     auto load_row = [&](const BwUnit& y, float2& ml, float (&dpr)[BW_SEL]) {
       const int pp = y.tile * TC_BM + row;
-      ml = __ldg(reinterpret_cast<const float2*>(P.row_stats) + (static_cast<int64_t>(y.b) * P.ops.total_heads + y.hg) * P.R2 + pp);
+      ml = __ldg(reinterpret_cast<const float2*>(P.row_stats) + (static_cast<int64_t>(y.b) * P.heads_all + P.ghead[y.l] + y.head) * P.R2 + pp);
 #pragma unroll
       for (int j = 0; j < BW_SEL; ++j)
         dpr[j] = j < P.n_idx ? __ldg(P.dmaps_sel + (static_cast<int64_t>(y.b) * P.n_idx + j) * P.R2 + pp) : 0.0f;
@@ -332,7 +368,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       const float wgt = P.ops.weight[x.l], scale = P.ops.scale[x.l];
       if (x.l != prev_l || x.b != prev_b) {
         named_bar_sync(1, TC_SOFTMAX_THREADS);
-        if (x.l != prev_l) {
+        if (!LR && x.l != prev_l) {
           const float ratio = static_cast<float>(s) / R;
           for (int e = stid; e < s * njp; e += TC_SOFTMAX_THREADS) {
             const int sx = e / njp, jj = e % njp, xx = max(0, (sx - 2) * up) + jj;
@@ -434,7 +470,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       ptx::tc_fence_after();
       pf[3] += clock64() - c1;
       c1 = clock64();
-      if (ch * 32 < d && !(P.dbg & 4)) {
+      if (!LR && ch * 32 < d && !(P.dbg & 4)) {
         uint32_t v[32];
         ptx::tmem_ld32(tm_dQ + lane_off + ch * 32, v);
         ptx::tmem_ld_wait();
@@ -446,6 +482,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
                           __uint_as_float(v[4 * q + 2]) * scale, __uint_as_float(v[4 * q + 3]) * scale);
         }
       }
+      if (!LR) {
       ptx::tc_fence_before();
       named_bar_sync(2, TC_SOFTMAX_THREADS);
       // ---- adjoint of the bicubic upsample: x-gather from staging, y taps as vector reductions
@@ -521,10 +558,35 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         }
       }
       named_bar_sync(2, TC_SOFTMAX_THREADS);
+      }
       pf[4] += clock64() - c1;
       c_end = clock64();
+      if (LR) {
+        // ---- dz: flush the window accumulator (token rows x 64 taps) when the next tile leaves this window
+        if (bw_flush_between<true>(P, x, nxu, u + 1 >= u_end) && ch < n_mh) {
+          const int t = tok0 + ch * 128 + row;
+          const int h = P.ops.heads[x.l];
+          const int r0 = lr_window_row0(x.tile, s, R, P.wnr[x.l]);
+          const int nvalid = min(TC_BK, s * s - r0 * s);      // taps of the window inside the source image
+          float* dz = P.dz[x.l] + ((static_cast<int64_t>(x.b) * h + x.head) * P.T + t) * (s * s) + r0 * s;
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            uint32_t v[32];
+            ptx::tmem_ld32(tm_dK + lane_off + ch * 64 + c * 32, v);
+            ptx::tmem_ld_wait();
+            if (t < P.T && !(P.dbg & 1)) {
+#pragma unroll
+              for (int q = 0; q < 8; ++q)
+                if (c * 32 + q * 4 < nvalid)
+                  red_add_v4(dz + c * 32 + q * 4, __uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]),
+                             __uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3]));
+            }
+          }
+          ptx::tc_fence_before();
+        }
+      } else
       // ---- dK: flush the TMEM accumulator when this head (or image, for a per-image k) is finished
-      if (bw_flush_between(P, x, nxu, u + 1 >= u_end) && ch < n_mh) {
+      if (bw_flush_between<false>(P, x, nxu, u + 1 >= u_end) && ch < n_mh) {
         const int t = tok0 + ch * 128 + row;
         float* dk = P.dk[x.l] + (static_cast<int64_t>(P.ops.k_shared[x.l] ? 0 : x.b) * P.T + t) * C + x.head * d;
         const float inv = 1.0f / kLog2eBw;
@@ -566,6 +628,11 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
 // ==========================================================================================
 // host side
 // ==========================================================================================
+// attn_tc_bwd_lr.cu / attn_tc_lr.cu
+size_t lr_bwd_post_workspace(const skp_attn_layer& a, int B, int T);
+int lr_bwd_post(const skp_attn_layer& a, int B, int T, const float* dz, char* ws, cudaStream_t st);
+int lr_launch_weights(int s, int R, const LrGeom& g, __nv_bfloat16* hi, __nv_bfloat16* lo, cudaStream_t st);
+
 bool attn_map_bwd_tc_supported(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int n_idx) {
   if (!attn_map_tc_supported(h_layers, n_layers, B, T, R, n_idx)) return false;
   if (n_idx < 1 || n_idx > BW_SEL || R > 256) return false;
@@ -577,21 +644,126 @@ bool attn_map_bwd_tc_supported(const skp_attn_layer* h_layers, int n_layers, int
   return true;
 }
 
+// Layers whose tiles interpolate from at most 64 source pixels (16^2 sources at R = 128) take the "upsample after the
+// logits" gradient; wider windows (32^2: 128 taps need 256 TMEM columns next to the 256 of S) keep the staged path.
+// SKP_BWD_LR=0 sends every layer down the staged path (A/B measurements).
+static bool bwd_layer_lr(const skp_attn_layer& a, int R) {
+  const char* e = getenv("SKP_BWD_LR");          // read per call: the tests switch it to cover both paths
+  const bool enabled = !(e && atoi(e) == 0);
+  return enabled && (a.s * a.s) % 8 == 0 && a.s != R && lr_geometry(a.s, R).kw == TC_BK;
+}
+
 size_t attn_map_bwd_tc_workspace(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int precision) {
-  size_t total = attn_map_tc_workspace(h_layers, n_layers, B, T, R, precision);
+  size_t total = attn_map_tc_workspace(h_layers, n_layers, B, T, R, precision) + 4096;
   const int nbuf = precision == SKP_PREC_TC_BF16 ? 1 : 2;
-  for (int l = 0; l < n_layers; ++l)
+  const size_t tiles = static_cast<size_t>(R) * R / TC_BM;
+  for (int l = 0; l < n_layers; ++l) {
     total += nbuf * tc_align_up(static_cast<size_t>(B) * h_layers[l].heads * BW_SEL * (h_layers[l].C / h_layers[l].heads) * 2, 1024);
+    if (bwd_layer_lr(h_layers[l], R))
+      total += lr_bwd_post_workspace(h_layers[l], B, T) + 2 * tc_align_up(tiles * TC_BM * TC_BK * 2, 1024);
+  }
   return total + 1024;
 }
 
-template <int NPROD, int NH>
+template <int NPROD, int NH, bool LR>
 static int launch_bwd(const BwdParams& P, cudaStream_t st) {
   using SM = BwSmem<NPROD>;
-  auto kern = attn_map_bwd_tc_kernel<NPROD, NH>;
+  auto kern = attn_map_bwd_tc_kernel<NPROD, NH, LR>;
   SKP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::kDynamic));
   kern<<<(::skp::note_launch(), P.n_chunks * NH), BW_THREADS, SM::kDynamic, st>>>(P);
   SKP_LAUNCH_CHECK();
+  return SKP_OK;
+}
+
+// one launch of the main kernel over a subset of the captured layers (`sub`, with their global head offsets)
+static int bwd_launch_group(const skp_attn_layer* sub, const int* ghead, int n_sub, int heads_all, bool lr, int B, int T, int R,
+                            const int64_t* token_idx, int n_idx, int64_t idx_stride, const float* dmaps_sel, const float* row_stats,
+                            bool x3, char** ws_io, cudaStream_t st) {
+  BwdParams P;
+  memset(&P, 0, sizeof(P));
+  char* ws = nullptr;
+  int rc = tc_prepare(sub, n_sub, B, T, R, x3, *ws_io, st, &P.ops, &ws);
+  if (rc != SKP_OK) return rc;
+  const int tiles = R * R / TC_BM;
+  __nv_bfloat16* w_tab[TC_MAX_LAYERS];
+  char* post_ws[TC_MAX_LAYERS];
+  for (int l = 0; l < n_sub; ++l) {
+    const skp_attn_layer& a = sub[l];
+    SKP_REQUIRE(a.dq && a.dk, "skp_attn_map_bwd: layer has null dq/dk");
+    const int d = a.C / a.heads;
+    const size_t bytes = tc_align_up(static_cast<size_t>(B) * a.heads * BW_SEL * d * 2, 1024);
+    __nv_bfloat16* hi = reinterpret_cast<__nv_bfloat16*>(ws); ws += bytes;
+    __nv_bfloat16* lo = nullptr;
+    if (x3) { lo = reinterpret_cast<__nv_bfloat16*>(ws); ws += bytes; }
+    dim3 g(BW_SEL, B);
+    if (x3) bw_prep_ksel_kernel<3><<<(::skp::note_launch(), g), 256, 0, st>>>(a.k, T, a.C, a.heads, a.k_shared, token_idx, n_idx, idx_stride, hi, lo);
+    else bw_prep_ksel_kernel<1><<<(::skp::note_launch(), g), 256, 0, st>>>(a.k, T, a.C, a.heads, a.k_shared, token_idx, n_idx, idx_stride, hi, lo);
+    SKP_LAUNCH_CHECK();
+    rc = tc_encode_map(&P.ksel_map[l][0], hi, d, BW_SEL, B * a.heads, BW_SEL);
+    if (rc == SKP_OK && x3) rc = tc_encode_map(&P.ksel_map[l][1], lo, d, BW_SEL, B * a.heads, BW_SEL);
+    if (rc != SKP_OK) return rc;
+    P.dq[l] = a.dq; P.dk[l] = a.dk; P.s[l] = a.s; P.C[l] = a.C; P.ghead[l] = ghead[l];
+    if (lr) {
+      const LrGeom geo = lr_geometry(a.s, R);
+      P.wnr[l] = geo.nr;
+      const size_t wb = tc_align_up(static_cast<size_t>(tiles) * TC_BM * TC_BK * 2, 1024);
+      int same = -1;
+      for (int m = 0; m < l; ++m)
+        if (sub[m].s == a.s) same = m;
+      if (same >= 0) {
+        w_tab[l] = w_tab[same];
+      } else {
+        w_tab[l] = reinterpret_cast<__nv_bfloat16*>(ws);
+        rc = lr_launch_weights(a.s, R, geo, w_tab[l], reinterpret_cast<__nv_bfloat16*>(ws + wb), st);
+        if (rc != SKP_OK) return rc;
+      }
+      ws += 2 * wb;
+      rc = tc_encode_map(&P.w_map[l], w_tab[l], TC_BK, TC_BM, tiles, TC_BM);
+      if (rc != SKP_OK) return rc;
+      const size_t dzb = tc_align_up(static_cast<size_t>(B) * a.heads * T * a.s * a.s * 4, 1024);
+      P.dz[l] = reinterpret_cast<float*>(ws);
+      SKP_CUDA(cudaMemsetAsync(ws, 0, dzb, st));
+      ws += dzb;
+      post_ws[l] = ws;
+      ws += lr_bwd_post_workspace(a, B, T) - dzb;
+    }
+  }
+  P.heads_all = heads_all;
+  P.B = B; P.T = T; P.R = R; P.R2 = R * R; P.n_idx = n_idx; P.tiles = tiles;
+  P.idx_stride = idx_stride; P.token_idx = token_idx; P.dmaps_sel = dmaps_sel; P.row_stats = row_stats;
+  P.n_units = P.ops.total_heads * B * P.tiles;
+  if (const char* e = getenv("SKP_BWD_DBG")) P.dbg = atoi(e);
+  static unsigned long long* d_prof = nullptr;
+  if (P.dbg & 8) {
+    if (!d_prof) cudaMalloc(&d_prof, 128);
+    cudaMemsetAsync(d_prof, 0, 128, st);
+    P.prof = d_prof;
+  }
+  const int nh = T > TC_BN ? 2 : 1;
+  P.n_chunks = kNumSMs / nh < P.n_units ? kNumSMs / nh : P.n_units;
+  if (lr) {
+    if (x3) rc = nh == 2 ? launch_bwd<3, 2, true>(P, st) : launch_bwd<3, 1, true>(P, st);
+    else rc = nh == 2 ? launch_bwd<1, 2, true>(P, st) : launch_bwd<1, 1, true>(P, st);
+  } else {
+    if (x3) rc = nh == 2 ? launch_bwd<3, 2, false>(P, st) : launch_bwd<3, 1, false>(P, st);
+    else rc = nh == 2 ? launch_bwd<1, 2, false>(P, st) : launch_bwd<1, 1, false>(P, st);
+  }
+  if (rc != SKP_OK) return rc;
+  if (P.dbg & 8) {
+    unsigned long long h[16];
+    cudaStreamSynchronize(st);
+    cudaMemcpy(h, d_prof, 128, cudaMemcpyDeviceToHost);
+    const double n = h[7] ? static_cast<double>(h[7]) : 1.0;
+    fprintf(stderr, "[bwd prof%s, cycles/unit over %llu units] mma: wait q_full %.0f, issue S %.0f, wait ds_full %.0f, issue dQ/dK %.0f | softmax: loop top %.0f, "
+            "wait s_full %.0f, dS %.0f, fence+arrive %.0f, wait mma_done %.0f, drain+adjoint %.0f\n", lr ? " LR" : "", h[7], h[0] / n, h[8] / n, h[1] / n, h[9] / n,
+            h[10] / n, h[2] / n, h[3] / n, h[4] / n, h[5] / n, h[6] / n);
+  }
+  if (lr)
+    for (int l = 0; l < n_sub; ++l) {
+      rc = lr_bwd_post(sub[l], B, T, P.dz[l], post_ws[l], st);
+      if (rc != SKP_OK) return rc;
+    }
+  *ws_io = ws;
   return SKP_OK;
 }
 
@@ -605,52 +777,23 @@ int attn_map_bwd_tc(const skp_attn_layer* h_layers, int n_layers, int B, int T, 
     return SKP_ERR_WORKSPACE;
   }
   const bool x3 = precision != SKP_PREC_TC_BF16;
-  BwdParams P;
-  memset(&P, 0, sizeof(P));
-  char* ws = nullptr;
-  int rc = tc_prepare(h_layers, n_layers, B, T, R, x3, workspace, st, &P.ops, &ws);
-  if (rc != SKP_OK) return rc;
+  // two launches: layers with narrow interpolation windows (LR) and the rest (staged dQ' / dK + bicubic adjoint)
+  skp_attn_layer group[2][TC_MAX_LAYERS];
+  int ghead[2][TC_MAX_LAYERS], n_group[2] = {0, 0}, heads_all = 0;
   for (int l = 0; l < n_layers; ++l) {
-    const skp_attn_layer& a = h_layers[l];
-    SKP_REQUIRE(a.dq && a.dk, "skp_attn_map_bwd: layer %d has null dq/dk", l);
-    const int d = a.C / a.heads;
-    const size_t bytes = tc_align_up(static_cast<size_t>(B) * a.heads * BW_SEL * d * 2, 1024);
-    __nv_bfloat16* hi = reinterpret_cast<__nv_bfloat16*>(ws); ws += bytes;
-    __nv_bfloat16* lo = nullptr;
-    if (x3) { lo = reinterpret_cast<__nv_bfloat16*>(ws); ws += bytes; }
-    dim3 g(BW_SEL, B);
-    if (x3) bw_prep_ksel_kernel<3><<<(::skp::note_launch(), g), 256, 0, st>>>(a.k, T, a.C, a.heads, a.k_shared, token_idx, n_idx, idx_stride, hi, lo);
-    else bw_prep_ksel_kernel<1><<<(::skp::note_launch(), g), 256, 0, st>>>(a.k, T, a.C, a.heads, a.k_shared, token_idx, n_idx, idx_stride, hi, lo);
-    SKP_LAUNCH_CHECK();
-    rc = tc_encode_map(&P.ksel_map[l][0], hi, d, BW_SEL, B * a.heads, BW_SEL);
-    if (rc == SKP_OK && x3) rc = tc_encode_map(&P.ksel_map[l][1], lo, d, BW_SEL, B * a.heads, BW_SEL);
+    const int gi = bwd_layer_lr(h_layers[l], R) ? 1 : 0;
+    group[gi][n_group[gi]] = h_layers[l];
+    ghead[gi][n_group[gi]++] = heads_all;
+    heads_all += h_layers[l].heads;
+  }
+  char* ws = reinterpret_cast<char*>(workspace);
+  for (int gi = 0; gi < 2; ++gi) {
+    if (n_group[gi] == 0) continue;
+    int rc = bwd_launch_group(group[gi], ghead[gi], n_group[gi], heads_all, gi == 1, B, T, R, token_idx, n_idx, idx_stride, dmaps_sel,
+                              row_stats, x3, &ws, st);
     if (rc != SKP_OK) return rc;
-    P.dq[l] = a.dq; P.dk[l] = a.dk; P.s[l] = a.s; P.C[l] = a.C;
   }
-  P.B = B; P.T = T; P.R = R; P.R2 = R * R; P.n_idx = n_idx; P.tiles = R * R / TC_BM;
-  P.idx_stride = idx_stride; P.token_idx = token_idx; P.dmaps_sel = dmaps_sel; P.row_stats = row_stats;
-  P.n_units = P.ops.total_heads * B * P.tiles;
-  if (const char* e = getenv("SKP_BWD_DBG")) P.dbg = atoi(e);
-  static unsigned long long* d_prof = nullptr;
-  if (P.dbg & 8) {
-    if (!d_prof) cudaMalloc(&d_prof, 128);
-    cudaMemsetAsync(d_prof, 0, 128, st);
-    P.prof = d_prof;
-  }
-  const int nh = T > TC_BN ? 2 : 1;
-  P.n_chunks = kNumSMs / nh < P.n_units ? kNumSMs / nh : P.n_units;
-  if (x3) rc = nh == 2 ? launch_bwd<3, 2>(P, st) : launch_bwd<3, 1>(P, st);
-  else rc = nh == 2 ? launch_bwd<1, 2>(P, st) : launch_bwd<1, 1>(P, st);
-  if (P.dbg & 8) {
-    unsigned long long h[16];
-    cudaStreamSynchronize(st);
-    cudaMemcpy(h, d_prof, 128, cudaMemcpyDeviceToHost);
-    const double n = h[7] ? static_cast<double>(h[7]) : 1.0;
-    fprintf(stderr, "[bwd prof, cycles/unit over %llu units] mma: wait q_full %.0f, issue S %.0f, wait ds_full %.0f, issue dQ/dK %.0f | softmax: loop top %.0f, "
-            "wait s_full %.0f, dS %.0f, fence+arrive %.0f, wait mma_done %.0f, drain+adjoint %.0f\n", h[7], h[0] / n, h[8] / n, h[1] / n, h[9] / n,
-            h[10] / n, h[2] / n, h[3] / n, h[4] / n, h[5] / n, h[6] / n);
-  }
-  return rc;
+  return SKP_OK;
 }
 
 }  // namespace skp

@@ -147,6 +147,12 @@ __global__ void lr_weights_kernel(int s, int R, int nr, int kw, __nv_bfloat16* _
   }
 }
 
+int lr_launch_weights(int s, int R, const LrGeom& g, __nv_bfloat16* hi, __nv_bfloat16* lo, cudaStream_t st) {
+  lr_weights_kernel<<<(::skp::note_launch(), R * R / TC_BM), 256, static_cast<size_t>(TC_BM) * (g.nr + s) * sizeof(float), st>>>(s, R, g.nr, g.kw, hi, lo);
+  SKP_LAUNCH_CHECK();
+  return SKP_OK;
+}
+
 // s_low[z][t][sp] = sum_d k[kz][t][d] * q[z][sp][d]   (q already carries scale * log2e), bf16x3
 __global__ void __launch_bounds__(LRG_THREADS) lr_logits_kernel(const __grid_constant__ LrGemmParams P) {
   extern __shared__ uint8_t smem_raw[];

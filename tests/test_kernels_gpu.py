@@ -77,13 +77,18 @@ def _random_layers(spec, T, B, seed, shared_k=True):
     return qs, ks, heads, scales
 
 
-@pytest.mark.parametrize("precision", ["simt_f32", "auto"])
+@pytest.mark.parametrize("precision", ["simt_f32", "auto", "auto-staged"])
 @pytest.mark.parametrize("spec,T,R,B,shared", [
     ([(4, 64, 4), (4, 64, 4), (8, 32, 2)], 37, 16, 2, True),          # unequal heads, ragged T
     ([(8, 128, 2), (16, 64, 4), (32, 32, 2)], 130, 32, 1, False),     # three scales incl. s == R
     ([(4, 96, 2)], 500, 16, 3, True),                                 # dim_head 48, full token count
+    ([(16, 128, 2), (32, 64, 1)], 70, 128, 1, True),                  # BASELINE geometry: 64- and 128-tap windows
 ])
-def test_attention_maps_vs_oracle_unequal_heads(ops, precision, spec, T, R, B, shared):
+def test_attention_maps_vs_oracle_unequal_heads(ops, monkeypatch, precision, spec, T, R, B, shared):
+    """"auto" = tcgen05 bf16x3, operands from the native-resolution logits where the windows allow it (attn_tc_lr.cu);
+    "auto-staged" = the same kernel on the staged upsampled q' (SKP_FWD_LR=0).  Same 1e-3 bar for all."""
+    monkeypatch.setenv("SKP_FWD_LR", "0" if precision == "auto-staged" else "1")
+    precision = "auto" if precision == "auto-staged" else precision
     qs, ks, heads, sc = _random_layers(spec, T, B, 3, shared)
     got = ops.attention_maps([_cu(q) for q in qs], [_cu(k) for k in ks], heads, sc, R, precision=precision).cpu()
     for b in range(B):
@@ -260,12 +265,19 @@ def test_resampling_matches_oracle(ops):
     assert torch.equal(ops.bilinear_upsample(_cu(y), 16).cpu(), y)
 
 
+@pytest.mark.parametrize("lr", ["0", "1"])
 @pytest.mark.parametrize("spec,T,R,B,shared", [
     ([(4, 64, 4), (8, 32, 2)], 40, 16, 2, True),             # dim_head 16, several pixel rows per tile
     ([(8, 128, 2), (16, 64, 1)], 300, 32, 2, False),         # dim_head 64, two token halves, per-image k
+    ([(16, 128, 2), (32, 64, 1)], 260, 128, 1, True),        # BASELINE geometry: one image row per tile, 8 tiles per window
 ])
-def test_attention_maps_backward_tcgen05_matches_oracle_autograd(ops, spec, T, R, B, shared):
-    """tcgen05 backward (bf16 gradient GEMMs, fp32 accumulate): 1e-2 of the gradient's max."""
+def test_attention_maps_backward_tcgen05_matches_oracle_autograd(ops, monkeypatch, spec, T, R, B, shared, lr):
+    """tcgen05 backward against fp64 autograd through the oracle.  Both gradient formulations: lr=0 staged q' with
+    dQ'/dK products and the bicubic adjoint (bf16 dS, k, q' operands): 1e-2 of the gradient's max; lr=1 "upsample after
+    the logits" on the layers with 64-tap windows (the interpolation table is a bf16 operand too): 1.5e-2 of the max
+    (measured 1.04e-2 worst case on these problems, 0.2-0.4e-2 on unit-variance inputs, scripts/bwd_err.py)."""
+    monkeypatch.setenv("SKP_BWD_LR", lr)
+    tol = 1.5e-2 if lr == "1" else 1e-2
     qs, ks, heads, sc = _random_layers(spec, T, B, 5, shared)
     g = torch.Generator().manual_seed(9)
     idx = torch.stack([torch.randperm(T, generator=g)[:6] for _ in range(B)])       # per-image token ids
@@ -286,14 +298,14 @@ def test_attention_maps_backward_tcgen05_matches_oracle_autograd(ops, spec, T, R
     for got, want in zip([t.grad for t in qc + kc], grads):
         scale = float(want.abs().max())
         assert torch.isfinite(got).all()
-        assert (got.cpu().double() - want).abs().max().item() <= 1e-2 * scale
+        assert (got.cpu().double() - want).abs().max().item() <= tol * scale
     # and the CUDA-core backward (no statistics passed) agrees on the same problem
     qd = [_cu(q).requires_grad_(True) for q in qs]
     kd = [_cu(k).requires_grad_(True) for k in ks]
     sel2 = ops.selected_planes(full, _cu(idx), qd, kd, heads, sc, R, precision="simt_f32")
     (sel2 * _cu(w)).sum().backward()
     for a, b_ in zip([t.grad for t in qc + kc], [t.grad for t in qd + kd]):
-        assert (a - b_).abs().max().item() <= 1e-2 * float(b_.abs().max())
+        assert (a - b_).abs().max().item() <= tol * float(b_.abs().max())
 
 
 def test_backward_full_size_tcgen05_vs_cuda_core(ops):
