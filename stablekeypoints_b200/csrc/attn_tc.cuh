@@ -25,6 +25,7 @@ struct TcOperands {
   CUtensorMap q_map[TC_MAX_LAYERS][2];   // [layer][hi, lo]: dims (d, R*R, B*h), box (64, 128, 1)
   CUtensorMap k_map[TC_MAX_LAYERS][2];   // [layer][hi, lo]: dims (d, T,   Bk*h), box (64, 256, 1)
   __nv_bfloat16* k_ptr[TC_MAX_LAYERS][2];
+  __nv_bfloat16* s_ptr[TC_MAX_LAYERS][2];   // lr: native-resolution logits hi, lo [b*h + head][token][s*s]
   int heads[TC_MAX_LAYERS], d[TC_MAX_LAYERS], k_shared[TC_MAX_LAYERS], head_base[TC_MAX_LAYERS];
   float weight[TC_MAX_LAYERS];           // layer weight / heads
   float scale[TC_MAX_LAYERS];

@@ -25,7 +25,7 @@ namespace skp {
 constexpr int BW_SEL = 16;            // selected tokens per launch (UMMA N of the S_sel product)
 constexpr int BW_KSEL_BYTES = BW_SEL * 128;   // 16 rows x 128 B
 constexpr int BW_DS_BYTES = TC_BM * TC_BN * 2;   // 64 KB: dS tile, 4 slabs of [128 px][64 tok] bf16
-constexpr int BW_WXT_FLOATS = 16 * 256;       // x-adjoint table (s rows of 5 R/s taps padded to a multiple of 4, <= 8 KB), or (LR) the 16 KB W tile
+constexpr int BW_WXT_FLOATS = 8 * 256;        // x-adjoint table: s rows of 5 R/s taps padded to a multiple of 4 (<= 8 R/s... R <= 256)
 constexpr float kLog2eBw = 1.4426950408889634f;
 constexpr int BW_STG_LD = 68;          // fp32 staging row pitch (64 + 4): conflict-free float4 stores with lane = row
 
@@ -35,11 +35,11 @@ struct BwdParams {
   float* dq[TC_MAX_LAYERS];                 // (B, s*s, C), accumulated into
   float* dk[TC_MAX_LAYERS];                 // (Bk, T, C), accumulated into
   int s[TC_MAX_LAYERS], C[TC_MAX_LAYERS];
-  // "upsample after the logits" launches (template LR): interpolation tables W hi [tile][128 px][64 taps] and the fp32
-  // accumulator of the native-resolution logit gradient dz[b*h + head][token][s*s] of every layer
-  CUtensorMap w_map[TC_MAX_LAYERS];
+  // "upsample after the logits" launches (template LR; ops then holds W tables / native-resolution logits, ksel_map the
+  // selected tokens' logit rows): fp32 accumulator of the logit gradient dz[b*h + head][token][s*s] of every layer
   float* dz[TC_MAX_LAYERS];
-  int wnr[TC_MAX_LAYERS];                   // source rows per window (LrGeom::nr)
+  const unsigned char* wr0[TC_MAX_LAYERS];  // first source row of every tile's window (lr_window_row0 costs two divisions
+                                            // and a float->int chain, ~700 cycles of dependent latency per call)
   int ghead[TC_MAX_LAYERS];                 // first head of the layer among ALL captured layers (row_stats index)
   int heads_all;                            // heads of all captured layers (row_stats stride)
   int B, T, R, R2, n_idx, tiles, n_units, n_chunks;
@@ -70,6 +70,20 @@ __global__ void bw_prep_ksel_kernel(const float* __restrict__ k, int T, int C, i
   }
 }
 
+// LR: s_sel[(b*h + head)][j][sp] = s_low[(b*h + head)][token_idx[b][j]][sp]  (rows j >= n_idx are zero)
+__global__ void bw_gather_ssel_kernel(const __nv_bfloat16* __restrict__ s_hi, const __nv_bfloat16* __restrict__ s_lo, int T, int s2,
+                                      int heads, const int64_t* __restrict__ token_idx, int n_idx, int64_t idx_stride,
+                                      __nv_bfloat16* __restrict__ hi, __nv_bfloat16* __restrict__ lo) {
+  const int j = blockIdx.x, z = blockIdx.y, b = z / heads;
+  const int t = j < n_idx ? static_cast<int>(token_idx[b * idx_stride + j]) : -1;
+  const bool ok = t >= 0 && t < T;
+  const int64_t src = (static_cast<int64_t>(z) * T + (ok ? t : 0)) * s2, dst = (static_cast<int64_t>(z) * BW_SEL + j) * s2;
+  for (int c = threadIdx.x; c < s2; c += blockDim.x) {
+    hi[dst + c] = ok ? s_hi[src + c] : __float2bfloat16_rn(0.0f);
+    if (lo) lo[dst + c] = ok ? s_lo[src + c] : __float2bfloat16_rn(0.0f);
+  }
+}
+
 template <int NPROD>
 struct BwSmem {
   static constexpr int kQStage = (NPROD == 3 ? 2 : 1) * TC_A_BYTES;
@@ -80,7 +94,7 @@ struct BwSmem {
   static constexpr int kKselBytes = (NPROD == 3 ? 2 : 1) * BW_KSEL_BYTES;
   static constexpr int kDsOff = kKselOff + kKselBytes;              // dS tile; aliased by the fp32 dQ' staging
   static constexpr int kWxtOff = kDsOff + BW_DS_BYTES;
-  static constexpr int kBarOff = kWxtOff + BW_WXT_FLOATS * 4;       // q_full[2], q_empty[2], s_full, ds_full, mma_done, w_full
+  static constexpr int kBarOff = kWxtOff + BW_WXT_FLOATS * 4;       // q_full[2], q_empty[2], s_full, ds_full, mma_done
   static constexpr int kTmemPtrOff = kBarOff + 8 * 8;
   static constexpr int kTokOff = kTmemPtrOff + 8;                   // int tok[16]
   static constexpr int kTotal = kTokOff + 4 * BW_SEL;
@@ -102,6 +116,9 @@ __device__ __host__ constexpr uint32_t bw_idesc(int M, int N, int a_mn, int b_mn
 }
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__global__ void bw_window_table_kernel(int s, int R, int nr, int tiles, unsigned char* tab) {
+  for (int t = threadIdx.x; t < tiles; t += blockDim.x) tab[t] = static_cast<unsigned char>(lr_window_row0(t, s, R, nr));
 }
 __device__ __forceinline__ void named_bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 struct BwUnit {
@@ -151,8 +168,7 @@ __device__ __forceinline__ BwUnit bw_next(const BwdParams& P, BwUnit x) {
 template <bool LR>
 __device__ __forceinline__ bool bw_flush_between(const BwdParams& P, const BwUnit& x, const BwUnit& nx, bool last) {
   if (LR)
-    return last || nx.hg != x.hg || nx.b != x.b ||
-           lr_window_row0(nx.tile, P.s[x.l], P.R, P.wnr[x.l]) != lr_window_row0(x.tile, P.s[x.l], P.R, P.wnr[x.l]);
+    return last || nx.hg != x.hg || nx.b != x.b || P.wr0[x.l][nx.tile] != P.wr0[x.l][x.tile];
   return last || nx.hg != x.hg || (!P.ops.k_shared[x.l] && nx.b != x.b);
 }
 
@@ -185,8 +201,6 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
   const uint32_t bar_sfull = base + SM::kBarOff + 8u * 4;
   const uint32_t bar_dsfull = base + SM::kBarOff + 8u * 5;
   const uint32_t bar_mmadone = base + SM::kBarOff + 8u * 6;
-  const uint32_t bar_wfull = base + SM::kBarOff + 8u * 7;
-  const uint32_t wtile = base + SM::kWxtOff;
   volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(base_ptr + SM::kTmemPtrOff);
   volatile int* tok_s = reinterpret_cast<volatile int*>(base_ptr + SM::kTokOff);
   float* wxt = reinterpret_cast<float*>(base_ptr + SM::kWxtOff);
@@ -200,7 +214,6 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
     ptx::mbar_init(bar_sfull, 1);
     ptx::mbar_init(bar_dsfull, TC_SOFTMAX_THREADS);
     ptx::mbar_init(bar_mmadone, 1);
-    ptx::mbar_init(bar_wfull, 1);
     ptx::fence_barrier_init();
   }
   if (warp == 1) {
@@ -218,39 +231,41 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
   if (warp == 0) {
     // =========================== TMA producer (one lane) ===================================
     if (lane == 0) {
-      int prev_hg = -1, prev_b = -1;
+      // LR: the A stage holds the interpolation table W of the tile (it also is the B operand of the dz product, as Q'
+      // is of dK), the "k" / "k_sel" buffers hold the tile's window of native-resolution logits of the CTA's 256 tokens
+      // / of the selected tokens: reloaded when the window moves (every R/s tiles) instead of once per head.
+      int prev_hg = -1, prev_b = -1, prev_r0 = -1;
       uint32_t it = 0;
       BwUnit x = bw_decode(P, u_begin);
       for (int u = u_begin; u < u_end; ++u, ++it, x = bw_next(P, x)) {
         const int h = P.ops.heads[x.l];
         const int st = it & 1;
         ptx::mbar_wait(bar_qempty(st), ((it >> 1) & 1u) ^ 1u);
-        const bool need_k = x.hg != prev_hg || (!P.ops.k_shared[x.l] && x.b != prev_b);
+        const int r0 = LR ? P.wr0[x.l][x.tile] : 0;
+        const bool need_k = LR ? (x.hg != prev_hg || x.b != prev_b || r0 != prev_r0)
+                               : (x.hg != prev_hg || (!P.ops.k_shared[x.l] && x.b != prev_b));
         const bool need_ksel = need_k || x.b != prev_b;
         if (need_ksel && it > 0) ptx::mbar_wait(bar_qempty((it - 1) & 1), ((it - 1) >> 1) & 1u);   // previous unit done with k / k_sel
         const uint32_t bytes = SM::kQStage + (need_k ? SM::kKBytes : 0) + (need_ksel ? SM::kKselBytes : 0);
         ptx::mbar_arrive_expect_tx(bar_qfull(st), bytes);
         const int qz = x.b * h + x.head;
         const uint32_t qs = base + SM::kQOff + st * SM::kQStage;
-        ptx::tma_load_3d(qs, &P.ops.q_map[x.l][0], bar_qfull(st), 0, x.tile * TC_BM, qz);
-        if (NPROD == 3) ptx::tma_load_3d(qs + TC_A_BYTES, &P.ops.q_map[x.l][1], bar_qfull(st), 0, x.tile * TC_BM, qz);
+        const int a_row = LR ? 0 : x.tile * TC_BM, a_z = LR ? x.tile : qz;     // (k, row, batch) of the A tile
+        const int b_k0 = LR ? r0 * P.s[x.l] : 0;                              // first tap of the window in the s*s row
+        ptx::tma_load_3d(qs, &P.ops.q_map[x.l][0], bar_qfull(st), 0, a_row, a_z);
+        if (NPROD == 3) ptx::tma_load_3d(qs + TC_A_BYTES, &P.ops.q_map[x.l][1], bar_qfull(st), 0, a_row, a_z);
         if (need_k) {
-          const int kz = (P.ops.k_shared[x.l] ? 0 : x.b * h) + x.head;
-          ptx::tma_load_3d(base + SM::kKOff, &P.ops.k_map[x.l][0], bar_qfull(st), 0, tok0, kz);
-          if (NPROD == 3) ptx::tma_load_3d(base + SM::kKOff + TC_B_BYTES, &P.ops.k_map[x.l][1], bar_qfull(st), 0, tok0, kz);
+          const int kz = LR ? qz : (P.ops.k_shared[x.l] ? 0 : x.b * h) + x.head;
+          ptx::tma_load_3d(base + SM::kKOff, &P.ops.k_map[x.l][0], bar_qfull(st), b_k0, tok0, kz);
+          if (NPROD == 3) ptx::tma_load_3d(base + SM::kKOff + TC_B_BYTES, &P.ops.k_map[x.l][1], bar_qfull(st), b_k0, tok0, kz);
         }
         if (need_ksel) {
-          ptx::tma_load_3d(base + SM::kKselOff, &P.ksel_map[x.l][0], bar_qfull(st), 0, 0, qz);
-          if (NPROD == 3) ptx::tma_load_3d(base + SM::kKselOff + BW_KSEL_BYTES, &P.ksel_map[x.l][1], bar_qfull(st), 0, 0, qz);
-        }
-        if (LR) {
-          // single W buffer: the dz product of the previous unit must have retired before it is overwritten
-          if (it > 0) ptx::mbar_wait(bar_qempty((it - 1) & 1), ((it - 1) >> 1) & 1u);
-          ptx::mbar_arrive_expect_tx(bar_wfull, TC_A_BYTES);
-          ptx::tma_load_3d(wtile, &P.w_map[x.l], bar_wfull, 0, 0, x.tile);
+          ptx::tma_load_3d(base + SM::kKselOff, &P.ksel_map[x.l][0], bar_qfull(st), b_k0, 0, qz);
+          if (NPROD == 3) ptx::tma_load_3d(base + SM::kKselOff + BW_KSEL_BYTES, &P.ksel_map[x.l][1], bar_qfull(st), b_k0, 0, qz);
         }
         prev_hg = x.hg;
         prev_b = x.b;
+        prev_r0 = r0;
       }
     }
   } else if (warp == 1) {
@@ -260,20 +275,17 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       bool dk_fresh = true;
       long long pf_q = 0, pf_ds = 0, pf_is = 0, pf_id = 0;      // profiler (SKP_BWD_DBG & 8), kept in registers
       BwUnit x = bw_decode(P, u_begin);
-      for (int u = u_begin; u < u_end; ++u, ++it) {
-        const BwUnit nxu = bw_next(P, x);
-        const int d = P.ops.d[x.l];
-        const int st = it & 1;
-        const uint32_t qs = base + SM::kQOff + st * SM::kQStage;
-        const uint32_t ks = base + SM::kKOff, ksel = base + SM::kKselOff, dsb = base + SM::kDsOff;
+      const uint32_t ks = base + SM::kKOff, ksel = base + SM::kKselOff, dsb = base + SM::kDsOff;
+      // ---- S = Q' K^T (256 tokens) and S_sel = Q' K_sel^T (16 tokens) of the unit in stage (jt & 1)
+      auto issue_S = [&](int l, uint32_t jt) {
+        const uint32_t qs = base + SM::kQOff + (jt & 1) * SM::kQStage;
         long long c0 = clock64();
-        ptx::mbar_wait(bar_qfull(st), (it >> 1) & 1u);
+        ptx::mbar_wait(bar_qfull(jt & 1), (jt >> 1) & 1u);
         ptx::tc_fence_after();
         pf_q += clock64() - c0;
         c0 = clock64();
-        // ---- S = Q' K^T (256 tokens) and S_sel = Q' K_sel^T (16 tokens)
         const uint32_t id_S = bw_idesc(TC_BM, TC_BN, 0, 0), id_sel = bw_idesc(TC_BM, BW_SEL, 0, 0);
-        const int nk16 = d / 16;
+        const int nk16 = P.ops.d[l] / 16;
         for (int kk = 0; kk < nk16; ++kk) {
           const uint64_t a_hi = bw_desc(qs + kk * 32, 16, 1024), b_hi = bw_desc(ks + kk * 32, 16, 1024);
           const uint64_t s_hi = bw_desc(ksel + kk * 32, 16, 1024);
@@ -294,11 +306,27 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         }
         ptx::umma_commit(bar_sfull);
         pf_is += clock64() - c0;
+      };
+      bool s_issued = false;       // S of this unit went out early, in the previous iteration
+      for (int u = u_begin; u < u_end; ++u, ++it) {
+        const BwUnit nxu = bw_next(P, x);
+        const int d = P.ops.d[x.l];
+        const int st = it & 1;
+        const uint32_t qs = base + SM::kQOff + st * SM::kQStage;
+        if (!s_issued) issue_S(x.l, it);
+        s_issued = false;
         // ---- wait for dS (bf16, [px][tok]) in shared memory
-        c0 = clock64();
+        long long c0 = clock64();
         ptx::mbar_wait(bar_dsfull, it & 1u);
         ptx::tc_fence_after();
         pf_ds += clock64() - c0;
+        // LR: the softmax warps are done with S(u), so S(u+1) can run AHEAD of the dz product of this unit (they start
+        // on the next unit ~1200 cycles earlier and only need dz(u) retired before their first dS store).  Not when
+        // the next unit reloads k / k_sel: those single buffers are only refilled after this unit's MMAs retire.
+        if (LR && u + 1 < u_end && nxu.hg == x.hg && nxu.b == x.b && P.wr0[x.l][nxu.tile] == P.wr0[x.l][x.tile]) {
+          issue_S(nxu.l, it + 1);
+          s_issued = true;
+        }
         c0 = clock64();
         if (!LR) {
           // dQ' (128 px x d) = dS (K-major A, K = 256 tokens) * K_hi (MN-major B: rows = tokens)
@@ -314,14 +342,13 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
               ptx::umma_bf16(tm_dK + mh * 64, bw_desc(dsb + mh * 2 * 16384 + k * 2048, 16384, 1024),
                              bw_desc(qs + k * 2048, 16384, 1024), id_dk, (dk_fresh && k == 0) ? 0u : 1u);
         } else {
-          // dz (128 tok x 64 taps per half) += dS^T (MN-major A: rows = pixels) * W_hi (MN-major B: rows = pixels)
-          ptx::mbar_wait(bar_wfull, it & 1u);
-          ptx::tc_fence_after();
+          // dz (128 tok x 64 taps per half) += dS^T (MN-major A: rows = pixels) * W_hi (MN-major B: rows = pixels; the
+          // A stage of this unit's S product)
           const uint32_t id_dz = bw_idesc(128, TC_BK, 1, 1);
           for (int mh = 0; mh < n_mh; ++mh)
             for (int k = 0; k < TC_BM / 16; ++k)
               ptx::umma_bf16(tm_dK + mh * 64, bw_desc(dsb + mh * 2 * 16384 + k * 2048, 16384, 1024),
-                             bw_desc(wtile + k * 2048, 16384, 1024), id_dz, (dk_fresh && k == 0) ? 0u : 1u);
+                             bw_desc(qs + k * 2048, 16384, 1024), id_dz, (dk_fresh && k == 0) ? 0u : 1u);
         }
         ptx::umma_commit(bar_mmadone);
         ptx::umma_commit(bar_qempty(st));
@@ -359,6 +386,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         dpr[j] = j < P.n_idx ? __ldg(P.dmaps_sel + (static_cast<int64_t>(y.b) * P.n_idx + j) * P.R2 + pp) : 0.0f;
     };
     long long pf[6] = {0, 0, 0, 0, 0, 0}, c_end = clock64();   // profiler (SKP_BWD_DBG & 8), kept in registers
+    bool mma_pending = false;      // LR: the wait for the previous unit's dz product is deferred to the first dS store
     BwUnit x = bw_decode(P, u_begin), nxu = x;
     for (int u = u_begin; u < u_end; ++u, ++it, x = nxu) {
       nxu = bw_next(P, x);
@@ -395,6 +423,9 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       float dp[BW_SEL];
 #pragma unroll
       for (int j = 0; j < BW_SEL; ++j) dp[j] = wgt * nx_dp[j];
+      // LR: next unit's row statistics / upstream gradients go out now and land under this unit's dS pass (there is
+      // no long MMA wait at the end of the unit to hide them any more)
+      if (LR && u + 1 < u_end && !(P.dbg & 16)) load_row(nxu, nx_ml, nx_dp);
 
       long long c1 = clock64();
       pf[5] += c1 - c_end;                      // loop top: decode, prefetch issue, table rebuilds
@@ -426,6 +457,11 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
           ptx::tmem_ld_wait();
           if (c < 3) ptx::tmem_ld32(tm_S + lane_off + col0 + 32 * (c + 1), v[(c + 1) & 1]);
           uint32_t pk[16];
+          if (LR && c == 0 && mma_pending) {
+            // the dS tile is still being read by the previous unit's dz product
+            ptx::mbar_wait(bar_mmadone, (it - 1) & 1u);
+            mma_pending = false;
+          }
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
             float e0 = ptx::ex2(__uint_as_float(v[c & 1][2 * j]) - m) * nd;
@@ -464,10 +500,15 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
 
       // next unit's row statistics / upstream gradients: issued here, where this thread would only spin
       // on the dQ/dK MMAs, they are back long before the next loop top
-      if (u + 1 < u_end && !(P.dbg & 16)) load_row(nxu, nx_ml, nx_dp);
+      if (!LR && u + 1 < u_end && !(P.dbg & 16)) load_row(nxu, nx_ml, nx_dp);
       // ---- dQ' tile: TMEM -> fp32 staging (aliases the dS tile, free once the MMAs are done)
-      ptx::mbar_wait(bar_mmadone, it & 1u);
-      ptx::tc_fence_after();
+      const bool lr_flush = LR && bw_flush_between<true>(P, x, nxu, u + 1 >= u_end);
+      if (!LR || lr_flush) {
+        ptx::mbar_wait(bar_mmadone, it & 1u);
+        ptx::tc_fence_after();
+      } else {
+        mma_pending = true;
+      }
       pf[3] += clock64() - c1;
       c1 = clock64();
       if (!LR && ch * 32 < d && !(P.dbg & 4)) {
@@ -563,10 +604,10 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       c_end = clock64();
       if (LR) {
         // ---- dz: flush the window accumulator (token rows x 64 taps) when the next tile leaves this window
-        if (bw_flush_between<true>(P, x, nxu, u + 1 >= u_end) && ch < n_mh) {
+        if (lr_flush && ch < n_mh) {
           const int t = tok0 + ch * 128 + row;
           const int h = P.ops.heads[x.l];
-          const int r0 = lr_window_row0(x.tile, s, R, P.wnr[x.l]);
+          const int r0 = P.wr0[x.l][x.tile];
           const int nvalid = min(TC_BK, s * s - r0 * s);      // taps of the window inside the source image
           float* dz = P.dz[x.l] + ((static_cast<int64_t>(x.b) * h + x.head) * P.T + t) * (s * s) + r0 * s;
 #pragma unroll
@@ -656,11 +697,12 @@ static bool bwd_layer_lr(const skp_attn_layer& a, int R) {
 size_t attn_map_bwd_tc_workspace(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int precision) {
   size_t total = attn_map_tc_workspace(h_layers, n_layers, B, T, R, precision) + 4096;
   const int nbuf = precision == SKP_PREC_TC_BF16 ? 1 : 2;
-  const size_t tiles = static_cast<size_t>(R) * R / TC_BM;
   for (int l = 0; l < n_layers; ++l) {
-    total += nbuf * tc_align_up(static_cast<size_t>(B) * h_layers[l].heads * BW_SEL * (h_layers[l].C / h_layers[l].heads) * 2, 1024);
-    if (bwd_layer_lr(h_layers[l], R))
-      total += lr_bwd_post_workspace(h_layers[l], B, T) + 2 * tc_align_up(tiles * TC_BM * TC_BK * 2, 1024);
+    const skp_attn_layer& a = h_layers[l];
+    const bool lr = bwd_layer_lr(a, R);
+    const size_t kd = lr ? static_cast<size_t>(a.s) * a.s : a.C / a.heads;     // selected-token rows: k rows, or (LR) logit rows
+    total += nbuf * tc_align_up(static_cast<size_t>(B) * a.heads * BW_SEL * kd * 2, 1024);
+    if (lr) total += attn_map_lr_workspace(&a, 1, B, T, R) + lr_bwd_post_workspace(a, B, T) + 2048;
   }
   return total + 1024;
 }
@@ -682,44 +724,35 @@ static int bwd_launch_group(const skp_attn_layer* sub, const int* ghead, int n_s
   BwdParams P;
   memset(&P, 0, sizeof(P));
   char* ws = nullptr;
-  int rc = tc_prepare(sub, n_sub, B, T, R, x3, *ws_io, st, &P.ops, &ws);
+  SKP_REQUIRE(!lr || x3, "skp_attn_map_bwd: the upsample-after-logits path is bf16x3 only");
+  int rc = lr ? tc_prepare_lr(sub, n_sub, B, T, R, *ws_io, st, &P.ops, &ws) : tc_prepare(sub, n_sub, B, T, R, x3, *ws_io, st, &P.ops, &ws);
   if (rc != SKP_OK) return rc;
   const int tiles = R * R / TC_BM;
-  __nv_bfloat16* w_tab[TC_MAX_LAYERS];
   char* post_ws[TC_MAX_LAYERS];
   for (int l = 0; l < n_sub; ++l) {
     const skp_attn_layer& a = sub[l];
     SKP_REQUIRE(a.dq && a.dk, "skp_attn_map_bwd: layer has null dq/dk");
     const int d = a.C / a.heads;
-    const size_t bytes = tc_align_up(static_cast<size_t>(B) * a.heads * BW_SEL * d * 2, 1024);
+    const int kd = lr ? a.s * a.s : d;       // inner length of the selected-token rows: dim_head, or (LR) the s*s logits
+    const size_t bytes = tc_align_up(static_cast<size_t>(B) * a.heads * BW_SEL * kd * 2, 1024);
     __nv_bfloat16* hi = reinterpret_cast<__nv_bfloat16*>(ws); ws += bytes;
     __nv_bfloat16* lo = nullptr;
     if (x3) { lo = reinterpret_cast<__nv_bfloat16*>(ws); ws += bytes; }
     dim3 g(BW_SEL, B);
-    if (x3) bw_prep_ksel_kernel<3><<<(::skp::note_launch(), g), 256, 0, st>>>(a.k, T, a.C, a.heads, a.k_shared, token_idx, n_idx, idx_stride, hi, lo);
+    if (lr) bw_gather_ssel_kernel<<<(::skp::note_launch(), dim3(BW_SEL, B * a.heads)), 128, 0, st>>>(P.ops.s_ptr[l][0], P.ops.s_ptr[l][1], T, kd, a.heads, token_idx, n_idx, idx_stride, hi, lo);
+    else if (x3) bw_prep_ksel_kernel<3><<<(::skp::note_launch(), g), 256, 0, st>>>(a.k, T, a.C, a.heads, a.k_shared, token_idx, n_idx, idx_stride, hi, lo);
     else bw_prep_ksel_kernel<1><<<(::skp::note_launch(), g), 256, 0, st>>>(a.k, T, a.C, a.heads, a.k_shared, token_idx, n_idx, idx_stride, hi, lo);
     SKP_LAUNCH_CHECK();
-    rc = tc_encode_map(&P.ksel_map[l][0], hi, d, BW_SEL, B * a.heads, BW_SEL);
-    if (rc == SKP_OK && x3) rc = tc_encode_map(&P.ksel_map[l][1], lo, d, BW_SEL, B * a.heads, BW_SEL);
+    rc = tc_encode_map(&P.ksel_map[l][0], hi, kd, BW_SEL, B * a.heads, BW_SEL);
+    if (rc == SKP_OK && x3) rc = tc_encode_map(&P.ksel_map[l][1], lo, kd, BW_SEL, B * a.heads, BW_SEL);
     if (rc != SKP_OK) return rc;
     P.dq[l] = a.dq; P.dk[l] = a.dk; P.s[l] = a.s; P.C[l] = a.C; P.ghead[l] = ghead[l];
     if (lr) {
       const LrGeom geo = lr_geometry(a.s, R);
-      P.wnr[l] = geo.nr;
-      const size_t wb = tc_align_up(static_cast<size_t>(tiles) * TC_BM * TC_BK * 2, 1024);
-      int same = -1;
-      for (int m = 0; m < l; ++m)
-        if (sub[m].s == a.s) same = m;
-      if (same >= 0) {
-        w_tab[l] = w_tab[same];
-      } else {
-        w_tab[l] = reinterpret_cast<__nv_bfloat16*>(ws);
-        rc = lr_launch_weights(a.s, R, geo, w_tab[l], reinterpret_cast<__nv_bfloat16*>(ws + wb), st);
-        if (rc != SKP_OK) return rc;
-      }
-      ws += 2 * wb;
-      rc = tc_encode_map(&P.w_map[l], w_tab[l], TC_BK, TC_BM, tiles, TC_BM);
-      if (rc != SKP_OK) return rc;
+      P.wr0[l] = reinterpret_cast<unsigned char*>(ws);
+      bw_window_table_kernel<<<(::skp::note_launch(), 1), 256, 0, st>>>(a.s, R, geo.nr, tiles, reinterpret_cast<unsigned char*>(ws));
+      SKP_LAUNCH_CHECK();
+      ws += 1024;
       const size_t dzb = tc_align_up(static_cast<size_t>(B) * a.heads * T * a.s * a.s * 4, 1024);
       P.dz[l] = reinterpret_cast<float*>(ws);
       SKP_CUDA(cudaMemsetAsync(ws, 0, dzb, st));

@@ -31,16 +31,15 @@ struct LrGradGemmParams {
   int64_t out_z;          // stride between output batches (0 for a shared k)
   int ld, d, heads, m_valid, K;
   int nsum, a_zstride, b_zstride;   // the sum over z: A batch = za + i * a_zstride, B batch = zb + i * b_zstride
-  int a_lo_zoff;          // A is split hi + lo: the lo batches start a_lo_zoff after the hi batches (same B)
   int b_shared;           // B batch ignores the image (dq product with a shared k)
   float alpha;
 };
 
 // dz fp32 [z][T][s2] -> bf16 [z][T][s2] and bf16 [z][s2][Tp] (Tp = T padded to 8, pad columns zero)
-// both as hi + lo residual: the lo arrays follow the hi arrays as Z more batches (out_lo = out + Z*T*s2, ...)
+// (a hi + lo split of dz was measured: no change of the gradient error, which is set by the bf16 dS / W operands of the
+// main kernel, so dz is rounded once)
 __global__ void lr_dz_convert_kernel(const float* __restrict__ dz, int T, int s2, int Tp, __nv_bfloat16* __restrict__ out,
                                      __nv_bfloat16* __restrict__ outT) {
-  const int64_t lo_off = static_cast<int64_t>(gridDim.z) * T * s2, loT_off = static_cast<int64_t>(gridDim.z) * s2 * Tp;
   __shared__ float tile[32][33];
   const int z = blockIdx.z, t0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
   const float* src = dz + static_cast<int64_t>(z) * T * s2;
@@ -49,21 +48,14 @@ __global__ void lr_dz_convert_kernel(const float* __restrict__ dz, int T, int s2
     float v = 0.0f;
     if (t < T && c < s2) {
       v = src[static_cast<int64_t>(t) * s2 + c];
-      const __nv_bfloat16 h = __float2bfloat16_rn(v);
-      out[(static_cast<int64_t>(z) * T + t) * s2 + c] = h;
-      out[lo_off + (static_cast<int64_t>(z) * T + t) * s2 + c] = __float2bfloat16_rn(v - __bfloat162float(h));
+      out[(static_cast<int64_t>(z) * T + t) * s2 + c] = __float2bfloat16_rn(v);
     }
     tile[r][threadIdx.x] = v;
   }
   __syncthreads();
   for (int r = threadIdx.y; r < 32; r += blockDim.y) {
     const int c = c0 + r, t = t0 + threadIdx.x;
-    if (c < s2 && t < Tp) {
-      const float v = tile[threadIdx.x][r];
-      const __nv_bfloat16 h = __float2bfloat16_rn(v);
-      outT[(static_cast<int64_t>(z) * s2 + c) * Tp + t] = h;
-      outT[loT_off + (static_cast<int64_t>(z) * s2 + c) * Tp + t] = __float2bfloat16_rn(v - __bfloat162float(h));
-    }
+    if (c < s2 && t < Tp) outT[(static_cast<int64_t>(z) * s2 + c) * Tp + t] = __float2bfloat16_rn(tile[threadIdx.x][r]);
   }
 }
 
@@ -117,17 +109,16 @@ __global__ void __launch_bounds__(LGG_THREADS) lr_grad_gemm_kernel(const __grid_
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
   const int nkb = (P.K + TC_BK - 1) / TC_BK;
-  const int total = nkb * P.nsum * 2;
+  const int total = nkb * P.nsum;
 
   if (warp == 0) {
     if (lane == 0) {
       // one thread runs both the TMA ring (LGG_STAGES blocks ahead) and the MMA issue
       constexpr uint32_t idesc = ptx::umma_idesc_bf16(TC_BM, LGG_BN);
       auto load = [&](int it) {
-        const int ip = it / nkb, kb = it - ip * nkb;
-        const int i = ip >> 1, part = ip & 1;
+        const int i = it / nkb, kb = it - i * nkb;
         const int s = it % LGG_STAGES;
-        const int za = (zo * P.heads + head) + i * P.a_zstride + part * P.a_lo_zoff;
+        const int za = (zo * P.heads + head) + i * P.a_zstride;
         const int zb = (P.b_shared ? head : zo * P.heads + head) + i * P.b_zstride;
         ptx::mbar_wait(bar_empty(s), ((it / LGG_STAGES) & 1u) ^ 1u);
         ptx::mbar_arrive_expect_tx(bar_full(s), LGG_STAGE);
@@ -194,8 +185,8 @@ size_t lr_bwd_post_workspace(const skp_attn_layer& a, int B, int T) {
   const size_t s2 = static_cast<size_t>(a.s) * a.s, Tp = (T + 7) / 8 * 8, Bk = a.k_shared ? 1 : B;
   size_t total = 0;
   total += tc_align_up(static_cast<size_t>(B) * a.heads * T * s2 * 4, 1024);        // dz fp32
-  total += tc_align_up(static_cast<size_t>(B) * a.heads * T * s2 * 4, 1024);        // dz bf16 hi + lo [t][sp]
-  total += tc_align_up(static_cast<size_t>(B) * a.heads * s2 * Tp * 4, 1024);       // dz bf16 hi + lo [sp][t]
+  total += tc_align_up(static_cast<size_t>(B) * a.heads * T * s2 * 2, 1024);        // dz bf16 [t][sp]
+  total += tc_align_up(static_cast<size_t>(B) * a.heads * s2 * Tp * 2, 1024);       // dz bf16 [sp][t]
   total += tc_align_up(Bk * static_cast<size_t>(a.C) * Tp * 2, 1024);               // k^T
   total += tc_align_up(static_cast<size_t>(B) * a.C * s2 * 2, 1024);                // q^T
   return total;
@@ -210,8 +201,8 @@ int lr_bwd_post(const skp_attn_layer& a, int B, int T, const float* dz, char* ws
     ws += tc_align_up(bytes, 1024);
     return p;
   };
-  __nv_bfloat16* dzb = take(static_cast<size_t>(Z) * T * s2 * 4);      // hi batches, then lo batches
-  __nv_bfloat16* dzT = take(static_cast<size_t>(Z) * s2 * Tp * 4);
+  __nv_bfloat16* dzb = take(static_cast<size_t>(Z) * T * s2 * 2);
+  __nv_bfloat16* dzT = take(static_cast<size_t>(Z) * s2 * Tp * 2);
   __nv_bfloat16* kT = take(static_cast<size_t>(Bk) * a.C * Tp * 2);
   __nv_bfloat16* qT = take(static_cast<size_t>(B) * a.C * s2 * 2);
   const dim3 tb(32, 8);
@@ -224,11 +215,11 @@ int lr_bwd_post(const skp_attn_layer& a, int B, int T, const float* dz, char* ws
   {
     LrGradGemmParams G;
     memset(&G, 0, sizeof(G));
-    int rc = tc_encode_map(&G.a_map, dzT, Tp, s2, 2 * Z, TC_BM);
+    int rc = tc_encode_map(&G.a_map, dzT, Tp, s2, Z, TC_BM);
     if (rc == SKP_OK) rc = tc_encode_map(&G.b_map, kT, Tp, d, Bk * a.heads, LGG_BN);
     if (rc != SKP_OK) return rc;
     G.out = a.dq; G.out_z = static_cast<int64_t>(s2) * a.C; G.ld = a.C; G.d = d; G.heads = a.heads; G.m_valid = s2; G.K = Tp;
-    G.nsum = 1; G.a_zstride = 0; G.b_zstride = 0; G.b_shared = a.k_shared; G.alpha = a.scale; G.a_lo_zoff = Z;
+    G.nsum = 1; G.a_zstride = 0; G.b_zstride = 0; G.b_shared = a.k_shared; G.alpha = a.scale;
     lr_grad_gemm_kernel<<<(::skp::note_launch(), dim3((s2 + TC_BM - 1) / TC_BM, Z)), LGG_THREADS, LGG_DYNAMIC, st>>>(G);
     SKP_LAUNCH_CHECK();
   }
@@ -236,11 +227,11 @@ int lr_bwd_post(const skp_attn_layer& a, int B, int T, const float* dz, char* ws
   {
     LrGradGemmParams G;
     memset(&G, 0, sizeof(G));
-    int rc = tc_encode_map(&G.a_map, dzb, s2, T, 2 * Z, TC_BM);
+    int rc = tc_encode_map(&G.a_map, dzb, s2, T, Z, TC_BM);
     if (rc == SKP_OK) rc = tc_encode_map(&G.b_map, qT, s2, d, Z, LGG_BN);
     if (rc != SKP_OK) return rc;
     G.out = a.dk; G.out_z = static_cast<int64_t>(T) * a.C; G.ld = a.C; G.d = d; G.heads = a.heads; G.m_valid = T; G.K = s2;
-    G.nsum = a.k_shared ? B : 1; G.a_zstride = a.heads; G.b_zstride = a.heads; G.b_shared = 0; G.alpha = a.scale; G.a_lo_zoff = Z;
+    G.nsum = a.k_shared ? B : 1; G.a_zstride = a.heads; G.b_zstride = a.heads; G.b_shared = 0; G.alpha = a.scale;
     lr_grad_gemm_kernel<<<(::skp::note_launch(), dim3((T + TC_BM - 1) / TC_BM, Bk * a.heads)), LGG_THREADS, LGG_DYNAMIC, st>>>(G);
     SKP_LAUNCH_CHECK();
   }

@@ -325,6 +325,7 @@ int tc_prepare_lr(const skp_attn_layer* h_layers, int n_layers, int B, int T, in
     if (rc == SKP_OK) rc = tc_encode_map(&O->k_map[l][1], s_lo, s2, T, B * a.heads, TC_BN);
     if (rc != SKP_OK) return rc;
     O->k_ptr[l][0] = k_hi; O->k_ptr[l][1] = k_lo;
+    O->s_ptr[l][0] = s_hi; O->s_ptr[l][1] = s_lo;
     O->heads[l] = a.heads; O->d[l] = g.kw; O->k_shared[l] = 0; O->head_base[l] = base;
     O->weight[l] = a.weight / a.heads; O->scale[l] = a.scale;
     O->win_s[l] = a.s; O->win_nr[l] = g.nr;
