@@ -318,7 +318,7 @@ def ours(args):
     flops_fwd = attn_algorithmic_flops(cfg["model"], cfg["T"], cfg["R"], len(cfg["layers"])) * imgs_per_call
     peak = peaks["bf16_tflops_sustained"]
 
-    def roof(symbol, label, flops_call, kernel, profile="r1d_attn_tc_full.txt"):
+    def roof(symbol, label, flops_call, kernel, profile="r1e_attn_tc_full.txt"):
         t = tm.get(symbol, {"calls": 0, "ms": 0.0})
         ach = flops_call * t["calls"] / (t["ms"] / 1e3) / 1e12 if t["ms"] > 0 else None
         return {"kernel": label, "bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
@@ -328,9 +328,9 @@ def ours(args):
                 "ms_per_launch": t["ms"] / max(1, t["calls"]), "algorithmic_flops_per_launch": flops_call,
                 "ms_per_step": t["ms"] / args.steps}
 
-    r_fwd = roof("skp_attn_map_fwd", "skp_attn_map_fwd (operand prep + attn_map_fwd_tc_kernel, bf16x3 on tcgen05)",
+    r_fwd = roof("skp_attn_map_fwd", "skp_attn_map_fwd (native-resolution logit GEMM + attn_map_fwd_tc_kernel, bf16x3 on tcgen05)",
                  flops_fwd, "attn_map_fwd_tc_kernel")
-    r_bwd = roof("skp_attn_map_bwd", "skp_attn_map_bwd (attn_map_bwd_tc_kernel: recompute + dQ/dK on tcgen05, bicubic adjoint)",
+    r_bwd = roof("skp_attn_map_bwd", "skp_attn_map_bwd (attn_map_bwd_tc_kernel: softmax recompute + dz = dS^T W (16^2 layers) or dQ'/dK + bicubic adjoint (32^2 layer) on tcgen05, native-resolution dq/dk GEMMs)",
                  2.0 * flops_fwd, "attn_map_bwd_tc_kernel")
     roofline, roofline_other = (r_bwd, r_fwd) if r_bwd["ms_per_step"] > r_fwd["ms_per_step"] else (r_fwd, r_bwd)
     total_kernel_ms = sum(v["ms"] for v in tm.values())
