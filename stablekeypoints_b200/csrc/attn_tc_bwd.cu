@@ -246,12 +246,12 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       for (int u = u_begin; u < u_end; ++u, ++it, x = bw_next(P, x)) {
         const int h = P.ops.heads[x.l];
         const int st = it & 1;
-        ptx::mbar_wait(bar_qempty(st), ((it >> 1) & 1u) ^ 1u);
+        ptx::mbar_wait_hint(bar_qempty(st), ((it >> 1) & 1u) ^ 1u, 2000u);
         const int r0 = LR ? x.r0 : 0;
         const bool need_k = LR ? (x.hg != prev_hg || x.b != prev_b || r0 != prev_r0)
                                : (x.hg != prev_hg || (!P.ops.k_shared[x.l] && x.b != prev_b));
         const bool need_ksel = need_k || x.b != prev_b;
-        if (need_ksel && it > 0) ptx::mbar_wait(bar_qempty((it - 1) & 1), ((it - 1) >> 1) & 1u);   // previous unit done with k / k_sel
+        if (need_ksel && it > 0) ptx::mbar_wait_hint(bar_qempty((it - 1) & 1), ((it - 1) >> 1) & 1u, 2000u);   // previous unit done with k / k_sel
         const uint32_t bytes = SM::kQStage + (need_k ? SM::kKBytes : 0) + (need_ksel ? SM::kKselBytes : 0);
         ptx::mbar_arrive_expect_tx(bar_qfull(st), bytes);
         const int qz = x.b * h + x.head;
@@ -286,7 +286,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       auto issue_S = [&](int l, uint32_t jt) {
         const uint32_t qs = base + SM::kQOff + (jt & 1) * SM::kQStage;
         long long c0 = clock64();
-        ptx::mbar_wait(bar_qfull(jt & 1), (jt >> 1) & 1u);
+        ptx::mbar_wait_hint(bar_qfull(jt & 1), (jt >> 1) & 1u, 2000u);
         ptx::tc_fence_after();
         pf_q += clock64() - c0;
         c0 = clock64();
@@ -323,7 +323,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         s_issued = false;
         // ---- wait for dS (bf16, [px][tok]) in shared memory
         long long c0 = clock64();
-        ptx::mbar_wait(bar_dsfull, it & 1u);
+        ptx::mbar_wait_hint(bar_dsfull, it & 1u, 2000u);
         ptx::tc_fence_after();
         pf_ds += clock64() - c0;
         // LR: the softmax warps are done with S(u), so S(u+1) can run AHEAD of the dz product of this unit (they start
@@ -756,15 +756,15 @@ attn_map_bwd_lr128_kernel(const __grid_constant__ BwdParams P) {
         BwUnit x = bw_decode(P, u_begin), px = x;
         for (int u = u_begin; u < u_end; ++u, ++it, px = x, x = bw_next(P, x)) {
           const uint32_t hs = it % 3, ls = it & 1;
-          ptx::mbar_wait(bar_whempty(hs), ((it / 3) & 1u) ^ 1u);
+          ptx::mbar_wait_hint(bar_whempty(hs), ((it / 3) & 1u) ^ 1u, 2000u);
           ptx::mbar_arrive_expect_tx(bar_whfull(hs), TC_A_BYTES);
           ptx::tma_load_3d(base + SM::kWhiOff + hs * TC_A_BYTES, &P.ops.q_map[x.l][0], bar_whfull(hs), 0, 0, x.tile);
-          ptx::mbar_wait(bar_wlempty(ls), ((it >> 1) & 1u) ^ 1u);
+          ptx::mbar_wait_hint(bar_wlempty(ls), ((it >> 1) & 1u) ^ 1u, 2000u);
           ptx::mbar_arrive_expect_tx(bar_wlfull(ls), TC_A_BYTES);
           ptx::tma_load_3d(base + SM::kWloOff + ls * TC_A_BYTES, &P.ops.q_map[x.l][1], bar_wlfull(ls), 0, 0, x.tile);
           if (it == 0 || new_window(px, x)) {
             const uint32_t kb = wc & 1;
-            ptx::mbar_wait(bar_kempty(kb), ((wc >> 1) & 1u) ^ 1u);
+            ptx::mbar_wait_hint(bar_kempty(kb), ((wc >> 1) & 1u) ^ 1u, 2000u);
             ptx::mbar_arrive_expect_tx(bar_kfull(kb), SM::kWinBytes);
             const uint32_t wb = base + SM::kWinOff + kb * SM::kWinBytes;
             const int qz = x.b * P.ops.heads[x.l] + x.head, k0 = x.r0 * P.s[x.l];
@@ -788,13 +788,13 @@ attn_map_bwd_lr128_kernel(const __grid_constant__ BwdParams P) {
         auto issue_S = [&]() {
           if (js == 0 || new_window(pxs, xs)) {
             if (js > 0) ptx::umma_commit(bar_kempty((wc - 1) & 1));    // every product on the previous window has been issued
-            ptx::mbar_wait(bar_kfull(wc & 1), (wc >> 1) & 1u);
+            ptx::mbar_wait_hint(bar_kfull(wc & 1), (wc >> 1) & 1u, 2000u);
             ++wc;
           }
           const uint32_t kb = (wc - 1) & 1;
           long long c0 = clock64();
-          ptx::mbar_wait(bar_whfull(js % 3), (js / 3) & 1u);
-          ptx::mbar_wait(bar_wlfull(js & 1), (js >> 1) & 1u);
+          ptx::mbar_wait_hint(bar_whfull(js % 3), (js / 3) & 1u, 2000u);
+          ptx::mbar_wait_hint(bar_wlfull(js & 1), (js >> 1) & 1u, 2000u);
           ptx::tc_fence_after();
           pf_q += clock64() - c0;
           c0 = clock64();
@@ -827,7 +827,7 @@ attn_map_bwd_lr128_kernel(const __grid_constant__ BwdParams P) {
         for (int i = 0; i < n; ++i) {
           const BwUnit nxu = bw_next(P, x);
           long long c0 = clock64();
-          ptx::mbar_wait(bar_dsfull(i & 1), (i >> 1) & 1u);
+          ptx::mbar_wait_hint(bar_dsfull(i & 1), (i >> 1) & 1u, 2000u);
           ptx::tc_fence_after();
           pf_ds += clock64() - c0;
           c0 = clock64();
