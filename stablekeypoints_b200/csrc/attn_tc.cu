@@ -646,7 +646,8 @@ bool attn_map_tc_supported(const skp_attn_layer* h_layers, int n_layers, int B, 
 }
 
 
-size_t attn_map_tc_workspace(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int precision) {
+// staged operands: upsampled q' and k, bf16 hi (+ lo)
+size_t attn_map_staged_workspace(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int precision) {
   const int nbuf = precision == SKP_PREC_TC_BF16 ? 1 : 2;
   size_t total = 0;
   for (int l = 0; l < n_layers; ++l) {
@@ -654,11 +655,20 @@ size_t attn_map_tc_workspace(const skp_attn_layer* h_layers, int n_layers, int B
     total += nbuf * tc_align_up(static_cast<size_t>(B) * R * R * a.C * 2, 1024);
     total += nbuf * tc_align_up(static_cast<size_t>(a.k_shared ? 1 : B) * T * a.C * 2, 1024);
   }
-  if (nbuf == 2 && attn_map_lr_supported(h_layers, n_layers, B, T, R, 0)) {
-    const size_t lr = attn_map_lr_workspace(h_layers, n_layers, B, T, R);
-    total = total > lr ? total : lr;
-  }
   return total + 1024;
+}
+
+// parity mode on shapes whose interpolation windows are narrow: upsample after the logits (attn_tc_lr.cu), no staged
+// q'.  SKP_FWD_LR=0 keeps the staged-operand path (A/B measurements, cross-checks); read per call.
+static bool fwd_uses_lr(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int n_idx, int precision) {
+  const char* e = getenv("SKP_FWD_LR");
+  return precision != SKP_PREC_TC_BF16 && !(e && atoi(e) == 0) && attn_map_lr_supported(h_layers, n_layers, B, T, R, n_idx);
+}
+
+// what the forward call will need: 0.45 GB for 8 SD-2.1 images on the upsample-after-logits path, 2.35 GB staged
+size_t attn_map_tc_workspace(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int precision) {
+  if (fwd_uses_lr(h_layers, n_layers, B, T, R, 0, precision)) return attn_map_lr_workspace(h_layers, n_layers, B, T, R) + 1024;
+  return attn_map_staged_workspace(h_layers, n_layers, B, T, R, precision);
 }
 
 template <int NPROD, int NSPLIT, bool SELECT>
@@ -750,11 +760,7 @@ int attn_map_fwd_tc(const skp_attn_layer* h_layers, int n_layers, int B, int T, 
   const int R2 = R * R;
   TcParams P;
   memset(&P, 0, sizeof(P));
-  // parity mode on shapes whose interpolation windows are narrow: upsample after the logits (attn_tc_lr.cu), no
-  // staged q'.  SKP_FWD_LR=0 keeps the staged-operand path (A/B measurements, cross-checks).
-  const char* lr_env = getenv("SKP_FWD_LR");     // read per call: the tests switch it to cover both paths
-  const bool lr_enabled = !(lr_env && atoi(lr_env) == 0);
-  const bool lr = x3 && lr_enabled && attn_map_lr_supported(h_layers, n_layers, B, T, R, token_idx ? n_idx : 0);
+  const bool lr = fwd_uses_lr(h_layers, n_layers, B, T, R, token_idx ? n_idx : 0, precision);
   int rc = lr ? tc_prepare_lr(h_layers, n_layers, B, T, R, workspace, st, &P.ops, nullptr)
               : tc_prepare(h_layers, n_layers, B, T, R, x3, workspace, st, &P.ops, nullptr);
   if (rc != SKP_OK) return rc;

@@ -56,6 +56,7 @@ int tc_prepare_lr(const skp_attn_layer* h_layers, int n_layers, int B, int T, in
 
 bool attn_map_tc_supported(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int n_idx);
 size_t attn_map_tc_workspace(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int precision);
+size_t attn_map_staged_workspace(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int precision);
 // runs the prep kernels on `st`, encodes the tensor maps; *ws_end = first free byte of the workspace
 int tc_prepare(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, bool x3, void* workspace, cudaStream_t st,
                TcOperands* out, char** ws_end);

@@ -1039,7 +1039,7 @@ static bool bwd_layer_lr(const skp_attn_layer& a, int R) {
 }
 
 size_t attn_map_bwd_tc_workspace(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int precision) {
-  size_t total = attn_map_tc_workspace(h_layers, n_layers, B, T, R, precision) + 4096;
+  size_t total = 8192;
   const int nbuf = precision == SKP_PREC_TC_BF16 ? 1 : 2;
   for (int l = 0; l < n_layers; ++l) {
     const skp_attn_layer& a = h_layers[l];
@@ -1047,6 +1047,7 @@ size_t attn_map_bwd_tc_workspace(const skp_attn_layer* h_layers, int n_layers, i
     const size_t kd = lr ? static_cast<size_t>(a.s) * a.s : a.C / a.heads;     // selected-token rows: k rows, or (LR) logit rows
     total += nbuf * tc_align_up(static_cast<size_t>(B) * a.heads * BW_SEL * kd * 2, 1024);
     if (lr) total += attn_map_lr_workspace(&a, 1, B, T, R) + lr_bwd_post_workspace(a, B, T) + 2048;
+    else total += attn_map_staged_workspace(&a, 1, B, T, R, precision);
   }
   return total + 1024;
 }
