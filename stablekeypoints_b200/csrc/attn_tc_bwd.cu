@@ -47,6 +47,7 @@ struct BwdParams {
   int64_t idx_stride;
   const int64_t* token_idx;
   const float* dmaps_sel;                   // (B, n_idx, R2)
+  const float* dpT;                         // pixel-major copy (B, R2, 16), planes j >= n_idx zero
   const float* row_stats;                   // (B, total_heads, R2, 2)
   unsigned long long* prof;                 // SKP_BWD_DBG & 8: per-phase cycle counters of CTA 0
   int dbg;                                  // SKP_BWD_DBG bits (profiling experiments only): 1 no reductions, 2 no adjoint, 4 no drain
@@ -117,6 +118,17 @@ __device__ __host__ constexpr uint32_t bw_idesc(int M, int N, int a_mn, int b_mn
 }
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+// dmaps_sel (B, n_idx, R2) -> (B, R2, 16): the softmax threads read the n_idx upstream gradients of their pixel row
+__global__ void bw_transpose_dp_kernel(const float* __restrict__ in, int n_idx, int R2, float* __restrict__ out) {
+  const int b = blockIdx.y, p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= R2) return;
+  float v[BW_SEL];
+#pragma unroll
+  for (int j = 0; j < BW_SEL; ++j) v[j] = j < n_idx ? in[(static_cast<int64_t>(b) * n_idx + j) * R2 + p] : 0.0f;
+  float4* o = reinterpret_cast<float4*>(out + (static_cast<int64_t>(b) * R2 + p) * BW_SEL);
+#pragma unroll
+  for (int q = 0; q < BW_SEL / 4; ++q) o[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
 }
 __global__ void bw_window_table_kernel(int s, int R, int nr, int tiles, unsigned char* tab) {
   for (int t = threadIdx.x; t < tiles; t += blockDim.x) tab[t] = static_cast<unsigned char>(lr_window_row0(t, s, R, nr));
@@ -329,7 +341,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         // LR: the softmax warps are done with S(u), so S(u+1) can run AHEAD of the dz product of this unit (they start
         // on the next unit ~1200 cycles earlier and only need dz(u) retired before their first dS store).  Not when
         // the next unit reloads k / k_sel: those single buffers are only refilled after this unit's MMAs retire.
-        if (LR && u + 1 < u_end && nxu.hg == x.hg && nxu.b == x.b && nxu.r0 == x.r0) {
+        if (LR && u + 1 < u_end && nxu.hg == x.hg && nxu.b == x.b && nxu.r0 == x.r0 && !(P.dbg & 32)) {
           issue_S(nxu.l, it + 1);
           s_issued = true;
         }
@@ -382,14 +394,20 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
     const int R = P.R;
     uint32_t it = 0;
     int prev_l = -1, prev_b = -1;
+    int tk[BW_SEL];                            // token ids of the selected planes of the current image
     float2 nx_ml = make_float2(0.f, 1.f);
     float nx_dp[BW_SEL];
     auto load_row = [&](const BwUnit& y, float2& ml, float (&dpr)[BW_SEL]) {
       const int pp = y.tile * TC_BM + row;
       ml = __ldg(reinterpret_cast<const float2*>(P.row_stats) + (static_cast<int64_t>(y.b) * P.heads_all + P.ghead[y.l] + y.head) * P.R2 + pp);
+      // upstream gradients of the row: one 64-byte row of the pixel-major copy (4 x 16-byte loads instead of 16 scalar
+      // loads from 16 planes)
+      const float4* g4 = reinterpret_cast<const float4*>(P.dpT) + (static_cast<int64_t>(y.b) * P.R2 + pp) * (BW_SEL / 4);
 #pragma unroll
-      for (int j = 0; j < BW_SEL; ++j)
-        dpr[j] = j < P.n_idx ? __ldg(P.dmaps_sel + (static_cast<int64_t>(y.b) * P.n_idx + j) * P.R2 + pp) : 0.0f;
+      for (int q = 0; q < BW_SEL / 4; ++q) {
+        const float4 g = __ldg(g4 + q);
+        dpr[4 * q] = g.x; dpr[4 * q + 1] = g.y; dpr[4 * q + 2] = g.z; dpr[4 * q + 3] = g.w;
+      }
     };
     long long pf[6] = {0, 0, 0, 0, 0, 0}, c_end = clock64();   // profiler (SKP_BWD_DBG & 8), kept in registers
     bool mma_pending = false;      // LR: the wait for the previous unit's dz product is deferred to the first dS store
@@ -419,6 +437,8 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         }
         if (stid < BW_SEL) tok_s[stid] = stid < P.n_idx ? static_cast<int>(P.token_idx[x.b * P.idx_stride + stid]) : -1;
         named_bar_sync(1, TC_SOFTMAX_THREADS);
+#pragma unroll
+        for (int j = 0; j < BW_SEL; ++j) tk[j] = tok_s[j];      // registers: the per-unit loops below read them 32 times
         prev_l = x.l;
         prev_b = x.b;
       }
@@ -446,7 +466,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         ptx::tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < BW_SEL; ++j) {
-          const int t = tok_s[j];
+          const int t = tk[j];
           const float ps = (t >= 0 && t < P.T) ? ptx::ex2(__uint_as_float(sv[j]) - m) * inv_l : 0.0f;
           delta = fmaf(ps, dp[j], delta);
           dp[j] *= ps;                          // dp[j] now holds P_sel[j] * dP[j]
@@ -489,7 +509,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       }
 #pragma unroll
       for (int j = 0; j < BW_SEL; ++j) {
-        const int t = tok_s[j] - tok0;
+        const int t = tk[j] - tok0;
         if (j < P.n_idx && t >= col0 && t < col0 + ncol) {
           const uint32_t off = (t >> 6) * 16384 + row * 128 + ((((t & 63) >> 3) ^ (row & 7)) << 4) + (t & 7) * 2;
           __nv_bfloat16* e = reinterpret_cast<__nv_bfloat16*>(ds_ptr + off);
@@ -861,14 +881,20 @@ attn_map_bwd_lr128_kernel(const __grid_constant__ BwdParams P) {
     const uint32_t lane_off = static_cast<uint32_t>(quad * 32) << 16;
     uint32_t it = 0;
     int prev_l = -1, prev_b = -1;
+    int tk[BW_SEL];                            // token ids of the selected planes of the current image
     float2 nx_ml = make_float2(0.f, 1.f);
     float nx_dp[BW_SEL];
     auto load_row = [&](const BwUnit& y, float2& ml, float (&dpr)[BW_SEL]) {
       const int pp = y.tile * TC_BM + row;
       ml = __ldg(reinterpret_cast<const float2*>(P.row_stats) + (static_cast<int64_t>(y.b) * P.heads_all + P.ghead[y.l] + y.head) * P.R2 + pp);
+      // upstream gradients of the row: one 64-byte row of the pixel-major copy (4 x 16-byte loads instead of 16 scalar
+      // loads from 16 planes)
+      const float4* g4 = reinterpret_cast<const float4*>(P.dpT) + (static_cast<int64_t>(y.b) * P.R2 + pp) * (BW_SEL / 4);
 #pragma unroll
-      for (int j = 0; j < BW_SEL; ++j)
-        dpr[j] = j < P.n_idx ? __ldg(P.dmaps_sel + (static_cast<int64_t>(y.b) * P.n_idx + j) * P.R2 + pp) : 0.0f;
+      for (int q = 0; q < BW_SEL / 4; ++q) {
+        const float4 g = __ldg(g4 + q);
+        dpr[4 * q] = g.x; dpr[4 * q + 1] = g.y; dpr[4 * q + 2] = g.z; dpr[4 * q + 3] = g.w;
+      }
     };
     long long pf[6] = {0, 0, 0, 0, 0, 0}, c_end = clock64();
     BwUnit x = bw_decode(P, u_begin), nxu = x;
@@ -880,6 +906,8 @@ attn_map_bwd_lr128_kernel(const __grid_constant__ BwdParams P) {
         named_bar_sync(1, TC_SOFTMAX_THREADS);
         if (stid < BW_SEL) tok_s[stid] = stid < P.n_idx ? static_cast<int>(P.token_idx[x.b * P.idx_stride + stid]) : -1;
         named_bar_sync(1, TC_SOFTMAX_THREADS);
+#pragma unroll
+        for (int j = 0; j < BW_SEL; ++j) tk[j] = tok_s[j];      // registers: the per-unit loops below read them 32 times
         prev_l = x.l;
         prev_b = x.b;
       }
@@ -903,7 +931,7 @@ attn_map_bwd_lr128_kernel(const __grid_constant__ BwdParams P) {
         ptx::tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < BW_SEL; ++j) {
-          const int t = tok_s[j];
+          const int t = tk[j];
           const float ps = (t >= 0 && t < P.T) ? ptx::ex2(__uint_as_float(sv[j]) - m) * inv_l : 0.0f;
           delta = fmaf(ps, dp[j], delta);
           dp[j] *= ps;                          // dp[j] now holds P_sel[j] * dP[j]
@@ -948,7 +976,7 @@ attn_map_bwd_lr128_kernel(const __grid_constant__ BwdParams P) {
       }
 #pragma unroll
       for (int j = 0; j < BW_SEL; ++j) {
-        const int t = tok_s[j] - tok0;
+        const int t = tk[j] - tok0;
         if (j < P.n_idx && t >= col0 && t < col0 + ncol) {
           const uint32_t off = (t >> 6) * 16384 + row * 128 + ((((t & 63) >> 3) ^ (row & 7)) << 4) + (t & 7) * 2;
           __nv_bfloat16* e = reinterpret_cast<__nv_bfloat16*>(ds_ptr + off);
@@ -1039,7 +1067,7 @@ static bool bwd_layer_lr(const skp_attn_layer& a, int R) {
 }
 
 size_t attn_map_bwd_tc_workspace(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int precision) {
-  size_t total = 8192;
+  size_t total = 8192 + tc_align_up(static_cast<size_t>(B) * R * R * BW_SEL * 4, 1024);
   const int nbuf = precision == SKP_PREC_TC_BF16 ? 1 : 2;
   for (int l = 0; l < n_layers; ++l) {
     const skp_attn_layer& a = h_layers[l];
@@ -1064,8 +1092,8 @@ static int launch_bwd(const BwdParams& P, cudaStream_t st) {
 
 // one launch of the main kernel over a subset of the captured layers (`sub`, with their global head offsets)
 static int bwd_launch_group(const skp_attn_layer* sub, const int* ghead, int n_sub, int heads_all, bool lr, int B, int T, int R,
-                            const int64_t* token_idx, int n_idx, int64_t idx_stride, const float* dmaps_sel, const float* row_stats,
-                            bool x3, char** ws_io, cudaStream_t st) {
+                            const int64_t* token_idx, int n_idx, int64_t idx_stride, const float* dmaps_sel, const float* dpT,
+                            const float* row_stats, bool x3, char** ws_io, cudaStream_t st) {
   BwdParams P;
   memset(&P, 0, sizeof(P));
   char* ws = nullptr;
@@ -1111,7 +1139,7 @@ static int bwd_launch_group(const skp_attn_layer* sub, const int* ghead, int n_s
   }
   P.heads_all = heads_all;
   P.B = B; P.T = T; P.R = R; P.R2 = R * R; P.n_idx = n_idx; P.tiles = tiles;
-  P.idx_stride = idx_stride; P.token_idx = token_idx; P.dmaps_sel = dmaps_sel; P.row_stats = row_stats;
+  P.idx_stride = idx_stride; P.token_idx = token_idx; P.dmaps_sel = dmaps_sel; P.dpT = dpT; P.row_stats = row_stats;
   P.n_units = P.ops.total_heads * B * P.tiles;
   if (const char* e = getenv("SKP_BWD_DBG")) P.dbg = atoi(e);
   static unsigned long long* d_prof = nullptr;
@@ -1179,11 +1207,15 @@ int attn_map_bwd_tc(const skp_attn_layer* h_layers, int n_layers, int B, int T, 
     ghead[gi][n_group[gi]++] = heads_all;
     heads_all += h_layers[l].heads;
   }
-  char* ws = reinterpret_cast<char*>(workspace);
+  char* ws = reinterpret_cast<char*>(tc_align_up(reinterpret_cast<size_t>(workspace), 1024));
+  float* dpT = reinterpret_cast<float*>(ws);
+  ws += tc_align_up(static_cast<size_t>(B) * R * R * BW_SEL * 4, 1024);
+  bw_transpose_dp_kernel<<<(::skp::note_launch(), dim3((R * R + 255) / 256, B)), 256, 0, st>>>(dmaps_sel, n_idx, R * R, dpT);
+  SKP_LAUNCH_CHECK();
   for (int gi = 0; gi < 2; ++gi) {
     if (n_group[gi] == 0) continue;
     int rc = bwd_launch_group(group[gi], ghead[gi], n_group[gi], heads_all, gi == 1, B, T, R, token_idx, n_idx, idx_stride, dmaps_sel,
-                              row_stats, x3, &ws, st);
+                              dpT, row_stats, x3, &ws, st);
     if (rc != SKP_OK) return rc;
   }
   return SKP_OK;
