@@ -3,4 +3,4 @@
 set -e
 cd "$(dirname "$0")/stablekeypoints_b200/csrc"
 nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -shared \
-     -o ../libskp_b200.so api.cu readout.cu resample.cu attn_simt.cu attn_api.cu attn_tc.cu attn_tc_bwd.cu attn_tc_lr.cu "$@"
+     -o ../libskp_b200.so *.cu "$@"
