@@ -96,7 +96,7 @@ struct BwSmem {
   static constexpr int kKselBytes = (NPROD == 3 ? 2 : 1) * BW_KSEL_BYTES;
   static constexpr int kDsOff = kKselOff + kKselBytes;              // dS tile; aliased by the fp32 dQ' staging
   static constexpr int kWxtOff = kDsOff + BW_DS_BYTES;
-  static constexpr int kBarOff = kWxtOff + BW_WXT_FLOATS * 4;       // q_full[2], q_empty[2], s_full, ds_full, mma_done
+  static constexpr int kBarOff = kWxtOff + BW_WXT_FLOATS * 4;       // q_full[2], q_empty[2], s_full, ds_full, mma_done, sel_full
   static constexpr int kTmemPtrOff = kBarOff + 8 * 8;
   static constexpr int kTokOff = kTmemPtrOff + 8;                   // int tok[16]
   static constexpr int kTotal = kTokOff + 4 * BW_SEL;
@@ -192,6 +192,9 @@ __device__ __forceinline__ bool bw_flush_between(const BwdParams& P, const BwUni
 
 // 12 warps = 3 warpgroups: {TMA, MMA, 2 idle} shrink to 56 registers, the 8 softmax warps grow to 224
 constexpr int BW_THREADS = 384;
+#ifndef BW_LR_HOLD
+#define BW_LR_HOLD 2      // chunks (32 tokens each) of a row's dS kept in registers across the wait for the previous dz product
+#endif
 constexpr int BW_SOFTMAX_WARP0 = 4;
 // LR: "upsample after the logits" gradient.  The dQ' / dK products and the bicubic adjoint are replaced by ONE product
 // dz += dS^T W (tokens x 64 taps, K = 128 pixels; same operand forms as the dK product with the W tile of this pixel
@@ -219,6 +222,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
   const uint32_t bar_sfull = base + SM::kBarOff + 8u * 4;
   const uint32_t bar_dsfull = base + SM::kBarOff + 8u * 5;
   const uint32_t bar_mmadone = base + SM::kBarOff + 8u * 6;
+  const uint32_t bar_selfull = base + SM::kBarOff + 8u * 7;
   volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(base_ptr + SM::kTmemPtrOff);
   volatile int* tok_s = reinterpret_cast<volatile int*>(base_ptr + SM::kTokOff);
   float* wxt = reinterpret_cast<float*>(base_ptr + SM::kWxtOff);
@@ -232,6 +236,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
     ptx::mbar_init(bar_sfull, 1);
     ptx::mbar_init(bar_dsfull, TC_SOFTMAX_THREADS);
     ptx::mbar_init(bar_mmadone, 1);
+    ptx::mbar_init(bar_selfull, 1);
     ptx::fence_barrier_init();
   }
   if (warp == 1) {
@@ -304,23 +309,41 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         c0 = clock64();
         const uint32_t id_S = bw_idesc(TC_BM, TC_BN, 0, 0), id_sel = bw_idesc(TC_BM, BW_SEL, 0, 0);
         const int nk16 = P.ops.d[l] / 16;
+        // The selected tokens' logits go out two per 256-token MMA during the first half of the product and get their
+        // own barrier: the softmax warps turn them into the row's delta (16 serial exponentials) while the second half
+        // still runs, and the N = 16 MMAs (latency-bound on one accumulator) hide under the N = 256 ones.
+        const int n_selblk = (nk16 + 1) >> 1;       // S k-blocks that carry two S_sel k-blocks each
         for (int kk = 0; kk < nk16; ++kk) {
           const uint64_t a_hi = bw_desc(qs + kk * 32, 16, 1024), b_hi = bw_desc(ks + kk * 32, 16, 1024);
-          const uint64_t s_hi = bw_desc(ksel + kk * 32, 16, 1024);
+          const int k0 = 2 * kk, k1 = 2 * kk + 1;
+          const bool sel0 = kk < n_selblk, sel1 = sel0 && k1 < nk16;
+          const uint64_t p_hi = bw_desc(qs + k0 * 32, 16, 1024), r_hi = bw_desc(qs + k1 * 32, 16, 1024);
+          const uint64_t s0_hi = bw_desc(ksel + k0 * 32, 16, 1024), s1_hi = bw_desc(ksel + k1 * 32, 16, 1024);
           if (NPROD == 3) {
             const uint64_t a_lo = bw_desc(qs + TC_A_BYTES + kk * 32, 16, 1024);
             const uint64_t b_lo = bw_desc(ks + TC_B_BYTES + kk * 32, 16, 1024);
-            const uint64_t s_lo = bw_desc(ksel + BW_KSEL_BYTES + kk * 32, 16, 1024);
+            const uint64_t p_lo = bw_desc(qs + TC_A_BYTES + k0 * 32, 16, 1024), r_lo = bw_desc(qs + TC_A_BYTES + k1 * 32, 16, 1024);
+            const uint64_t s0_lo = bw_desc(ksel + BW_KSEL_BYTES + k0 * 32, 16, 1024);
+            const uint64_t s1_lo = bw_desc(ksel + BW_KSEL_BYTES + k1 * 32, 16, 1024);
             ptx::umma_bf16(tm_S, a_hi, b_lo, id_S, kk != 0);
+            if (sel0) {
+              ptx::umma_bf16(tm_sel, p_hi, s0_lo, id_sel, kk != 0);
+              ptx::umma_bf16(tm_sel, p_lo, s0_hi, id_sel, 1u);
+            }
             ptx::umma_bf16(tm_S, a_lo, b_hi, id_S, 1u);
+            if (sel0) ptx::umma_bf16(tm_sel, p_hi, s0_hi, id_sel, 1u);
+            if (sel1) ptx::umma_bf16(tm_sel, r_hi, s1_lo, id_sel, 1u);
             ptx::umma_bf16(tm_S, a_hi, b_hi, id_S, 1u);
-            ptx::umma_bf16(tm_sel, a_hi, s_lo, id_sel, kk != 0);
-            ptx::umma_bf16(tm_sel, a_lo, s_hi, id_sel, 1u);
-            ptx::umma_bf16(tm_sel, a_hi, s_hi, id_sel, 1u);
+            if (sel1) {
+              ptx::umma_bf16(tm_sel, r_lo, s1_hi, id_sel, 1u);
+              ptx::umma_bf16(tm_sel, r_hi, s1_hi, id_sel, 1u);
+            }
           } else {
             ptx::umma_bf16(tm_S, a_hi, b_hi, id_S, kk != 0);
-            ptx::umma_bf16(tm_sel, a_hi, s_hi, id_sel, kk != 0);
+            if (sel0) ptx::umma_bf16(tm_sel, p_hi, s0_hi, id_sel, kk != 0);
+            if (sel1) ptx::umma_bf16(tm_sel, r_hi, s1_hi, id_sel, 1u);
           }
+          if (kk + 1 == n_selblk) ptx::umma_commit(bar_selfull);
         }
         ptx::umma_commit(bar_sfull);
         pf_is += clock64() - c0;
@@ -374,7 +397,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         dk_fresh = bw_flush_between<LR>(P, x, nxu, u + 1 >= u_end);
         x = nxu;
       }
-      if (P.prof && blockIdx.x == 0) {
+      if (P.prof && blockIdx.x == ((P.dbg >> 6) & 1)) {
         P.prof[0] = pf_q; P.prof[1] = pf_ds; P.prof[8] = pf_is; P.prof[9] = pf_id;
       }
     }
@@ -451,11 +474,13 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       for (int j = 0; j < BW_SEL; ++j) dp[j] = wgt * nx_dp[j];
       // LR: next unit's row statistics / upstream gradients go out now and land under this unit's dS pass (there is
       // no long MMA wait at the end of the unit to hide them any more)
-      if (LR && u + 1 < u_end && !(P.dbg & 16)) load_row(nxu, nx_ml, nx_dp);
+      // Unconditional (the last unit re-reads its own row): a load under a branch made the compiler copy the loaded
+      // registers right behind it, i.e. wait for the whole memory round trip at the loop top (780 cycles per unit).
+      if (LR) load_row(u + 1 < u_end ? nxu : x, nx_ml, nx_dp);
 
       long long c1 = clock64();
       pf[5] += c1 - c_end;                      // loop top: decode, prefetch issue, table rebuilds
-      ptx::mbar_wait(bar_sfull, it & 1u);
+      ptx::mbar_wait(bar_selfull, it & 1u);
       ptx::tc_fence_after();
       pf[0] += clock64() - c1;
       c1 = clock64();
@@ -475,35 +500,61 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       // ---- dS = P * (dP - delta): dense part -P*delta for my 128 columns, then the n_idx corrections
       const float nd = -delta * inv_l;
       {
+        long long c2 = clock64();
+        ptx::mbar_wait(bar_sfull, it & 1u);
+        ptx::tc_fence_after();
+        const long long c3 = clock64();
+        pf[0] += c3 - c2;
+        c1 += c3 - c2;                          // the dS slot of the profile excludes this wait
+      }
+      {
         uint32_t v[2][32];
-        const bool full = ncol == 128;
+        // LR: the first HOLD chunks of dS stay packed in registers until the previous unit's dz product has retired
+        // (it still reads the single dS tile): the exponentials of those chunks run under that product
+        constexpr int HOLD = LR ? BW_LR_HOLD : 1;
+        uint32_t pk[4][16];
+        auto store_chunk = [&](int c) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int cc = col0 + 32 * c + 8 * q;
+            const uint32_t off = (cc >> 6) * 16384 + row * 128 + ((((cc & 63) >> 3) ^ (row & 7)) << 4);
+            *reinterpret_cast<uint4*>(ds_ptr + off) = make_uint4(pk[c][4 * q], pk[c][4 * q + 1], pk[c][4 * q + 2], pk[c][4 * q + 3]);
+          }
+        };
         ptx::tmem_ld32(tm_S + lane_off + col0, v[0]);
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           ptx::tmem_ld_wait();
           if (c < 3) ptx::tmem_ld32(tm_S + lane_off + col0 + 32 * (c + 1), v[(c + 1) & 1]);
-          uint32_t pk[16];
-          if (LR && c == 0 && mma_pending) {
-            // the dS tile is still being read by the previous unit's dz product
-            ptx::mbar_wait(bar_mmadone, (it - 1) & 1u);
-            mma_pending = false;
-          }
+          if (32 * (c + 1) <= ncol) {
+            // all 32 columns of the chunk are tokens (all but the chunk holding T's end): no per-column range test
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            float e0 = ptx::ex2(__uint_as_float(v[c & 1][2 * j]) - m) * nd;
-            float e1 = ptx::ex2(__uint_as_float(v[c & 1][2 * j + 1]) - m) * nd;
-            if (!full) {
+            for (int j = 0; j < 16; ++j) {
+              const float e0 = ptx::ex2(__uint_as_float(v[c & 1][2 * j]) - m) * nd;
+              const float e1 = ptx::ex2(__uint_as_float(v[c & 1][2 * j + 1]) - m) * nd;
+              const __nv_bfloat162 h2 = __floats2bfloat162_rn(e0, e1);
+              pk[c][j] = *reinterpret_cast<const uint32_t*>(&h2);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              float e0 = ptx::ex2(__uint_as_float(v[c & 1][2 * j]) - m) * nd;
+              float e1 = ptx::ex2(__uint_as_float(v[c & 1][2 * j + 1]) - m) * nd;
               e0 = (32 * c + 2 * j < ncol) ? e0 : 0.0f;
               e1 = (32 * c + 2 * j + 1 < ncol) ? e1 : 0.0f;
+              const __nv_bfloat162 h2 = __floats2bfloat162_rn(e0, e1);
+              pk[c][j] = *reinterpret_cast<const uint32_t*>(&h2);
             }
-            const __nv_bfloat162 h2 = __floats2bfloat162_rn(e0, e1);
-            pk[j] = *reinterpret_cast<const uint32_t*>(&h2);
           }
+          if (c + 1 == HOLD) {
+            if (LR && mma_pending) {
+              ptx::mbar_wait(bar_mmadone, (it - 1) & 1u);
+              mma_pending = false;
+            }
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const int cc = col0 + 32 * c + 8 * q;
-            const uint32_t off = (cc >> 6) * 16384 + row * 128 + ((((cc & 63) >> 3) ^ (row & 7)) << 4);
-            *reinterpret_cast<uint4*>(ds_ptr + off) = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+            for (int cc = 0; cc <= c; ++cc) store_chunk(cc);
+          } else if (c + 1 > HOLD) {
+            store_chunk(c);
           }
         }
       }
@@ -526,7 +577,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
 
       // next unit's row statistics / upstream gradients: issued here, where this thread would only spin
       // on the dQ/dK MMAs, they are back long before the next loop top
-      if (!LR && u + 1 < u_end && !(P.dbg & 16)) load_row(nxu, nx_ml, nx_dp);
+      if (!LR) load_row(u + 1 < u_end ? nxu : x, nx_ml, nx_dp);
       // ---- dQ' tile: TMEM -> fp32 staging (aliases the dS tile, free once the MMAs are done)
       const bool lr_flush = LR && bw_flush_between<true>(P, x, nxu, u + 1 >= u_end);
       if (!LR || lr_flush) {
@@ -675,7 +726,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         ptx::tc_fence_before();
       }
     }
-    if (P.prof && blockIdx.x == 0 && stid == 0) {
+    if (P.prof && blockIdx.x == ((P.dbg >> 6) & 1) && stid == 0) {
       for (int i = 0; i < 5; ++i) P.prof[2 + i] = pf[i];
       P.prof[7] = it;
       P.prof[10] = pf[5];
@@ -864,7 +915,7 @@ attn_map_bwd_lr128_kernel(const __grid_constant__ BwdParams P) {
           if (i + 2 < n) issue_S();          // the softmax warps have read S(i): its accumulator takes S(i+2)
           x = nxu;
         }
-        if (P.prof && blockIdx.x == 0) {
+        if (P.prof && blockIdx.x == ((P.dbg >> 6) & 1)) {
           P.prof[0] = pf_q; P.prof[1] = pf_ds; P.prof[8] = pf_is; P.prof[9] = pf_id;
         }
       }
@@ -916,7 +967,7 @@ attn_map_bwd_lr128_kernel(const __grid_constant__ BwdParams P) {
       float dp[BW_SEL];
 #pragma unroll
       for (int j = 0; j < BW_SEL; ++j) dp[j] = wgt * nx_dp[j];
-      if (u + 1 < u_end) load_row(nxu, nx_ml, nx_dp);       // lands under this unit's dS pass
+      load_row(u + 1 < u_end ? nxu : x, nx_ml, nx_dp);      // lands under this unit's dS pass; unconditional, see the serial kernel
 
       long long c1 = clock64();
       pf[5] += c1 - c_end;
@@ -1019,7 +1070,7 @@ attn_map_bwd_lr128_kernel(const __grid_constant__ BwdParams P) {
       pf[4] += clock64() - c1;
       c_end = clock64();
     }
-    if (P.prof && blockIdx.x == 0 && stid == 0) {
+    if (P.prof && blockIdx.x == ((P.dbg >> 6) & 1) && stid == 0) {
       // printed by the host under the 256-token kernel's labels: s_full wait, [dS] = S_sel part, [fence+arrive] = wait for
       // dz(it-2), [wait mma_done] = dense dS + arrive, [drain+adjoint] = window test + flush
       for (int i = 0; i < 5; ++i) P.prof[2 + i] = pf[i];
