@@ -308,11 +308,37 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         pf_q += clock64() - c0;
         c0 = clock64();
         const uint32_t id_S = bw_idesc(TC_BM, TC_BN, 0, 0), id_sel = bw_idesc(TC_BM, BW_SEL, 0, 0);
-        const int nk16 = P.ops.d[l] / 16;
+        // LR: the K dimension is the 64-tap window (the launcher only sends such layers here): fixed trip count, the
+        // descriptors of the unrolled loop are the stage's base descriptors plus constants
+        const int nk16 = LR ? TC_BK / 16 : P.ops.d[l] / 16;
         // The selected tokens' logits go out two per 256-token MMA during the first half of the product and get their
         // own barrier: the softmax warps turn them into the row's delta (16 serial exponentials) while the second half
         // still runs, and the N = 16 MMAs (latency-bound on one accumulator) hide under the N = 256 ones.
         const int n_selblk = (nk16 + 1) >> 1;       // S k-blocks that carry two S_sel k-blocks each
+        if (P.dbg & 128) {
+          // diagnostic order: S and S_sel of a k-block together (same A operands), both barriers at the end
+#pragma unroll
+          for (int kk = 0; kk < nk16; ++kk) {
+            const uint64_t a_hi = bw_desc(qs + kk * 32, 16, 1024), b_hi = bw_desc(ks + kk * 32, 16, 1024);
+            const uint64_t s_hi = bw_desc(ksel + kk * 32, 16, 1024);
+            if (NPROD == 3) {
+              const uint64_t a_lo = bw_desc(qs + TC_A_BYTES + kk * 32, 16, 1024);
+              const uint64_t b_lo = bw_desc(ks + TC_B_BYTES + kk * 32, 16, 1024);
+              const uint64_t s_lo = bw_desc(ksel + BW_KSEL_BYTES + kk * 32, 16, 1024);
+              ptx::umma_bf16(tm_S, a_hi, b_lo, id_S, kk != 0);
+              ptx::umma_bf16(tm_sel, a_hi, s_lo, id_sel, kk != 0);
+              ptx::umma_bf16(tm_S, a_lo, b_hi, id_S, 1u);
+              ptx::umma_bf16(tm_sel, a_lo, s_hi, id_sel, 1u);
+              ptx::umma_bf16(tm_S, a_hi, b_hi, id_S, 1u);
+              ptx::umma_bf16(tm_sel, a_hi, s_hi, id_sel, 1u);
+            } else {
+              ptx::umma_bf16(tm_S, a_hi, b_hi, id_S, kk != 0);
+              ptx::umma_bf16(tm_sel, a_hi, s_hi, id_sel, kk != 0);
+            }
+          }
+          ptx::umma_commit(bar_selfull);
+        } else
+#pragma unroll
         for (int kk = 0; kk < nk16; ++kk) {
           const uint64_t a_hi = bw_desc(qs + kk * 32, 16, 1024), b_hi = bw_desc(ks + kk * 32, 16, 1024);
           const int k0 = 2 * kk, k1 = 2 * kk + 1;
