@@ -96,8 +96,8 @@ struct BwSmem {
   static constexpr int kKselBytes = (NPROD == 3 ? 2 : 1) * BW_KSEL_BYTES;
   static constexpr int kDsOff = kKselOff + kKselBytes;              // dS tile; aliased by the fp32 dQ' staging
   static constexpr int kWxtOff = kDsOff + BW_DS_BYTES;
-  static constexpr int kBarOff = kWxtOff + BW_WXT_FLOATS * 4;       // q_full[2], q_empty[2], s_full, ds_full, mma_done, sel_full
-  static constexpr int kTmemPtrOff = kBarOff + 8 * 8;
+  static constexpr int kBarOff = kWxtOff + BW_WXT_FLOATS * 4;       // q_full[2], q_empty[2], s_full, ds_full, mma_done, sel_full[2]
+  static constexpr int kTmemPtrOff = kBarOff + 8 * 10;
   static constexpr int kTokOff = kTmemPtrOff + 8;                   // int tok[16]
   static constexpr int kTotal = kTokOff + 4 * BW_SEL;
   static constexpr int kDynamic = kTotal + 1024;
@@ -222,7 +222,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
   const uint32_t bar_sfull = base + SM::kBarOff + 8u * 4;
   const uint32_t bar_dsfull = base + SM::kBarOff + 8u * 5;
   const uint32_t bar_mmadone = base + SM::kBarOff + 8u * 6;
-  const uint32_t bar_selfull = base + SM::kBarOff + 8u * 7;
+  auto bar_selfull = [&](uint32_t i) { return base + SM::kBarOff + 8u * (7 + (i & 1u)); };
   volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(base_ptr + SM::kTmemPtrOff);
   volatile int* tok_s = reinterpret_cast<volatile int*>(base_ptr + SM::kTokOff);
   float* wxt = reinterpret_cast<float*>(base_ptr + SM::kWxtOff);
@@ -236,7 +236,8 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
     ptx::mbar_init(bar_sfull, 1);
     ptx::mbar_init(bar_dsfull, TC_SOFTMAX_THREADS);
     ptx::mbar_init(bar_mmadone, 1);
-    ptx::mbar_init(bar_selfull, 1);
+    ptx::mbar_init(bar_selfull(0), 1);
+    ptx::mbar_init(bar_selfull(1), 1);
     ptx::fence_barrier_init();
   }
   if (warp == 1) {
@@ -247,7 +248,8 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
-  const uint32_t tm_S = tmem_base, tm_dQ = tmem_base + 256, tm_dK = tmem_base + 320, tm_sel = tmem_base + 448;
+  const uint32_t tm_S = tmem_base, tm_dQ = tmem_base + 256, tm_dK = tmem_base + 320;
+  auto tm_sel = [&](uint32_t i) { return tmem_base + 448u + 16u * (i & 1u); };     // S_sel, double-buffered by unit parity
 
   if (warp < BW_SOFTMAX_WARP0) {
   ptx::setmaxnreg_dec<56>();
@@ -300,8 +302,10 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       BwUnit x = bw_decode(P, u_begin);
       const uint32_t ks = base + SM::kKOff, ksel = base + SM::kKselOff, dsb = base + SM::kDsOff;
       // ---- S = Q' K^T (256 tokens) and S_sel = Q' K_sel^T (16 tokens) of the unit in stage (jt & 1)
-      auto issue_S = [&](int l, uint32_t jt) {
+      // mode 0: both, S_sel interleaved into the first half of S; 1: S_sel only; 2: S only
+      auto issue_S = [&](int l, uint32_t jt, int mode) {
         const uint32_t qs = base + SM::kQOff + (jt & 1) * SM::kQStage;
+        const uint32_t tsel = tm_sel(jt), selbar = bar_selfull(jt);
         long long c0 = clock64();
         ptx::mbar_wait_hint(bar_qfull(jt & 1), (jt >> 1) & 1u, 2000u);
         ptx::tc_fence_after();
@@ -309,35 +313,48 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         c0 = clock64();
         const uint32_t id_S = bw_idesc(TC_BM, TC_BN, 0, 0), id_sel = bw_idesc(TC_BM, BW_SEL, 0, 0);
         // LR: the K dimension is the 64-tap window (the launcher only sends such layers here): fixed trip count, the
-        // descriptors of the unrolled loop are the stage's base descriptors plus constants
+        // descriptors of the unrolled loops are the stage's base descriptors plus constants
         const int nk16 = LR ? TC_BK / 16 : P.ops.d[l] / 16;
+        if (mode == 1) {
+#pragma unroll
+          for (int kk = 0; kk < nk16; ++kk) {
+            const uint64_t a_hi = bw_desc(qs + kk * 32, 16, 1024), s_hi = bw_desc(ksel + kk * 32, 16, 1024);
+            if (NPROD == 3) {
+              const uint64_t a_lo = bw_desc(qs + TC_A_BYTES + kk * 32, 16, 1024);
+              const uint64_t s_lo = bw_desc(ksel + BW_KSEL_BYTES + kk * 32, 16, 1024);
+              ptx::umma_bf16(tsel, a_hi, s_lo, id_sel, kk != 0);
+              ptx::umma_bf16(tsel, a_lo, s_hi, id_sel, 1u);
+              ptx::umma_bf16(tsel, a_hi, s_hi, id_sel, 1u);
+            } else {
+              ptx::umma_bf16(tsel, a_hi, s_hi, id_sel, kk != 0);
+            }
+          }
+          ptx::umma_commit(selbar);
+          pf_is += clock64() - c0;
+          return;
+        }
+        if (mode == 2) {
+#pragma unroll
+          for (int kk = 0; kk < nk16; ++kk) {
+            const uint64_t a_hi = bw_desc(qs + kk * 32, 16, 1024), b_hi = bw_desc(ks + kk * 32, 16, 1024);
+            if (NPROD == 3) {
+              const uint64_t a_lo = bw_desc(qs + TC_A_BYTES + kk * 32, 16, 1024);
+              const uint64_t b_lo = bw_desc(ks + TC_B_BYTES + kk * 32, 16, 1024);
+              ptx::umma_bf16(tm_S, a_hi, b_lo, id_S, kk != 0);
+              ptx::umma_bf16(tm_S, a_lo, b_hi, id_S, 1u);
+              ptx::umma_bf16(tm_S, a_hi, b_hi, id_S, 1u);
+            } else {
+              ptx::umma_bf16(tm_S, a_hi, b_hi, id_S, kk != 0);
+            }
+          }
+          ptx::umma_commit(bar_sfull);
+          pf_is += clock64() - c0;
+          return;
+        }
         // The selected tokens' logits go out two per 256-token MMA during the first half of the product and get their
         // own barrier: the softmax warps turn them into the row's delta (16 serial exponentials) while the second half
         // still runs, and the N = 16 MMAs (latency-bound on one accumulator) hide under the N = 256 ones.
         const int n_selblk = (nk16 + 1) >> 1;       // S k-blocks that carry two S_sel k-blocks each
-        if (P.dbg & 128) {
-          // diagnostic order: S and S_sel of a k-block together (same A operands), both barriers at the end
-#pragma unroll
-          for (int kk = 0; kk < nk16; ++kk) {
-            const uint64_t a_hi = bw_desc(qs + kk * 32, 16, 1024), b_hi = bw_desc(ks + kk * 32, 16, 1024);
-            const uint64_t s_hi = bw_desc(ksel + kk * 32, 16, 1024);
-            if (NPROD == 3) {
-              const uint64_t a_lo = bw_desc(qs + TC_A_BYTES + kk * 32, 16, 1024);
-              const uint64_t b_lo = bw_desc(ks + TC_B_BYTES + kk * 32, 16, 1024);
-              const uint64_t s_lo = bw_desc(ksel + BW_KSEL_BYTES + kk * 32, 16, 1024);
-              ptx::umma_bf16(tm_S, a_hi, b_lo, id_S, kk != 0);
-              ptx::umma_bf16(tm_sel, a_hi, s_lo, id_sel, kk != 0);
-              ptx::umma_bf16(tm_S, a_lo, b_hi, id_S, 1u);
-              ptx::umma_bf16(tm_sel, a_lo, s_hi, id_sel, 1u);
-              ptx::umma_bf16(tm_S, a_hi, b_hi, id_S, 1u);
-              ptx::umma_bf16(tm_sel, a_hi, s_hi, id_sel, 1u);
-            } else {
-              ptx::umma_bf16(tm_S, a_hi, b_hi, id_S, kk != 0);
-              ptx::umma_bf16(tm_sel, a_hi, s_hi, id_sel, kk != 0);
-            }
-          }
-          ptx::umma_commit(bar_selfull);
-        } else
 #pragma unroll
         for (int kk = 0; kk < nk16; ++kk) {
           const uint64_t a_hi = bw_desc(qs + kk * 32, 16, 1024), b_hi = bw_desc(ks + kk * 32, 16, 1024);
@@ -353,23 +370,23 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
             const uint64_t s1_lo = bw_desc(ksel + BW_KSEL_BYTES + k1 * 32, 16, 1024);
             ptx::umma_bf16(tm_S, a_hi, b_lo, id_S, kk != 0);
             if (sel0) {
-              ptx::umma_bf16(tm_sel, p_hi, s0_lo, id_sel, kk != 0);
-              ptx::umma_bf16(tm_sel, p_lo, s0_hi, id_sel, 1u);
+              ptx::umma_bf16(tsel, p_hi, s0_lo, id_sel, kk != 0);
+              ptx::umma_bf16(tsel, p_lo, s0_hi, id_sel, 1u);
             }
             ptx::umma_bf16(tm_S, a_lo, b_hi, id_S, 1u);
-            if (sel0) ptx::umma_bf16(tm_sel, p_hi, s0_hi, id_sel, 1u);
-            if (sel1) ptx::umma_bf16(tm_sel, r_hi, s1_lo, id_sel, 1u);
+            if (sel0) ptx::umma_bf16(tsel, p_hi, s0_hi, id_sel, 1u);
+            if (sel1) ptx::umma_bf16(tsel, r_hi, s1_lo, id_sel, 1u);
             ptx::umma_bf16(tm_S, a_hi, b_hi, id_S, 1u);
             if (sel1) {
-              ptx::umma_bf16(tm_sel, r_lo, s1_hi, id_sel, 1u);
-              ptx::umma_bf16(tm_sel, r_hi, s1_hi, id_sel, 1u);
+              ptx::umma_bf16(tsel, r_lo, s1_hi, id_sel, 1u);
+              ptx::umma_bf16(tsel, r_hi, s1_hi, id_sel, 1u);
             }
           } else {
             ptx::umma_bf16(tm_S, a_hi, b_hi, id_S, kk != 0);
-            if (sel0) ptx::umma_bf16(tm_sel, p_hi, s0_hi, id_sel, kk != 0);
-            if (sel1) ptx::umma_bf16(tm_sel, r_hi, s1_hi, id_sel, 1u);
+            if (sel0) ptx::umma_bf16(tsel, p_hi, s0_hi, id_sel, kk != 0);
+            if (sel1) ptx::umma_bf16(tsel, r_hi, s1_hi, id_sel, 1u);
           }
-          if (kk + 1 == n_selblk) ptx::umma_commit(bar_selfull);
+          if (kk + 1 == n_selblk) ptx::umma_commit(selbar);
         }
         ptx::umma_commit(bar_sfull);
         pf_is += clock64() - c0;
@@ -380,8 +397,13 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         const int d = P.ops.d[x.l];
         const int st = it & 1;
         const uint32_t qs = base + SM::kQOff + st * SM::kQStage;
-        if (!s_issued) issue_S(x.l, it);
+        if (!s_issued) issue_S(x.l, it, 0);
         s_issued = false;
+        // LR, next tile in the same window (no k / k_sel reload, whose TMA would wait for this unit's MMAs): its S_sel only
+        // needs the next W tile, so it runs on the idle tensor pipe while the softmax warps are in this unit's dS pass
+        const bool early = LR && u + 1 < u_end && nxu.hg == x.hg && nxu.b == x.b && nxu.r0 == x.r0 && !(P.dbg & 32);
+        const bool sel_early = early && !(P.dbg & 128);
+        if (sel_early) issue_S(nxu.l, it + 1, 1);
         // ---- wait for dS (bf16, [px][tok]) in shared memory
         long long c0 = clock64();
         ptx::mbar_wait_hint(bar_dsfull, it & 1u, 2000u);
@@ -390,8 +412,8 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         // LR: the softmax warps are done with S(u), so S(u+1) can run AHEAD of the dz product of this unit (they start
         // on the next unit ~1200 cycles earlier and only need dz(u) retired before their first dS store).  Not when
         // the next unit reloads k / k_sel: those single buffers are only refilled after this unit's MMAs retire.
-        if (LR && u + 1 < u_end && nxu.hg == x.hg && nxu.b == x.b && nxu.r0 == x.r0 && !(P.dbg & 32)) {
-          issue_S(nxu.l, it + 1);
+        if (early) {
+          issue_S(nxu.l, it + 1, sel_early ? 2 : 0);
           s_issued = true;
         }
         c0 = clock64();
@@ -506,14 +528,14 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
 
       long long c1 = clock64();
       pf[5] += c1 - c_end;                      // loop top: decode, prefetch issue, table rebuilds
-      ptx::mbar_wait(bar_selfull, it & 1u);
+      ptx::mbar_wait(bar_selfull(it), (it >> 1) & 1u);
       ptx::tc_fence_after();
       pf[0] += clock64() - c1;
       c1 = clock64();
       float delta = 0.0f;
       {
         uint32_t sv[BW_SEL];
-        ptx::tmem_ld16(tm_sel + lane_off, sv);
+        ptx::tmem_ld16(tm_sel(it) + lane_off, sv);
         ptx::tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < BW_SEL; ++j) {
@@ -575,6 +597,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
           if (c + 1 == HOLD) {
             if (LR && mma_pending) {
               ptx::mbar_wait(bar_mmadone, (it - 1) & 1u);
+              ptx::tc_fence_after();
               mma_pending = false;
             }
 #pragma unroll
