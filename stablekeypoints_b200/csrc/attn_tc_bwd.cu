@@ -96,7 +96,7 @@ struct BwSmem {
   static constexpr int kKselBytes = (NPROD == 3 ? 2 : 1) * BW_KSEL_BYTES;
   static constexpr int kDsOff = kKselOff + kKselBytes;              // dS tile; aliased by the fp32 dQ' staging
   static constexpr int kWxtOff = kDsOff + BW_DS_BYTES;
-  static constexpr int kBarOff = kWxtOff + BW_WXT_FLOATS * 4;       // q_full[2], q_empty[2], s_full, ds_full, mma_done, sel_full[2]
+  static constexpr int kBarOff = kWxtOff + BW_WXT_FLOATS * 4;       // q_full[2], q_empty[2], s_full, ds_full, mma_done, sel_full[2], s_free
   static constexpr int kTmemPtrOff = kBarOff + 8 * 10;
   static constexpr int kTokOff = kTmemPtrOff + 8;                   // int tok[16]
   static constexpr int kTotal = kTokOff + 4 * BW_SEL;
@@ -222,6 +222,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
   const uint32_t bar_sfull = base + SM::kBarOff + 8u * 4;
   const uint32_t bar_dsfull = base + SM::kBarOff + 8u * 5;
   const uint32_t bar_mmadone = base + SM::kBarOff + 8u * 6;
+  const uint32_t bar_sfree = base + SM::kBarOff + 8u * 9;
   auto bar_selfull = [&](uint32_t i) { return base + SM::kBarOff + 8u * (7 + (i & 1u)); };
   volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(base_ptr + SM::kTmemPtrOff);
   volatile int* tok_s = reinterpret_cast<volatile int*>(base_ptr + SM::kTokOff);
@@ -238,6 +239,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
     ptx::mbar_init(bar_mmadone, 1);
     ptx::mbar_init(bar_selfull(0), 1);
     ptx::mbar_init(bar_selfull(1), 1);
+    ptx::mbar_init(bar_sfree, TC_SOFTMAX_THREADS);
     ptx::fence_barrier_init();
   }
   if (warp == 1) {
@@ -404,6 +406,17 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         const bool early = LR && u + 1 < u_end && nxu.hg == x.hg && nxu.b == x.b && nxu.r0 == x.r0 && !(P.dbg & 32);
         const bool sel_early = early && !(P.dbg & 128);
         if (sel_early) issue_S(nxu.l, it + 1, 1);
+        // ... and its S as soon as every softmax thread holds the last chunk of S(u) in registers (s_free), one chunk of
+        // exponentials + the corrections ahead of ds_full
+        const bool s_ahead = early && !(P.dbg & 256);
+        if (s_ahead) {
+          long long c9 = clock64();
+          ptx::mbar_wait_hint(bar_sfree, it & 1u, 1000u);
+          ptx::tc_fence_after();
+          pf_ds += clock64() - c9;
+          issue_S(nxu.l, it + 1, sel_early ? 2 : 0);
+          s_issued = true;
+        }
         // ---- wait for dS (bf16, [px][tok]) in shared memory
         long long c0 = clock64();
         ptx::mbar_wait_hint(bar_dsfull, it & 1u, 2000u);
@@ -412,7 +425,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         // LR: the softmax warps are done with S(u), so S(u+1) can run AHEAD of the dz product of this unit (they start
         // on the next unit ~1200 cycles earlier and only need dz(u) retired before their first dS store).  Not when
         // the next unit reloads k / k_sel: those single buffers are only refilled after this unit's MMAs retire.
-        if (early) {
+        if (early && !s_ahead) {
           issue_S(nxu.l, it + 1, sel_early ? 2 : 0);
           s_issued = true;
         }
@@ -574,6 +587,11 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         for (int c = 0; c < 4; ++c) {
           ptx::tmem_ld_wait();
           if (c < 3) ptx::tmem_ld32(tm_S + lane_off + col0 + 32 * (c + 1), v[(c + 1) & 1]);
+          if (LR && c == 3) {
+            // S(u) is in registers: the tensor pipe may overwrite the accumulator with S(u+1)
+            ptx::tc_fence_before();
+            ptx::mbar_arrive(bar_sfree);
+          }
           if (32 * (c + 1) <= ncol) {
             // all 32 columns of the chunk are tokens (all but the chunk holding T's end): no per-column range test
 #pragma unroll
