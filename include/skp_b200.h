@@ -77,6 +77,13 @@ typedef struct {
 /* bytes of scratch the forward/backward need for this problem (0 for SIMT) */
 size_t skp_attn_map_workspace_bytes(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R,
                                     int precision);
+/* The same per call: the query above covers every call the caller might make with one buffer, including the
+ * fp32 CUDA-core backward (row_stats == NULL), whose upsampled-gradient scratch is the largest term by far.
+ * `call` = SKP_WS_FWD (skp_attn_map_fwd), SKP_WS_BWD_STATS (skp_attn_map_bwd with row_stats),
+ * SKP_WS_BWD_NOSTATS (skp_attn_map_bwd with row_stats == NULL), SKP_WS_ANY (= the query above). */
+enum { SKP_WS_ANY = 0, SKP_WS_FWD = 1, SKP_WS_BWD_STATS = 2, SKP_WS_BWD_NOSTATS = 3 };
+size_t skp_attn_map_workspace_bytes_for(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R,
+                                        int precision, int call);
 
 /* maps (B, T', R, R): T' = n_idx when token_idx != NULL (gather, optimize.py:58-59) else T.
  * token_idx holds n_idx ids for image b at token_idx + b*idx_stride (idx_stride 0: the same

@@ -14,6 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libskp_b200.so")
 
 PREC_AUTO, PREC_SIMT_F32, PREC_TC_BF16, PREC_TC_BF16X3 = 0, 1, 2, 3
+WS_ANY, WS_FWD, WS_BWD_STATS, WS_BWD_NOSTATS = 0, 1, 2, 3
 PRECISIONS = {"auto": PREC_AUTO, "simt_f32": PREC_SIMT_F32, "tc_bf16": PREC_TC_BF16, "tc_bf16x3": PREC_TC_BF16X3}
 
 
@@ -32,6 +33,7 @@ SIGNATURES = {
     "skp_device_arch": (_I, [_I]),
     "skp_kernel_launches": (C.c_longlong, []),
     "skp_attn_map_workspace_bytes": (_Z, [C.POINTER(AttnLayer), _I, _I, _I, _I, _I]),
+    "skp_attn_map_workspace_bytes_for": (_Z, [C.POINTER(AttnLayer), _I, _I, _I, _I, _I, _I]),
     "skp_attn_map_fwd": (_I, [C.POINTER(AttnLayer), _I, _I, _I, _I, _P, _I, _L, _P, _P, _I, _P, _Z, _P]),
     "skp_attn_map_bwd": (_I, [C.POINTER(AttnLayer), _I, _I, _I, _I, _P, _I, _L, _P, _P, _I, _P, _Z, _P]),
     "skp_bilinear_upsample": (_I, [_P, _I, _I, _I, _P, _I, _I, _P]),

@@ -25,16 +25,28 @@ static int resolve_precision(const skp_attn_layer* h_layers, int n_layers, int B
   return precision;
 }
 
-extern "C" size_t skp_attn_map_workspace_bytes(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int precision) {
+extern "C" size_t skp_attn_map_workspace_bytes_for(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R,
+                                                   int precision, int call) {
   if (!h_layers || n_layers < 1) return 0;
-  size_t bwd = attn_map_bwd_simt_workspace(h_layers, n_layers, B, R);
-  int p = resolve_precision(h_layers, n_layers, B, T, R, 0, precision);
-  size_t fwd = (p == SKP_PREC_SIMT_F32) ? 0 : attn_map_tc_workspace(h_layers, n_layers, B, T, R, p);
-  if (p != SKP_PREC_SIMT_F32 && attn_map_bwd_tc_supported(h_layers, n_layers, B, T, R, 1)) {
-    size_t b2 = attn_map_bwd_tc_workspace(h_layers, n_layers, B, T, R, p);
-    fwd = fwd > b2 ? fwd : b2;
+  const int p = resolve_precision(h_layers, n_layers, B, T, R, 0, precision);
+  const bool tc = p != SKP_PREC_SIMT_F32;
+  const size_t fwd = tc ? attn_map_tc_workspace(h_layers, n_layers, B, T, R, p) : 0;
+  // skp_attn_map_bwd dispatch: tcgen05 with row_stats when the shape is supported, else the CUDA-core kernel
+  const bool bwd_tc = tc && attn_map_bwd_tc_supported(h_layers, n_layers, B, T, R, 1);
+  const size_t bwd_stats = bwd_tc ? attn_map_bwd_tc_workspace(h_layers, n_layers, B, T, R, p) : attn_map_bwd_simt_workspace(h_layers, n_layers, B, R);
+  const size_t bwd_nostats = attn_map_bwd_simt_workspace(h_layers, n_layers, B, R);
+  switch (call) {
+    case SKP_WS_FWD: return fwd;
+    case SKP_WS_BWD_STATS: return bwd_stats;
+    case SKP_WS_BWD_NOSTATS: return bwd_nostats;
+    default: {
+      size_t m = fwd > bwd_stats ? fwd : bwd_stats;
+      return m > bwd_nostats ? m : bwd_nostats;
+    }
   }
-  return fwd > bwd ? fwd : bwd;
+}
+extern "C" size_t skp_attn_map_workspace_bytes(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int precision) {
+  return skp_attn_map_workspace_bytes_for(h_layers, n_layers, B, T, R, precision, SKP_WS_ANY);
 }
 
 extern "C" int skp_attn_map_fwd(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, const int64_t* token_idx,

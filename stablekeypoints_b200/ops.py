@@ -272,8 +272,9 @@ def _layer_array(qs, ks, heads, scales, weights, dqs=None, dks=None):
     return arr
 
 
-def _workspace(arr, n_layers, B, T, R, prec, device):
-    need = _lib.load().skp_attn_map_workspace_bytes(arr, n_layers, B, T, R, prec)
+def _workspace(arr, n_layers, B, T, R, prec, device, call=_lib.WS_ANY):
+    # sized for the call that follows (the any-call query includes the CUDA-core backward's 2.4 GB at BASELINE shapes)
+    need = _lib.load().skp_attn_map_workspace_bytes_for(arr, n_layers, B, T, R, prec, call)
     return torch.empty(max(int(need), 16), dtype=torch.uint8, device=device), int(need)
 
 
@@ -304,7 +305,7 @@ class _AttentionMaps(torch.autograd.Function):
         stats = torch.empty(B, sum(heads), R * R, 2, dtype=torch.float32, device=dev)
         arr = _layer_array(qs, ks, heads, scales, weights)
         with _guard(maps):
-            ws, nbytes = _workspace(arr, n, B, T, R, prec, dev)
+            ws, nbytes = _workspace(arr, n, B, T, R, prec, dev, _lib.WS_FWD)
             call("skp_attn_map_fwd", arr, n, B, T, R, ptr(token_idx), t_out if token_idx is not None else 0, stride,
                  ptr(maps), ptr(stats), prec, ptr(ws), nbytes, stream_of(maps))
         ctx.save_for_backward(token_idx, stats, *qs, *ks)
@@ -329,7 +330,7 @@ class _AttentionMaps(torch.autograd.Function):
         if token_idx is not None and token_idx.dim() == 2:
             # per-image ids: the gradient is already compact, (B, n_idx, R, R)
             with _guard(g):
-                ws, nbytes = _workspace(arr, n, B, T, R, prec, dev)
+                ws, nbytes = _workspace(arr, n, B, T, R, prec, dev, _lib.WS_BWD_STATS if stats is not None else _lib.WS_BWD_NOSTATS)
                 for i in range(0, token_idx.shape[1], chunk):
                     tok = token_idx[:, i:i + chunk].contiguous()
                     dsel = g[:, i:i + chunk].contiguous()
@@ -341,7 +342,7 @@ class _AttentionMaps(torch.autograd.Function):
         if live.numel():
             tok = live if token_idx is None else token_idx[live]
             with _guard(g):
-                ws, nbytes = _workspace(arr, n, B, T, R, prec, dev)
+                ws, nbytes = _workspace(arr, n, B, T, R, prec, dev, _lib.WS_BWD_STATS if stats is not None else _lib.WS_BWD_NOSTATS)
                 for i in range(0, live.numel(), chunk):
                     sel = live[i:i + chunk]
                     dsel = g.index_select(1, sel).contiguous()
@@ -362,7 +363,7 @@ def _attn_backward_compact(meta, token_idx, g, qs, ks, stats=None):
     arr = _layer_array(qs, ks, heads, scales, weights, dqs, dks)
     per_image = token_idx.dim() == 2
     with _guard(g):
-        ws, nbytes = _workspace(arr, n, B, T, R, prec, g.device)
+        ws, nbytes = _workspace(arr, n, B, T, R, prec, g.device, _lib.WS_BWD_STATS if stats is not None else _lib.WS_BWD_NOSTATS)
         for i in range(0, token_idx.shape[-1], chunk):
             tok = token_idx[..., i:i + chunk].contiguous()
             dsel = g[:, i:i + chunk].contiguous()

@@ -33,8 +33,28 @@ def test_library_exports_every_declared_symbol():
 def test_library_binds_and_reports_version():
     from stablekeypoints_b200 import _lib
     lib = _lib.load()
-    assert lib.skp_version() >= 101
+    assert lib.skp_version() >= 104
     assert isinstance(lib.skp_last_error(), bytes)
+
+
+def test_workspace_query_per_call_is_host_only_and_consistent():
+    """skp_attn_map_workspace_bytes[_for] are pure host arithmetic: BASELINE capture set (SD-2.1-base, T=500, R=128, 8 images)."""
+    from stablekeypoints_b200 import _lib
+    lib = _lib.load()
+    spec = [(16, 1280, 20)] * 3 + [(32, 640, 10)]
+    arr = (_lib.AttnLayer * len(spec))()
+    for i, (s, c, h) in enumerate(spec):
+        arr[i].s, arr[i].C, arr[i].heads, arr[i].k_shared = s, c, h, 1
+        arr[i].scale, arr[i].weight = (c // h) ** -0.5, 1.0 / len(spec)
+    q = lambda prec, call: lib.skp_attn_map_workspace_bytes_for(arr, len(spec), 8, 500, 128, prec, call)
+    for prec in (_lib.PREC_AUTO, _lib.PREC_TC_BF16X3):
+        fwd, bs, bn = q(prec, _lib.WS_FWD), q(prec, _lib.WS_BWD_STATS), q(prec, _lib.WS_BWD_NOSTATS)
+        assert q(prec, _lib.WS_ANY) == max(fwd, bs, bn) == lib.skp_attn_map_workspace_bytes(arr, len(spec), 8, 500, 128, prec)
+        assert 0 < fwd < 600e6 and 0 < bs < 1.2e9          # tcgen05 paths: operand copies at native resolution
+        assert bn == 4 * 8 * 128 * 128 * (3 * 1280 + 640) + 4 * 8 * 128 * 16 * 1280 > 2e9   # CUDA-core backward: upsampled dq + tmp
+    assert q(_lib.PREC_SIMT_F32, _lib.WS_FWD) == 0
+    assert q(_lib.PREC_SIMT_F32, _lib.WS_BWD_STATS) == q(_lib.PREC_SIMT_F32, _lib.WS_BWD_NOSTATS)
+    assert lib.skp_attn_map_workspace_bytes_for(None, 0, 8, 500, 128, 0, 0) == 0
 
 
 def test_cpu_tensors_are_refused():
