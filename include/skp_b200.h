@@ -96,6 +96,23 @@ int skp_attn_map_fwd(const skp_attn_layer* h_layers, int n_layers, int B, int T,
                      const int64_t* token_idx, int n_idx, int64_t idx_stride, float* maps, float* row_stats,
                      int precision, void* workspace, size_t workspace_bytes, void* stream);
 
+/* skp_attn_map_fwd without a caller workspace and without any allocation.
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot
+ * call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  The tcgen05
+ * operands are staged in a file-scope `static __device__` array of SKP_STATIC_WS_BYTES inside the library
+ * (held by every GPU that loads it until the process exits).  Same arguments and results as
+ * skp_attn_map_fwd minus (workspace, workspace_bytes); problems whose forward workspace
+ * (skp_attn_map_workspace_bytes_for(..., SKP_WS_FWD)) exceeds SKP_STATIC_WS_BYTES return
+ * SKP_ERR_WORKSPACE (96 MiB holds one BASELINE-size image: SD-2.1 capture set, T=500, R=128 = 83.6 MiB).
+ * Calls cudaGetSymbolAddress once per device (first call on that device, that device current) and
+ * otherwise no cudaMalloc/cudaFree/allocating routine.  All calls on a device share the array: calls
+ * that overlap on the GPU (different streams without a dependency) race; nothing in it has to start at
+ * zero (the staging kernels overwrite everything the main kernel reads). */
+#define SKP_STATIC_WS_BYTES (96u << 20)
+int skp_attn_map_fwd_static(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R,
+                            const int64_t* token_idx, int n_idx, int64_t idx_stride, float* maps, float* row_stats,
+                            int precision, void* stream);
+
 /* Backward of the above for a gradient that is non-zero on n_idx token planes only
  * (the losses read attn_map[top_k indices], optimize.py:420-424).
  * dmaps_sel (B, n_idx, R, R) = d loss / d maps[b, token_idx[j]].  Accumulates into
