@@ -408,3 +408,33 @@ def attention_maps_from_qk(q_lows: Sequence[Tensor], ks: Sequence[Tensor], heads
                                   feature_res, sc)
               for q, k, h, sc in zip(q_lows, ks, heads, scales)]
     return collect_maps(stored, layers=range(len(stored)), upsample_res=upsample_res, indices=indices)
+
+
+def attention_maps_at_pixels(q_lows: Sequence[Tensor], ks: Sequence[Tensor], heads: Sequence[int],
+                             scales: Sequence[float], feature_res: int, pixels: Tensor, dtype=torch.float64,
+                             return_lse2: bool = False):
+    """`attention_maps_from_qk` restricted to a subset of the R x R feature pixels, so that BASELINE-size problems
+    (T = 500, R = 128, 70 heads) can be pinned in fp64 in seconds: the maps of a pixel depend on no other pixel.
+
+    q_lows[l] (s_l^2, C_l), ks[l] (T, C_l) for ONE image; `pixels` (n,) flat indices into R*R.
+    Same arithmetic as `layer_probs_from_qk` + `collect_maps` (`ptp_utils.py:513-538`, `optimize.py:44-75`): the
+    bicubically upsampled q' of pixel (y, x) is sum_{i,j} My[y,i] Mx[x,j] q[i,j,:]; logits q'.k * scale per head;
+    softmax over tokens; mean over heads, then over layers.  -> (T, n); differentiable.
+    return_lse2: also the per-(head, pixel) log2-sum-exp2 of the logits in log2 units (total heads, n), which is what
+    the forward kernel's row statistics encode (m + log2(l))."""
+    R = feature_res
+    py, px = pixels // R, pixels % R
+    out = 0.0
+    lse = []
+    for q, k, h, sc in zip(q_lows, ks, heads, scales):
+        s = int(round(q.shape[0] ** 0.5))
+        C = q.shape[1]
+        M = bicubic_matrix(s, R, dtype)
+        W = (M[py][:, :, None] * M[px][:, None, :]).reshape(len(pixels), s * s)        # (n, s^2)
+        qp = (W @ q.to(dtype)).reshape(len(pixels), h, C // h).permute(1, 0, 2)        # (h, n, d)
+        kh = k.to(dtype).reshape(-1, h, C // h).permute(1, 0, 2)                       # (h, T, d)
+        sim = torch.einsum("hnd,htd->hnt", qp, kh) * sc
+        out = out + torch.softmax(sim, dim=-1).mean(dim=0).t() / len(q_lows)           # (T, n)
+        if return_lse2:
+            lse.append(torch.logsumexp(sim, dim=-1) * 1.4426950408889634)
+    return (out, torch.cat(lse, dim=0)) if return_lse2 else out

@@ -86,3 +86,26 @@ def test_known_answers():
     for i, c in enumerate([3, 0, 8, 15, 5]):
         line[i, 4, c] = 1
     assert O.furthest_points(line, 3, torch.arange(5)).tolist()[:2] == [1, 3]
+
+
+def test_pixel_restricted_oracle_equals_full_oracle():
+    """`attention_maps_at_pixels` (the fp64 pin of the BASELINE-size GPU tests) == `attention_maps_from_qk` on those pixels,
+    unequal heads per layer, and its log2-sum-exp2 equals the logits' own."""
+    import torch
+    from oracle import keypoint_oracle as O
+    g = torch.Generator().manual_seed(0)
+    spec = [(4, 64, 4), (8, 32, 2), (16, 32, 1)]
+    qs = [torch.randn(s * s, c, generator=g).double() for s, c, _ in spec]
+    ks = [torch.randn(23, c, generator=g).double() for _, c, _ in spec]
+    heads = [h for _, _, h in spec]
+    sc = [(c // h) ** -0.5 for _, c, h in spec]
+    full = O.attention_maps_from_qk(qs, ks, heads, sc, 16).reshape(23, -1)
+    pix = torch.tensor([0, 5, 17, 255, 128, 15, 16, 240])
+    sub, lse2 = O.attention_maps_at_pixels(qs, ks, heads, sc, 16, pix, return_lse2=True)
+    assert torch.allclose(sub, full[:, pix], rtol=1e-12, atol=1e-15)
+    assert lse2.shape == (sum(heads), len(pix))
+    probs = O.layer_probs_from_qk(qs[0][None], ks[0][None], heads[0], 16, sc[0])       # (h, R^2, T)
+    up = O.bicubic_upsample(qs[0].reshape(1, 4, 4, 64).permute(0, 3, 1, 2), 16).permute(0, 2, 3, 1).reshape(1, 256, 64)
+    sim = torch.einsum("bid,bjd->bij", O.split_heads(up, 4), O.split_heads(ks[0][None], 4)) * sc[0]
+    assert torch.allclose(lse2[:4], torch.logsumexp(sim, -1)[:, pix] * 1.4426950408889634, rtol=1e-12)
+    assert torch.allclose(torch.exp2(sim[:, pix] * 1.4426950408889634 - lse2[:4, :, None]), probs[:, pix], rtol=1e-10)
