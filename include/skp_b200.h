@@ -166,6 +166,9 @@ int skp_gaussian_circles(const float* pos, int S, int N, int size, float sigma, 
 /* torch.argsort(score, descending=False)[:top_k] (ptp_utils.py:110-112, :185-187); ties by index.
  * N <= 4096. */
 int skp_rank_ascending(const float* score, int N, int top_k, int64_t* out, void* stream);
+/* B score vectors in one launch: score (B, N) -> out (B, top_k).  The token optimisation ranks the tokens of every
+ * image of the batch (optimize.py:403-418 runs per image; one CTA per image here). */
+int skp_rank_ascending_batched(const float* score, int B, int N, int top_k, int64_t* out, void* stream);
 /* ptp_utils.py:115-159 furthest_point_sampling on the per-plane argmax locations.
  * argmax_flat (N) int64 from skp_plane_argmax; candidates (n_cand) int64 token ids; out (top_k)
  * int64 in selection order, n_out (1) int32 = how many were written (== top_k unless the
@@ -173,6 +176,9 @@ int skp_rank_ascending(const float* score, int N, int top_k, int64_t* out, void*
  * reference's tensor ops, so indices are bit-exact. n_cand <= 1024. */
 int skp_furthest_point_sampling(const int64_t* argmax_flat, int N, int H, int W, const int64_t* candidates,
                                 int n_cand, int top_k, int64_t* out, int32_t* n_out, void* stream);
+/* B images in one launch: argmax_flat (B, N), candidates (B, n_cand) -> out (B, top_k), n_out (B). */
+int skp_furthest_point_sampling_batched(const int64_t* argmax_flat, int B, int N, int H, int W, const int64_t* candidates,
+                                        int n_cand, int top_k, int64_t* out, int32_t* n_out, void* stream);
 
 /* ---------------------------------------------------------------------------------------
  * (4) Losses.  Replaces optimize.py:157-206 (+ invertable_transform.py:72-92 for the un-warp).
@@ -189,6 +195,19 @@ int skp_keypoint_losses_fwd(const float* maps_a, const float* maps_b, const int6
 int skp_keypoint_losses_bwd(const float* maps_a, const float* maps_b, const int64_t* idx, int K, int H, int W,
                             const float* theta_inv, float sigma, int num_subjects, float g_sharp, float g_equiv,
                             float* d_a_sel, float* d_b_sel, void* stream);
+
+/* The same for the B images of a batch in ONE launch (the loop over images of optimize.py:403-429).
+ * maps_a / maps_b (B, planes, H, W); idx (B, K) plane ids inside each image's stack (idx_stride = K) or one shared row
+ * (idx_stride = 0); theta_inv (B, 2, 3) DEVICE; loss_parts (B, K, 2).
+ * Backward: g (B, 2) DEVICE fp32 = d total / d (mean sharpening, mean equivariance) of every image -- a device pointer, so
+ * the autograd glue never synchronises the stream to read upstream scalars; d_a_sel written, d_b_sel accumulated
+ * (caller zero-fills), both (B, K, H, W). */
+int skp_keypoint_losses_batched_fwd(const float* maps_a, const float* maps_b, const int64_t* idx, int64_t idx_stride, int B,
+                                    int planes, int K, int H, int W, const float* theta_inv, float sigma, int num_subjects,
+                                    float* loss_parts, void* stream);
+int skp_keypoint_losses_batched_bwd(const float* maps_a, const float* maps_b, const int64_t* idx, int64_t idx_stride, int B,
+                                    int planes, int K, int H, int W, const float* theta_inv, float sigma, int num_subjects,
+                                    const float* g, float* d_a_sel, float* d_b_sel, void* stream);
 
 /* ---------------------------------------------------------------------------------------
  * (5) Test-time-augmentation ensemble.  Replaces eval.py:221-222, 260-266, 327-330 and the

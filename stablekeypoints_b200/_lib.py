@@ -47,6 +47,10 @@ SIGNATURES = {
     "skp_plane_stats": (_I, [_P, _I, _I, _I, _F, _F, _I, _P, _P, _P, _P]),
     "skp_gaussian_circles": (_I, [_P, _I, _I, _I, _F, _P, _P]),
     "skp_rank_ascending": (_I, [_P, _I, _I, _P, _P]),
+    "skp_rank_ascending_batched": (_I, [_P, _I, _I, _I, _P, _P]),
+    "skp_furthest_point_sampling_batched": (_I, [_P, _I, _I, _I, _I, _P, _I, _I, _P, _P, _P]),
+    "skp_keypoint_losses_batched_fwd": (_I, [_P, _P, _P, _L, _I, _I, _I, _I, _I, _P, _F, _I, _P, _P]),
+    "skp_keypoint_losses_batched_bwd": (_I, [_P, _P, _P, _L, _I, _I, _I, _I, _I, _P, _F, _I, _P, _P, _P, _P]),
     "skp_furthest_point_sampling": (_I, [_P, _I, _I, _I, _P, _I, _I, _P, _P, _P]),
     "skp_keypoint_losses_fwd": (_I, [_P, _P, _P, _I, _I, _I, _P, _F, _I, _P, _P]),
     "skp_keypoint_losses_bwd": (_I, [_P, _P, _P, _I, _I, _I, _P, _F, _I, _F, _F, _P, _P, _P]),

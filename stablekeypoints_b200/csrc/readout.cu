@@ -416,6 +416,8 @@ __global__ void gaussian_circles_kernel(const float* __restrict__ pos, int S, in
 // =========================================================================================
 __global__ void rank_ascending_kernel(const float* __restrict__ score, int N, int top_k, int64_t* out) {
   extern __shared__ unsigned long long keys[];
+  score += static_cast<int64_t>(blockIdx.x) * N;      // one CTA per score vector (batched launches)
+  out += static_cast<int64_t>(blockIdx.x) * top_k;
   int P = 1;
   while (P < N) P <<= 1;
   for (int i = threadIdx.x; i < P; i += blockDim.x) {
@@ -463,6 +465,10 @@ __global__ void fps_kernel(const int64_t* __restrict__ argmax_flat, int N, int H
   int* chosen = tok + n_cand;                               // [top_k] candidate positions
   __shared__ unsigned long long scratch[32];
   __shared__ int n_sel;
+  argmax_flat += static_cast<int64_t>(blockIdx.x) * N;   // one CTA per image (batched launches)
+  cand += static_cast<int64_t>(blockIdx.x) * n_cand;
+  out += static_cast<int64_t>(blockIdx.x) * top_k;
+  n_out += blockIdx.x;
   for (int i = threadIdx.x; i < n_cand; i += blockDim.x) {
     int t = static_cast<int>(cand[i]);
     tok[i] = t;
@@ -547,17 +553,28 @@ __device__ __forceinline__ float sample_bilinear_zeros(const float* __restrict__
   return v;
 }
 
+// grid (K, B): plane k of image b.  Batched launches (B > 1): maps_a / maps_b (B, planes, H, W), idx (B, K) or one shared
+// row (idx_stride 0), theta_inv (B, 2, 3), outputs (B, K, ...).  g_dev (backward, optional): (B, 2) DEVICE upstream
+// gradients (d total / d mean sharpening, d total / d mean equivariance) of each image, multiplied into ca / cb here so
+// that the autograd glue never reads a scalar back to the host.
 template <bool kBackward>
 __global__ void keypoint_losses_kernel(const float* __restrict__ maps_a, const float* __restrict__ maps_b,
-                                       const int64_t* __restrict__ idx, int H, int W, const float* __restrict__ theta_inv,
-                                       float sigma, int num_subjects, float* loss_parts, float ca, float cb,
-                                       float* d_a_sel, float* d_b_sel) {
+                                       const int64_t* __restrict__ idx, int64_t idx_stride, int planes, int H, int W,
+                                       const float* __restrict__ theta_inv, float sigma, int num_subjects, float* loss_parts,
+                                       float ca, float cb, const float* __restrict__ g_dev, float* d_a_sel, float* d_b_sel) {
   __shared__ unsigned long long scratch[32];
   __shared__ double dscratch[32];
   const int n = H * W;
-  const int64_t t = idx[blockIdx.x];
+  const int img = blockIdx.y, K = gridDim.x;
+  const int64_t t = idx[img * idx_stride + blockIdx.x] + static_cast<int64_t>(img) * planes;
   const float* a = maps_a + t * n;
   const float* b = maps_b ? maps_b + t * n : nullptr;
+  theta_inv = theta_inv ? theta_inv + 6 * img : nullptr;
+  const int64_t oplane = static_cast<int64_t>(img) * K + blockIdx.x;
+  if (kBackward && g_dev) {
+    ca *= g_dev[2 * img];
+    cb *= g_dev[2 * img + 1];
+  }
   Discs d;
   d.n = 0;
   d.rad2 = static_cast<float>((0.05 * static_cast<double>(H)) * (0.05 * static_cast<double>(H)));
@@ -600,9 +617,9 @@ __global__ void keypoint_losses_kernel(const float* __restrict__ maps_a, const f
       ss += static_cast<double>(ds) * ds;
       se += static_cast<double>(de) * de;
     } else {
-      d_a_sel[static_cast<int64_t>(blockIdx.x) * n + i] = ca * ds + cb * de;
+      d_a_sel[oplane * n + i] = ca * ds + cb * de;
       if (b && d_b_sel) {
-        float* db = d_b_sel + static_cast<int64_t>(blockIdx.x) * n;
+        float* db = d_b_sel + oplane * n;
         const float gco = -cb * de;
         float x0f = floorf(ig.ix), y0f = floorf(ig.iy);
         int x0 = static_cast<int>(x0f), y0 = static_cast<int>(y0f);
@@ -622,8 +639,8 @@ __global__ void keypoint_losses_kernel(const float* __restrict__ maps_a, const f
     ss = block_sum(ss, dscratch);
     se = block_sum(se, dscratch);
     if (threadIdx.x == 0) {
-      loss_parts[blockIdx.x * 2 + 0] = static_cast<float>(ss);
-      loss_parts[blockIdx.x * 2 + 1] = static_cast<float>(se);
+      loss_parts[oplane * 2 + 0] = static_cast<float>(ss);
+      loss_parts[oplane * 2 + 1] = static_cast<float>(se);
     }
   }
 }
@@ -702,24 +719,33 @@ extern "C" int skp_gaussian_circles(const float* pos, int S, int N, int size, fl
   return SKP_OK;
 }
 
-extern "C" int skp_rank_ascending(const float* score, int N, int top_k, int64_t* out, void* stream) {
-  SKP_REQUIRE(score && out && N > 0 && N <= 4096 && top_k >= 0 && top_k <= N, "skp_rank_ascending: need 0 < N <= 4096, top_k <= N");
+extern "C" int skp_rank_ascending_batched(const float* score, int B, int N, int top_k, int64_t* out, void* stream) {
+  SKP_REQUIRE(score && out && B > 0 && N > 0 && N <= 4096 && top_k >= 0 && top_k <= N,
+              "skp_rank_ascending: need B > 0, 0 < N <= 4096, top_k <= N");
   int P = 1;
   while (P < N) P <<= 1;
-  rank_ascending_kernel<<<(::skp::note_launch(), 1), 512, P * sizeof(unsigned long long), as_stream(stream)>>>(score, N, top_k, out);
+  rank_ascending_kernel<<<(::skp::note_launch(), B), 512, P * sizeof(unsigned long long), as_stream(stream)>>>(score, N, top_k, out);
   SKP_LAUNCH_CHECK();
   return SKP_OK;
 }
+extern "C" int skp_rank_ascending(const float* score, int N, int top_k, int64_t* out, void* stream) {
+  return skp_rank_ascending_batched(score, 1, N, top_k, out, stream);
+}
 
-extern "C" int skp_furthest_point_sampling(const int64_t* argmax_flat, int N, int H, int W, const int64_t* candidates,
-                                           int n_cand, int top_k, int64_t* out, int32_t* n_out, void* stream) {
+extern "C" int skp_furthest_point_sampling_batched(const int64_t* argmax_flat, int B, int N, int H, int W,
+                                                   const int64_t* candidates, int n_cand, int top_k, int64_t* out,
+                                                   int32_t* n_out, void* stream) {
   SKP_REQUIRE(argmax_flat && candidates && out && n_out, "skp_furthest_point_sampling: null pointer");
-  SKP_REQUIRE(n_cand >= 2 && n_cand <= 1024 && top_k >= 2 && top_k <= n_cand && N > 0,
+  SKP_REQUIRE(n_cand >= 2 && n_cand <= 1024 && top_k >= 2 && top_k <= n_cand && N > 0 && B > 0,
               "skp_furthest_point_sampling: need 2 <= top_k <= n_cand <= 1024 (the reference raises NameError below 2 candidates)");
   size_t smem = sizeof(float) * 2 * n_cand + sizeof(int) * (n_cand + top_k);
-  fps_kernel<<<(::skp::note_launch(), 1), 256, smem, as_stream(stream)>>>(argmax_flat, N, H, W, candidates, n_cand, top_k, out, n_out);
+  fps_kernel<<<(::skp::note_launch(), B), 256, smem, as_stream(stream)>>>(argmax_flat, N, H, W, candidates, n_cand, top_k, out, n_out);
   SKP_LAUNCH_CHECK();
   return SKP_OK;
+}
+extern "C" int skp_furthest_point_sampling(const int64_t* argmax_flat, int N, int H, int W, const int64_t* candidates,
+                                           int n_cand, int top_k, int64_t* out, int32_t* n_out, void* stream) {
+  return skp_furthest_point_sampling_batched(argmax_flat, 1, N, H, W, candidates, n_cand, top_k, out, n_out, stream);
 }
 
 extern "C" int skp_keypoint_losses_fwd(const float* maps_a, const float* maps_b, const int64_t* idx, int K, int H, int W,
@@ -727,8 +753,35 @@ extern "C" int skp_keypoint_losses_fwd(const float* maps_a, const float* maps_b,
   SKP_REQUIRE(maps_a && idx && loss_parts && K > 0 && H > 0 && W > 0, "skp_keypoint_losses_fwd: bad arguments");
   SKP_REQUIRE(!maps_b || theta_inv, "skp_keypoint_losses_fwd: theta_inv required with maps_b");
   SKP_REQUIRE(num_subjects >= 1 && num_subjects <= 8, "skp_keypoint_losses_fwd: 1 <= num_subjects <= 8");
-  keypoint_losses_kernel<false><<<(::skp::note_launch(), K), 512, 0, as_stream(stream)>>>(maps_a, maps_b, idx, H, W, theta_inv, sigma, num_subjects,
-                                                                  loss_parts, 0.f, 0.f, nullptr, nullptr);
+  keypoint_losses_kernel<false><<<(::skp::note_launch(), K), 512, 0, as_stream(stream)>>>(maps_a, maps_b, idx, 0, 0, H, W, theta_inv, sigma, num_subjects,
+                                                                  loss_parts, 0.f, 0.f, nullptr, nullptr, nullptr);
+  SKP_LAUNCH_CHECK();
+  return SKP_OK;
+}
+
+extern "C" int skp_keypoint_losses_batched_fwd(const float* maps_a, const float* maps_b, const int64_t* idx, int64_t idx_stride,
+                                               int B, int planes, int K, int H, int W, const float* theta_inv, float sigma,
+                                               int num_subjects, float* loss_parts, void* stream) {
+  SKP_REQUIRE(maps_a && idx && loss_parts && B > 0 && B <= 65535 && K > 0 && planes > 0 && H > 0 && W > 0,
+              "skp_keypoint_losses_batched_fwd: bad arguments");
+  SKP_REQUIRE(!maps_b || theta_inv, "skp_keypoint_losses_batched_fwd: theta_inv required with maps_b");
+  SKP_REQUIRE(num_subjects >= 1 && num_subjects <= 8, "skp_keypoint_losses_batched_fwd: 1 <= num_subjects <= 8");
+  keypoint_losses_kernel<false><<<(::skp::note_launch(), dim3(K, B)), 512, 0, as_stream(stream)>>>(
+      maps_a, maps_b, idx, idx_stride, planes, H, W, theta_inv, sigma, num_subjects, loss_parts, 0.f, 0.f, nullptr, nullptr, nullptr);
+  SKP_LAUNCH_CHECK();
+  return SKP_OK;
+}
+
+extern "C" int skp_keypoint_losses_batched_bwd(const float* maps_a, const float* maps_b, const int64_t* idx, int64_t idx_stride,
+                                               int B, int planes, int K, int H, int W, const float* theta_inv, float sigma,
+                                               int num_subjects, const float* g, float* d_a_sel, float* d_b_sel, void* stream) {
+  SKP_REQUIRE(maps_a && idx && d_a_sel && g && B > 0 && B <= 65535 && K > 0 && planes > 0 && H > 0 && W > 0,
+              "skp_keypoint_losses_batched_bwd: bad arguments");
+  SKP_REQUIRE(!maps_b || theta_inv, "skp_keypoint_losses_batched_bwd: theta_inv required with maps_b");
+  SKP_REQUIRE(num_subjects >= 1 && num_subjects <= 8, "skp_keypoint_losses_batched_bwd: 1 <= num_subjects <= 8");
+  const float nrm = 2.0f / (static_cast<float>(K) * H * W);
+  keypoint_losses_kernel<true><<<(::skp::note_launch(), dim3(K, B)), 512, 0, as_stream(stream)>>>(
+      maps_a, maps_b, idx, idx_stride, planes, H, W, theta_inv, sigma, num_subjects, nullptr, nrm, nrm, g, d_a_sel, d_b_sel);
   SKP_LAUNCH_CHECK();
   return SKP_OK;
 }
@@ -740,8 +793,8 @@ extern "C" int skp_keypoint_losses_bwd(const float* maps_a, const float* maps_b,
   SKP_REQUIRE(!maps_b || theta_inv, "skp_keypoint_losses_bwd: theta_inv required with maps_b");
   SKP_REQUIRE(num_subjects >= 1 && num_subjects <= 8, "skp_keypoint_losses_bwd: 1 <= num_subjects <= 8");
   const float nrm = 2.0f / (static_cast<float>(K) * H * W);
-  keypoint_losses_kernel<true><<<(::skp::note_launch(), K), 512, 0, as_stream(stream)>>>(maps_a, maps_b, idx, H, W, theta_inv, sigma, num_subjects,
-                                                                 nullptr, g_sharp * nrm, g_equiv * nrm, d_a_sel, d_b_sel);
+  keypoint_losses_kernel<true><<<(::skp::note_launch(), K), 512, 0, as_stream(stream)>>>(maps_a, maps_b, idx, 0, 0, H, W, theta_inv, sigma, num_subjects,
+                                                                 nullptr, g_sharp * nrm, g_equiv * nrm, nullptr, d_a_sel, d_b_sel);
   SKP_LAUNCH_CHECK();
   return SKP_OK;
 }

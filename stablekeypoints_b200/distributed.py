@@ -95,6 +95,24 @@ def interleave_shards(gathered: torch.Tensor, n: int) -> torch.Tensor:
     return gathered.reshape(ws, per, *gathered.shape[1:]).transpose(0, 1).reshape(ws * per, *gathered.shape[1:])[:n]
 
 
+def rank_generators(device, seed: int | None = None):
+    """(CPU generator, generator on `device`) for this rank's random draws (augmentation thetas, DataLoader order; DDIM
+    noise), seeded `base + rank`, or (None, None) = the global generators.
+
+    The reference draws an independent affine and independent noise for every image of a batch
+    (`invertable_transform.py:42-57`, `ptp_utils.py:219`).  With one process per GPU every process starts from the same
+    default seeds, so without this all ranks would sample the SAME transform and noise each step and an N-GPU step would
+    average N images that share them.  Single process with seed None: the global generators, i.e. a user's
+    `torch.manual_seed` keeps its meaning."""
+    if seed is None and world_size() == 1:
+        return None, None
+    base = torch.initial_seed() if seed is None else int(seed)
+    s = (base + rank()) % (2 ** 63)
+    g_cpu = torch.Generator().manual_seed(s)
+    g_dev = torch.Generator(device=device).manual_seed(s) if torch.device(device).type == "cuda" else g_cpu
+    return g_cpu, g_dev
+
+
 def barrier() -> None:
     if is_dist():
         dist.barrier()

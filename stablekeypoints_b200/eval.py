@@ -63,6 +63,82 @@ def find_corresponding_points(maps: torch.Tensor, num_points: int = 10):
     return find_max_pixel(chosen).reshape(ni, order.numel(), 2), order
 
 
+def _image_chw(image, device):
+    if not torch.is_tensor(image):
+        image = torch.as_tensor(image)
+    image = image.to(device=device, dtype=torch.float32, non_blocking=True)
+    if image.dim() == 3 and image.shape[-1] == 3 and image.shape[0] != 3:
+        image = image.permute(2, 0, 1)           # numpy HWC (what the reference passes) -> CHW
+    return image
+
+
+def run_images_with_context_augmented(
+    ldm,
+    images,
+    context,
+    indices,
+    device="cuda",
+    from_where=["down_cross", "mid_cross", "up_cross"],
+    layers=[0, 1, 2, 3, 4, 5],
+    augmentation_iterations=20,
+    noise_level=-1,
+    augment_degrees=30,
+    augment_scale=(0.9, 1.1),
+    augment_translate=(0.1, 0.1),
+    controllers=None,
+    num_gpus=1,
+    upscale_size=512,
+    thetas: Optional[torch.Tensor] = None,
+    noise: Optional[torch.Tensor] = None,
+    seeds=None,
+):
+    """`run_image_with_context_augmented` (`eval.py:197-355`) for n images at once -> (n, K, upscale_size, upscale_size).
+
+    Every UNet pass carries `num_gpus` augmented copies of EACH of the n images (n * num_gpus images per pass, one fused
+    attention-map launch for all of them); images are independent, so the result per image is what the single-image
+    call returns.  `thetas` (n, iters*num_gpus, 2, 3) / `noise` (n, iters*num_gpus, 4, h, w) pin the randomness;
+    `seeds` (n ints) instead draws image j's transforms and noise from private generators seeded seeds[j], which makes
+    the result independent of how images are grouped into passes or sharded over ranks."""
+    from . import ptp_utils
+
+    images = [_image_chw(im, device) for im in images]
+    n = len(images)
+    k = len(indices)
+    indices = torch.as_tensor(indices).to(device=device, dtype=torch.int64)
+    sum_samples = torch.zeros(n, k, upscale_size, upscale_size, device=device)
+    num_samples = torch.zeros(n, k, upscale_size, upscale_size, device=device)
+    transform = RandomAffineWithInverse(degrees=augment_degrees, scale=augment_scale, translate=augment_translate)
+    g_cpu = g_dev = [None] * n
+    if seeds is not None:
+        g_cpu = [torch.Generator().manual_seed(int(s)) for s in seeds]
+        g_dev = [torch.Generator(device=device).manual_seed(int(s)) for s in seeds]
+    stacked = torch.stack(images)
+    n_it = augmentation_iterations // num_gpus
+    for i in range(n_it):
+        sl = slice(i * num_gpus, (i + 1) * num_gpus)
+        batch = stacked[:, None].expand(-1, num_gpus, -1, -1, -1).reshape(n * num_gpus, *stacked.shape[1:])
+        if thetas is not None:
+            th = thetas[:, sl].reshape(n * num_gpus, 2, 3)
+        else:
+            th = torch.cat([transform.sample_theta(num_gpus, g_cpu[j]) for j in range(n)])
+        augmented = transform(batch, theta=th)
+        if noise is not None:
+            nz = noise[:, sl].reshape(n * num_gpus, *noise.shape[2:])
+        elif seeds is not None:
+            lat = (num_gpus, 4, stacked.shape[-2] // 8, stacked.shape[-1] // 8)
+            nz = torch.cat([torch.randn(lat, device=device, generator=g_dev[j]) for j in range(n)])
+        else:
+            nz = None
+        maps = ptp_utils.run_and_find_attn_batched(
+            ldm, augmented, context, layers=layers, noise_level=noise_level, from_where=from_where,
+            upsample_res=-1, device=device, controllers=controllers, indices=indices, noise=nz)   # (n*G,K,R,R)
+        th_inv = transform.inverse_theta()
+        for j in range(n):
+            ops.tta_accumulate(maps[j * num_gpus:(j + 1) * num_gpus], th_inv[j * num_gpus:(j + 1) * num_gpus],
+                               sum_samples[j], num_samples[j])
+    return ops.tta_finalize(sum_samples, num_samples)
+
+
 def run_image_with_context_augmented(
     ldm,
     image,
@@ -83,6 +159,7 @@ def run_image_with_context_augmented(
     upscale_size=512,
     thetas: Optional[torch.Tensor] = None,
     noise: Optional[torch.Tensor] = None,
+    seed: Optional[int] = None,
 ):
     """TTA ensemble of `eval.py:197-355`: mean over augmentations of the un-warped maps of the
     selected tokens, normalised by coverage, NaN -> 0.  -> (K, upscale_size, upscale_size).
@@ -92,33 +169,17 @@ def run_image_with_context_augmented(
     copies (the reference's DataParallel scatter == our per-device batch); the (K,512,512)
     bilinear upsample, the inverse warp and the accumulation are one kernel
     (`skp_tta_accumulate`) reading the (K,R,R) feature-resolution planes.
-    `thetas` ((iters*num_gpus,2,3)) / `noise` pin the otherwise unseeded randomness for parity tests.
+    `thetas` ((iters*num_gpus,2,3)) / `noise` pin the otherwise unseeded randomness for parity tests;
+    `seed` draws both from private generators.
     """
-    from . import ptp_utils
-
     if visualize:
         raise NotImplementedError("visualisation (matplotlib) is outside the hot path")
-    if not torch.is_tensor(image):
-        image = torch.as_tensor(image)
-    image = image.to(device=device, dtype=torch.float32)
-    if image.dim() == 3 and image.shape[-1] == 3 and image.shape[0] != 3:
-        image = image.permute(2, 0, 1)           # numpy HWC (what the reference passes) -> CHW
-    k = len(indices)
-    indices = torch.as_tensor(indices).to(device=device, dtype=torch.int64)
-    sum_samples = torch.zeros(k, upscale_size, upscale_size, device=device)
-    num_samples = torch.zeros(k, upscale_size, upscale_size, device=device)
-    transform = RandomAffineWithInverse(degrees=augment_degrees, scale=augment_scale, translate=augment_translate)
-    n_it = augmentation_iterations // num_gpus
-    for i in range(n_it):
-        batch = image[None].expand(num_gpus, -1, -1, -1)
-        th = None if thetas is None else thetas[i * num_gpus:(i + 1) * num_gpus]
-        augmented = transform(batch, theta=th)
-        nz = None if noise is None else noise[i * num_gpus:(i + 1) * num_gpus]
-        maps = ptp_utils.run_and_find_attn_batched(
-            ldm, augmented, context, layers=layers, noise_level=noise_level, from_where=from_where,
-            upsample_res=-1, device=device, controllers=controllers, indices=indices, noise=nz)   # (G,K,R,R)
-        ops.tta_accumulate(maps, transform.inverse_theta(), sum_samples, num_samples)
-    return ops.tta_finalize(sum_samples, num_samples)
+    return run_images_with_context_augmented(
+        ldm, [image], context, indices, device=device, from_where=from_where, layers=layers,
+        augmentation_iterations=augmentation_iterations, noise_level=noise_level, augment_degrees=augment_degrees,
+        augment_scale=augment_scale, augment_translate=augment_translate, controllers=controllers, num_gpus=num_gpus,
+        upscale_size=upscale_size, thetas=None if thetas is None else thetas[None], noise=None if noise is None else noise[None],
+        seeds=None if seed is None else [seed])[0]
 
 
 # --------------------------------------------------------------------------------------
@@ -158,6 +219,24 @@ def keypoint_error(estimated_kpts: torch.Tensor, gt_kpts: torch.Tensor, evaluati
 
 
 @torch.no_grad()
+def extract_keypoints(ldm, samples, context, indices, *, device, from_where, layers, noise_level, augmentation_iterations,
+                      augment_degrees, augment_scale, augment_translate, controllers, num_gpus, max_loc_strategy="argmax",
+                      seeds=None, upscale_size=512):
+    """Keypoints in [0, 1] of a group of dataset samples: TTA maps of all of them in shared UNet passes
+    (`run_images_with_context_augmented`), then the readout of `eval.py:468-476` / `keypoint_regressor.py:196-203`
+    as ONE launch over all (image, keypoint) planes.  -> (n, K, 2) (row, col)."""
+    maps = run_images_with_context_augmented(
+        ldm, [s["img"] for s in samples], context, indices, device=device, from_where=from_where, layers=layers,
+        noise_level=noise_level, augmentation_iterations=augmentation_iterations, augment_degrees=augment_degrees,
+        augment_scale=augment_scale, augment_translate=augment_translate, controllers=controllers, num_gpus=num_gpus,
+        upscale_size=upscale_size, seeds=seeds)
+    n, k, h, w = maps.shape
+    flat = maps.reshape(n * k, h, w)
+    kp = find_max_pixel(flat) if max_loc_strategy == "argmax" else pixel_from_weighted_avg(flat)
+    return kp.reshape(n, k, 2) / float(upscale_size)
+
+
+@torch.no_grad()
 def evaluate(
     ldm,
     context,
@@ -185,10 +264,14 @@ def evaluate(
     validation=False,
     dataset=None,
     log_fn=print,
+    images_per_pass=1,
+    seed=None,
 ):
     """`eval.py:374-539`: TTA extraction -> readout -> linear regressor -> dataset metric, per test
     image; writes `all_errors.pt` into `save_folder` like the reference and returns the (N,) errors.
-    Images are sharded across ranks, one all_gather of the scalar errors at the end."""
+    Images are sharded across ranks, one all_gather of the scalar errors at the end.
+    `images_per_pass` images share each UNet pass (the reference: 1); `seed` makes image i draw its augmentations and
+    noise from generators seeded seed + i, so the result does not depend on the sharding or the grouping."""
     import os
     from . import distributed as dist_
     from .optimize import _make_dataset
@@ -199,18 +282,20 @@ def evaluate(
     per = (n + world - 1) // world
     regressor = torch.as_tensor(regressor).to(device=device, dtype=torch.float32)
     errs = []
-    for i in dist_.shard_range(n, rank, world):
-        sample = dataset[i]
-        maps = run_image_with_context_augmented(
-            ldm, sample["img"], context, torch.as_tensor(indices).cpu(), device=device, from_where=from_where,
-            layers=layers, noise_level=noise_level, augmentation_iterations=augmentation_iterations,
-            augment_degrees=augment_degrees, augment_scale=augment_scale, augment_translate=augment_translate,
-            controllers=controllers, num_gpus=num_gpus, save_folder=save_folder)
-        kp = (find_max_pixel(maps) if max_loc_strategy == "argmax" else pixel_from_weighted_avg(maps)) / 512.0
-        est = (((kp.reshape(1, -1) - 0.5) @ regressor) + 0.5).reshape(-1, 2)
-        gt = torch.as_tensor(sample["kpts"]).to(device=device, dtype=torch.float32)
-        vis = torch.as_tensor(sample["visibility"]).to(device) if "visibility" in sample else None
-        errs.append(keypoint_error(est, gt, evaluation_method, vis))
+    mine = list(dist_.shard_range(n, rank, world))
+    for c in range(0, len(mine), max(1, int(images_per_pass))):
+        ids = mine[c:c + max(1, int(images_per_pass))]
+        samples = [dataset[i] for i in ids]
+        kps = extract_keypoints(
+            ldm, samples, context, torch.as_tensor(indices).cpu(), device=device, from_where=from_where, layers=layers,
+            noise_level=noise_level, augmentation_iterations=augmentation_iterations, augment_degrees=augment_degrees,
+            augment_scale=augment_scale, augment_translate=augment_translate, controllers=controllers, num_gpus=num_gpus,
+            max_loc_strategy=max_loc_strategy, seeds=None if seed is None else [seed + i for i in ids])
+        for sample, kp in zip(samples, kps):
+            est = (((kp.reshape(1, -1) - 0.5) @ regressor) + 0.5).reshape(-1, 2)
+            gt = torch.as_tensor(sample["kpts"]).to(device=device, dtype=torch.float32)
+            vis = torch.as_tensor(sample["visibility"]).to(device) if "visibility" in sample else None
+            errs.append(keypoint_error(est, gt, evaluation_method, vis))
     t = torch.stack(errs) if errs else torch.zeros(0, device=device)
     if world > 1:
         t = torch.cat([t, torch.zeros(per - t.shape[0], device=device)])

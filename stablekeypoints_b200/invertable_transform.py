@@ -29,21 +29,25 @@ class RandomAffineWithInverse:
         theta[:, :2] = theta[:, :2] * scale
         return theta.unsqueeze(0)
 
-    def sample_theta(self, n: int) -> torch.Tensor:
+    def sample_theta(self, n: int, generator=None) -> torch.Tensor:
         """Same draw order as the reference (`:44-51`): angle, scale, tx, ty per image from the
-        global CPU generator, so a seeded run reproduces the reference's transforms."""
+        global CPU generator, so a seeded run reproduces the reference's transforms.  `generator`
+        (a CPU torch.Generator) replaces the global one: multi-rank jobs draw from a per-rank
+        generator so that the ranks do not all sample the same transform."""
+        def r():
+            return torch.rand(1, generator=generator).item()
         out = []
         for _ in range(n):
-            angle = torch.rand(1).item() * (2 * self.degrees) - self.degrees
-            scale_factor = torch.rand(1).item() * (self.scale[1] - self.scale[0]) + self.scale[0]
-            tr = (torch.rand(1).item() * (2 * self.translate[0]) - self.translate[0],
-                  torch.rand(1).item() * (2 * self.translate[1]) - self.translate[1])
+            angle = r() * (2 * self.degrees) - self.degrees
+            scale_factor = r() * (self.scale[1] - self.scale[0]) + self.scale[0]
+            tr = (r() * (2 * self.translate[0]) - self.translate[0],
+                  r() * (2 * self.translate[1]) - self.translate[1])
             out.append(self.create_affine_matrix(angle, scale_factor, tr))
         return torch.cat(out, dim=0)
 
-    def __call__(self, img_tensor: torch.Tensor, theta=None) -> torch.Tensor:
+    def __call__(self, img_tensor: torch.Tensor, theta=None, generator=None) -> torch.Tensor:
         if theta is None:
-            theta = self.sample_theta(img_tensor.shape[0])
+            theta = self.sample_theta(img_tensor.shape[0], generator)
         theta = theta.to(device=img_tensor.device, dtype=torch.float32)
         self.last_params = {"theta": theta}
         return ops.affine_warp(img_tensor, theta)

@@ -11,8 +11,8 @@ import torch
 
 from . import distributed as dist_
 from . import ops
-from .eval import find_max_pixel, pixel_from_weighted_avg, run_image_with_context_augmented
-from .optimize import _make_dataset, select_tokens
+from .eval import extract_keypoints
+from .optimize import _make_dataset, select_tokens_batched
 
 
 def vote_top_k(indices_list: torch.Tensor, top_k: int) -> torch.Tensor:
@@ -67,9 +67,8 @@ def find_best_indices(
         maps = ptp_utils.run_and_find_attn_batched(
             ldm, image, context, layers=layers, noise_level=noise_level, from_where=from_where,
             upsample_res=upsample_res, device=device, controllers=controllers)
-        for m in maps.unbind(0):
-            votes.append(select_tokens(m, m, top_k_strategy, furthest_point_num_samples, top_k, sigma, num_subjects))
-    votes = torch.stack(votes) if votes else torch.empty(0, top_k, dtype=torch.int64, device=device)
+        votes.append(select_tokens_batched(maps, maps, top_k_strategy, furthest_point_num_samples, top_k, sigma, num_subjects))
+    votes = torch.cat(votes) if votes else torch.empty(0, top_k, dtype=torch.int64, device=device)
     votes = dist_.all_gather_cat(votes)
     return vote_top_k(votes, top_k)
 
@@ -97,42 +96,50 @@ def precompute_all_keypoints(
     save_folder="outputs",
     validation=False,
     dataset=None,
+    images_per_pass=1,
+    seed=None,
 ):
     """`keypoint_regressor.py:124-224` -> (source (N,K,2), target (N,n,2), visibility|None), in
     dataset order.  Images are sharded across ranks; one all_gather of the (N_local,K,2) keypoints
-    at the end (the reference shuffles with batch_size 1; order does not affect the regressor)."""
+    at the end (the reference shuffles with batch_size 1; order does not affect the regressor).
+    `images_per_pass` images share each UNet pass (the reference: 1); `seed`: image i draws its augmentations and noise
+    from generators seeded seed + i (results independent of sharding / grouping)."""
     world, rank = dist_.world_size(), dist_.rank()
     dataset = _make_dataset(dataset_name, dataset_loc, dataset)
     n = min(len(dataset), max_num_points)
     mine = list(dist_.shard_range(n, rank, world))
     per = (n + world - 1) // world
     src, tgt, vis = [], [], []
-    for i in mine:
-        sample = dataset[i]
-        maps = run_image_with_context_augmented(
-            ldm, sample["img"], context, top_indices, device=device, from_where=from_where, layers=layers,
-            noise_level=noise_level, augmentation_iterations=augmentation_iterations, augment_degrees=augment_degrees,
-            augment_scale=augment_scale, augment_translate=augment_translate, controllers=controllers,
-            save_folder=save_folder, num_gpus=num_gpus)
-        kp = find_max_pixel(maps) / 512.0 if max_loc_strategy == "argmax" else pixel_from_weighted_avg(maps) / 512.0
-        src.append(kp)
-        tgt.append(torch.as_tensor(sample["kpts"]).to(device=device, dtype=torch.float32))
-        if "visibility" in sample:
-            vis.append(torch.as_tensor(sample["visibility"]).to(device=device, dtype=torch.float32))
+    # every rank issues the same collectives with equal shapes, whatever its shard holds: the shapes come from sample 0
+    # and the argument list, not from the local rows (a rank with an empty shard must neither skip a gather nor guess)
+    first = dataset[0] if n > 0 else {}
+    has_vis = "visibility" in first
+    n_kpts = tuple(torch.as_tensor(first["kpts"]).shape) if n > 0 else (0, 2)
+    step = max(1, int(images_per_pass))
+    for c in range(0, len(mine), step):
+        ids = mine[c:c + step]
+        samples = [dataset[i] for i in ids]
+        kps = extract_keypoints(
+            ldm, samples, context, top_indices, device=device, from_where=from_where, layers=layers, noise_level=noise_level,
+            augmentation_iterations=augmentation_iterations, augment_degrees=augment_degrees, augment_scale=augment_scale,
+            augment_translate=augment_translate, controllers=controllers, num_gpus=num_gpus, max_loc_strategy=max_loc_strategy,
+            seeds=None if seed is None else [seed + i for i in ids])
+        for sample, kp in zip(samples, kps):
+            src.append(kp)
+            tgt.append(torch.as_tensor(sample["kpts"]).to(device=device, dtype=torch.float32))
+            if has_vis:
+                vis.append(torch.as_tensor(sample["visibility"]).to(device=device, dtype=torch.float32))
 
-    def _gather(rows):
-        if not rows and world == 1:
-            return None
-        t = torch.stack(rows) if rows else None
+    def _gather(rows, row_shape):
+        t = torch.stack(rows) if rows else torch.zeros(0, *row_shape, device=device)
         if world == 1:
-            return t
-        if t is None or t.shape[0] < per:      # pad the short shard so all_gather shapes agree
-            like = rows[0] if rows else torch.zeros(1, device=device)
-            pad = torch.zeros(per - len(rows), *like.shape, device=device, dtype=like.dtype)
-            t = pad if t is None else torch.cat([t, pad])
+            return t if n > 0 else None
+        if t.shape[0] < per:                    # pad the short shard so all_gather shapes agree
+            t = torch.cat([t, torch.zeros(per - t.shape[0], *row_shape, device=device, dtype=t.dtype)])
         return dist_.interleave_shards(dist_.all_gather_cat(t), n)
 
-    return _gather(src), _gather(tgt), (_gather(vis) if vis else None)
+    return (_gather(src, (len(top_indices), 2)), _gather(tgt, n_kpts),
+            _gather(vis, n_kpts[:1]) if has_vis else None)
 
 
 # --------------------------------------------------------------------------------------

@@ -94,6 +94,32 @@ def rank_ascending(score: torch.Tensor, top_k: int) -> torch.Tensor:
     return out
 
 
+def rank_ascending_batched(score: torch.Tensor, top_k: int) -> torch.Tensor:
+    """score (B, N) -> (B, top_k) int64: `torch.argsort(score[b])[:top_k]` for every row, one launch."""
+    score = _f32(score)
+    b, n = score.shape
+    out = torch.empty(b, top_k, dtype=torch.int64, device=score.device)
+    with _guard(score):
+        call("skp_rank_ascending_batched", ptr(score), b, n, top_k, ptr(out), stream_of(score))
+    return out
+
+
+def furthest_point_sampling_batched(argmax_flat: torch.Tensor, h: int, w: int, candidates: torch.Tensor, top_k: int) -> torch.Tensor:
+    """argmax_flat (B, N) int64, candidates (B, n_cand) unique ids per row -> (B, top_k) int64, one launch, no host sync."""
+    if argmax_flat.dtype != torch.int64 or candidates.dtype != torch.int64:
+        raise RuntimeError("indices must be int64")
+    b, n = argmax_flat.shape
+    if candidates.shape[1] < 2:
+        raise NameError("furthest_pair")   # what the reference raises (ptp_utils.py:140)
+    k = min(top_k, candidates.shape[1])
+    out = torch.empty(b, k, dtype=torch.int64, device=argmax_flat.device)
+    n_out = torch.empty(b, dtype=torch.int32, device=argmax_flat.device)
+    with _guard(argmax_flat):
+        call("skp_furthest_point_sampling_batched", ptr(argmax_flat.contiguous()), b, n, h, w, ptr(candidates.contiguous()),
+             candidates.shape[1], k, ptr(out), ptr(n_out), stream_of(argmax_flat))
+    return out
+
+
 def furthest_point_sampling(argmax_flat: torch.Tensor, h: int, w: int, candidates: torch.Tensor, top_k: int,
                             assume_unique: bool = True) -> torch.Tensor:
     """`ptp_utils.py:115-159` on precomputed per-plane argmax indices.  With unique candidates
@@ -222,6 +248,55 @@ class _KeypointLosses(torch.autograd.Function):
         ga = torch.zeros_like(maps_a).index_add_(0, idx, d_a)
         gb = torch.zeros_like(maps_b).index_add_(0, idx, d_b) if maps_b is not None else None
         return ga, gb, None, None, None, None
+
+
+class _KeypointLossesBatched(torch.autograd.Function):
+    """The per-image loop of `optimize.py:403-429` as one launch.  `planes` (B, K, H, W) are the selected planes of B
+    images (sharpening only), or with `paired` (2B, K, H, W): rows [0, B) the images, rows [B, 2B) their transformed copies,
+    theta_inv (B, 2, 3).  -> (B, 2) = per image (mean sharpening, mean equivariance).  The backward hands the (B, 2)
+    upstream gradient to the kernel as a DEVICE pointer and returns one compact gradient of `planes`' shape: no host
+    read, no scatter, no concatenation."""
+
+    @staticmethod
+    def forward(ctx, planes, theta_inv, paired, sigma, num_subjects):
+        planes = _f32(planes)
+        n, k, h, w = planes.shape
+        b = n // 2 if paired else n
+        dev = planes.device
+        if paired:
+            if n != 2 * b:
+                raise RuntimeError("paired planes need an even leading dimension")
+            theta_inv = _f32(theta_inv.to(dev)).reshape(b, 6)
+        planes_b = planes[b:] if paired else None
+        idx = torch.arange(k, device=dev, dtype=torch.int64)
+        parts = torch.empty(b, k, 2, dtype=torch.float32, device=dev)
+        with _guard(planes):
+            call("skp_keypoint_losses_batched_fwd", ptr(planes), ptr(planes_b), ptr(idx), 0, b, k, k, h, w,
+                 ptr(theta_inv) if paired else None, float(sigma), int(num_subjects), ptr(parts), stream_of(planes))
+        ctx.save_for_backward(planes, idx, theta_inv if paired else None)
+        ctx.cfg = (float(sigma), int(num_subjects), bool(paired))
+        return parts.sum(dim=1) / float(k * h * w)
+
+    @staticmethod
+    def backward(ctx, g):
+        planes, idx, theta_inv = ctx.saved_tensors
+        sigma, ns, paired = ctx.cfg
+        n, k, h, w = planes.shape
+        b = n // 2 if paired else n
+        g = _f32(g)
+        d = torch.empty_like(planes)
+        if paired:
+            d[b:].zero_()                      # the un-warp's adjoint accumulates (atomics)
+        with _guard(planes):
+            call("skp_keypoint_losses_batched_bwd", ptr(planes), ptr(planes[b:]) if paired else None, ptr(idx), 0, b, k, k, h, w,
+                 ptr(theta_inv) if paired else None, sigma, ns, ptr(g), ptr(d), ptr(d[b:]) if paired else None, stream_of(planes))
+        return d, None, None, None, None
+
+
+def keypoint_losses_batched(planes, theta_inv=None, sigma: float = 1.0, num_subjects: int = 1) -> torch.Tensor:
+    """-> (B, 2): (mean sharpening loss, mean equivariance loss) of every image, one launch each way.
+    theta_inv given: `planes` is (2B, K, H, W) = images then transformed copies; else (B, K, H, W), sharpening only."""
+    return _KeypointLossesBatched.apply(planes, theta_inv, theta_inv is not None, sigma, num_subjects)
 
 
 def keypoint_losses(maps_a, maps_b, idx, theta_inv, sigma: float, num_subjects: int = 1):

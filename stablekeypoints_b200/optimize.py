@@ -166,37 +166,51 @@ def select_tokens(attn_map, attn_map_transformed, top_k_strategy, furthest_point
     return ptp_utils.furthest_point_sampling(attn_map_transformed, top_k, cand)
 
 
+def select_tokens_batched(maps, maps_transformed, top_k_strategy, furthest_point_num_samples, top_k, sigma, num_subjects):
+    """`select_tokens` for the B images of a batch with one launch per stage (statistics over all B*T planes, one
+    ranking CTA and one furthest-point CTA per image).  maps / maps_transformed (B, T, H, W) -> (B, top_k) int64."""
+    B, T, H, W = maps.shape
+    n_cand = min(int(furthest_point_num_samples), T)
+    flat = maps.reshape(B * T, H, W)
+    if top_k_strategy == "entropy":
+        _, score, _ = ops.plane_stats(flat, want_kl=False, want_entropy=True)
+    elif top_k_strategy == "gaussian":
+        score, _, _ = ops.plane_stats(flat, sigma=float(sigma), epsilon=1e-5, num_subjects=int(num_subjects), want_kl=True)
+    elif top_k_strategy == "consistent":
+        score = None
+    else:
+        raise NotImplementedError
+    cand = (torch.arange(n_cand, device=maps.device).expand(B, -1).contiguous() if score is None
+            else ops.rank_ascending_batched(score.reshape(B, T), n_cand))
+    am = ops.plane_argmax(maps_transformed.reshape(B * T, H, W)).reshape(B, T)
+    return ops.furthest_point_sampling_batched(am, H, W, cand, int(top_k))
+
+
 def token_opt_losses(ldm, image, transformed_img, context, transform, controllers, *, layers, noise_level, from_where,
-                     device, top_k_strategy, furthest_point_num_samples, top_k, sigma, num_subjects, noise=None):
+                     device, top_k_strategy, furthest_point_num_samples, top_k, sigma, num_subjects, noise=None,
+                     generator=None):
     """One image-iteration of `optimize.py:372-429` for a batch of B images on this device.
 
     Both UNet passes of the reference (image, transformed image) run as ONE pass over 2B images
     (every normalisation in the UNet is per-sample, so batching does not change any value).
+    Selection and losses of all B images are one launch per stage; nothing is read back to the host.
     -> (mean sharpening loss, mean equivariance loss, idx (B, top_k))."""
     from . import ptp_utils
     B = image.shape[0]
     ctrl = ptp_utils._controller_list(controllers)[0]
     ctrl.reset()
-    ctrl.context_shared = True
     both = torch.cat([image, transformed_img], dim=0)
-    ptp_utils.find_pred_noise(ldm, both, context, noise_level=noise_level, device=device, noise=noise)
+    ptp_utils.find_pred_noise(ldm, both, context, noise_level=noise_level, device=device, noise=noise, generator=generator)
     handles = _selected_handles(ctrl, layers)
     qs, ks, heads, scales, R = _layer_args(handles)
     ctrl.reset()
     with torch.no_grad():
         maps, stats = ops.attention_maps([q.detach() for q in qs], [k.detach() for k in ks], heads, scales, R,
                                          return_stats=True)                                              # (2B,T,R,R)
-        idx = torch.stack([select_tokens(maps[i], maps[B + i], top_k_strategy, furthest_point_num_samples, top_k,
-                                         sigma, num_subjects) for i in range(B)])
+        idx = select_tokens_batched(maps[:B], maps[B:], top_k_strategy, furthest_point_num_samples, top_k, sigma, num_subjects)
     sel = ops.selected_planes(maps, torch.cat([idx, idx], dim=0), qs, ks, heads, scales, R, row_stats=stats)   # (2B,K,R,R)
-    theta_inv = transform.inverse_theta()
-    ar = _arange_like(idx.shape[1], idx)
-    sharp, equiv = [], []
-    for i in range(B):
-        s_, e_ = ops.keypoint_losses(sel[i], sel[B + i], ar, theta_inv[i], float(sigma), int(num_subjects))
-        sharp.append(s_)
-        equiv.append(e_)
-    return torch.stack(sharp).mean(), torch.stack(equiv).mean(), idx
+    per_image = ops.keypoint_losses_batched(sel, transform.inverse_theta(), float(sigma), int(num_subjects))
+    return per_image[:, 0].mean(), per_image[:, 1].mean(), idx
 
 
 def _make_dataset(dataset_name, dataset_loc, dataset=None, **kw):
@@ -243,12 +257,17 @@ def optimize_embedding(
     context_dim=None,
     log_fn=None,
     step_hook=None,
+    seed=None,
+    grad_hook=None,
 ):
     """`optimize.py:269-475` with the same arguments.  `num_gpus` keeps the reference's meaning
     "images per UNet pass" (its DataLoader batch, `optimize.py:356`); here those images share
     ONE GPU.  Across processes (torchrun, one per GPU) every rank runs this function on its own
     shard of each batch and the context gradient is all-reduced (mean) before each optimiser
     step (`distributed.allreduce_mean_`), replacing `nn.DataParallel` (`optimize_token.py:43-44`).
+    Random draws (augmentation, noise, batch order) come from per-rank generators seeded `seed + rank`
+    (`distributed.rank_generators`; `seed=None` in a single process keeps the global generators).
+    `grad_hook(context.grad)` is called after the all-reduce, before the optimiser step.
     Returns the optimised context, detached (identical on every rank)."""
     from . import distributed as dist_
     from . import ptp_utils
@@ -269,8 +288,9 @@ def optimize_embedding(
         raise ValueError(f"batch_size {batch_size} must be a multiple of num_gpus*world_size = {per_pass * world}")
     accum = batch_size // (per_pass * world)
     host_data = not torch.as_tensor(dataset[0]["img"]).is_cuda
+    g_cpu, g_dev = dist_.rank_generators(device, seed)
     loader = torch.utils.data.DataLoader(dist_.shard_dataset(dataset, rank, world), batch_size=per_pass,
-                                         shuffle=True, drop_last=True, pin_memory=host_data)
+                                         shuffle=True, drop_last=True, pin_memory=host_data, generator=g_cpu)
     it = iter(loader)
     start = it_start = time.time()
     run_eq = run_sh = run_tot = 0.0
@@ -281,11 +301,12 @@ def optimize_embedding(
             it = iter(loader)
             mini_batch = next(it)
         image = mini_batch["img"].to(device, non_blocking=True)
-        transformed = transform(image)
+        transformed = transform(image, generator=g_cpu)
         sh, eq, _ = token_opt_losses(
             ldm, image, transformed, context, transform, controllers, layers=layers, noise_level=noise_level,
             from_where=from_where, device=device, top_k_strategy=top_k_strategy,
-            furthest_point_num_samples=furthest_point_num_samples, top_k=top_k, sigma=sigma, num_subjects=num_subjects)
+            furthest_point_num_samples=furthest_point_num_samples, top_k=top_k, sigma=sigma, num_subjects=num_subjects,
+            generator=g_dev)
         loss = eq * equivariance_attn_loss_weight + sh * sharpening_loss_weight
         run_eq = run_eq + eq.detach() / accum * equivariance_attn_loss_weight
         run_sh = run_sh + sh.detach() / accum * sharpening_loss_weight
@@ -293,6 +314,8 @@ def optimize_embedding(
         (loss / accum).backward()
         if (iteration + 1) % accum == 0:
             dist_.allreduce_mean_(context.grad)
+            if grad_hook is not None:
+                grad_hook(context.grad)
             optimizer.step()
             optimizer.zero_grad()
             if log_fn is False:

@@ -122,7 +122,6 @@ class AttentionStore(AttentionControl):
         self.max_query_tokens = max_query_tokens
         self.max_captured_layers = max_captured_layers
         self.stop_after_capture = False
-        self.context_shared = False      # set by find_pred_noise: every image sees the same context
 
 
 # --------------------------------------------------------------------------------------
@@ -147,7 +146,10 @@ def register_attention_control(model, controller, feature_upsample_res=256):
                        and sequence_length <= getattr(controller, "max_query_tokens", 32 ** 2)
                        and len(store["attn"]) < getattr(controller, "max_captured_layers", 4))
             q = self.to_q(x)
-            shared = is_cross and getattr(controller, "context_shared", False) and batch_size > 1
+            # one context for the whole batch (`context.expand(B, -1, -1)`, what `ptp_utils.py:229`'s repeat amounts
+            # to): detected from the tensor itself, per call, so a genuinely per-sample (B, T, C) context (CFG,
+            # SDXL-style conditioning) through the same controller is never collapsed to sample 0's
+            shared = is_cross and batch_size > 1 and context.shape[0] == batch_size and context.stride(0) == 0
             ctx = (context[:1] if shared else context) if is_cross else x
             k = self.to_k(ctx)
             if capture:
@@ -222,12 +224,14 @@ def image2latent(model, image, device):
         return latents * 0.18215
 
 
-def find_pred_noise(ldm, image, context, noise_level=-1, device="cuda", noise=None):
+def find_pred_noise(ldm, image, context, noise_level=-1, device="cuda", noise=None, generator=None):
     """`ptp_utils.py:205-231`.  `image` (B,3,H,W) in [0,1] stays on the GPU (the reference goes
-    through numpy).  `noise` pins `randn_like(latent)` for parity tests."""
+    through numpy).  `noise` pins `randn_like(latent)` for parity tests; `generator` (a torch.Generator
+    on the latent's device) draws it from a private stream (per-rank / per-image seeding)."""
     latent = image2latent(ldm, image, device)
     if noise is None:
-        noise = torch.randn_like(latent)
+        noise = (torch.randn_like(latent) if generator is None
+                 else torch.randn(latent.shape, device=latent.device, dtype=latent.dtype, generator=generator))
     t = ldm.scheduler.timesteps[noise_level]
     noisy_image = ldm.scheduler.add_noise(latent, noise.to(latent.device), t)
     b = noisy_image.shape[0]
@@ -246,14 +250,13 @@ def _controller_list(controllers) -> List[AttentionStore]:
 
 def run_and_find_attn_batched(ldm, image, context, noise_level=-1, device="cuda",
                               from_where=["down_cross", "mid_cross", "up_cross"], layers=[0, 1, 2, 3, 4, 5],
-                              upsample_res=32, indices=None, controllers=None, noise=None) -> torch.Tensor:
+                              upsample_res=32, indices=None, controllers=None, noise=None, generator=None) -> torch.Tensor:
     """One UNet pass over a batch of images on this device -> (B, T', R', R') maps (one fused
     kernel for all images).  `run_and_find_attn` is the reference-shaped view of this."""
     from .optimize import collect_maps_batched
     ctrl = _controller_list(controllers)[0]
     ctrl.reset()
-    ctrl.context_shared = True
-    find_pred_noise(ldm, image, context, noise_level=noise_level, device=device, noise=noise)
+    find_pred_noise(ldm, image, context, noise_level=noise_level, device=device, noise=noise, generator=generator)
     maps = collect_maps_batched(ctrl, from_where=from_where, upsample_res=upsample_res, layers=layers, indices=indices)
     ctrl.reset()
     return maps

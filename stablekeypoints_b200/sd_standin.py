@@ -383,12 +383,14 @@ class PipelineStandIn:
     """The `ldm` object contract of SURVEY.md §8(b): `.unet`, `.vae`, `.scheduler`, `.text_encoder`."""
 
     def __init__(self, cfg: UNetConfig, vae_channels=(128, 256, 512, 512), seed: int = 0):
-        g = torch.random.get_rng_state()
-        torch.manual_seed(seed)
-        self.unet = UNet2DConditionStandIn(cfg)
-        self.vae = VAEEncoderStandIn(vae_channels)
-        self.text_encoder = nn.Linear(1, 1)   # only `.parameters()` is touched (`optimize_token.py:74`)
-        torch.random.set_rng_state(g)
+        # weight init under a forked RNG: `torch.manual_seed` also reseeds every CUDA generator, and a pipeline
+        # constructor must not leave all ranks of a job with the same CUDA seed (they would draw the same noise)
+        devices = list(range(torch.cuda.device_count())) if torch.cuda.is_available() else []
+        with torch.random.fork_rng(devices=devices):
+            torch.manual_seed(seed)
+            self.unet = UNet2DConditionStandIn(cfg)
+            self.vae = VAEEncoderStandIn(vae_channels)
+            self.text_encoder = nn.Linear(1, 1)   # only `.parameters()` is touched (`optimize_token.py:74`)
         self.scheduler = DDIMSchedulerStandIn()
         self.cfg = cfg
 

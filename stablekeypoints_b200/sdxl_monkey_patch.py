@@ -118,7 +118,6 @@ class AttentionStore(AttentionControl):
         self.max_query_tokens = max_query_tokens
         self.max_captured_layers = max_captured_layers     # first N up-path cross-attention layers (`ptp_utils.py:508-512`)
         self.stop_after_capture = False
-        self.context_shared = False
 
 
 def register_attention_control(model, controller, feature_upsample_res=128):
@@ -141,7 +140,7 @@ def register_attention_control(model, controller, feature_upsample_res=128):
                        and n <= getattr(controller, "max_query_tokens", 32 ** 2)
                        and len(store["up_cross"]) < getattr(controller, "max_captured_layers", 4))
             q = self.to_q(x)
-            shared = is_cross and getattr(controller, "context_shared", False) and b > 1
+            shared = is_cross and b > 1 and context.shape[0] == b and context.stride(0) == 0   # context.expand(B, ...)
             ctx = (context[:1] if shared else context) if is_cross else x
             k = self.to_k(ctx)
             if capture:

@@ -39,7 +39,13 @@ def _worker(rank, world, port, out):
     full = D.interleave_shards(D.all_gather_cat(rows), n)
     # 5. sharded dataset
     ds = D.shard_dataset(list(range(n)))
-    out[rank] = dict(mine=mine, g=g, ctx=ctx, full=full, ds=[ds[i] for i in range(len(ds))])
+    # 6. per-rank random streams (the reference draws an independent affine per image, invertable_transform.py:42-57;
+    #    every process starts from the same default seed, so ranks must derive their own)
+    from stablekeypoints_b200.invertable_transform import RandomAffineWithInverse
+    g_cpu, g_dev = D.rank_generators("cpu", seed=11)
+    theta = RandomAffineWithInverse(degrees=15, scale=(0.8, 1.0), translate=(0.25, 0.25)).sample_theta(2, g_cpu)
+    out[rank] = dict(mine=mine, g=g, ctx=ctx, full=full, ds=[ds[i] for i in range(len(ds))], theta=theta,
+                     noise=torch.randn(3, generator=g_dev))
     D.barrier()
     dist.destroy_process_group()
 
@@ -54,6 +60,8 @@ def test_gloo_world2_sharding_allreduce_and_gathers():
     assert sorted(a["mine"] + b["mine"]) == list(range(7)) and not set(a["mine"]) & set(b["mine"])
     assert abs(len(a["mine"]) - len(b["mine"])) <= 1
     assert a["ds"] == a["mine"] and b["ds"] == b["mine"]
+    assert not torch.equal(a["theta"], b["theta"]) and not torch.equal(a["noise"], b["noise"])
+    assert not torch.equal(a["theta"][0], a["theta"][1])           # and independent per image within a rank
     for r in (a, b):
         assert torch.allclose(r["g"], torch.full((1, 5, 3), 1.5))
         assert torch.equal(r["ctx"], torch.zeros(2, 2))
@@ -68,6 +76,10 @@ def test_single_process_helpers_are_noops():
     D.broadcast_(t)
     assert torch.equal(D.all_gather_cat(t), t) and list(D.shard_range(5)) == [0, 1, 2, 3, 4]
     assert D.init_from_env() == (0, 0, 1)
+    assert D.rank_generators("cpu") == (None, None)       # single process, no seed: the global generators stay in charge
+    g1, _ = D.rank_generators("cpu", seed=3)
+    g2, _ = D.rank_generators("cpu", seed=3)
+    assert torch.equal(torch.rand(4, generator=g1), torch.rand(4, generator=g2))
 
 
 def test_vote_top_k_counts_and_tie_rule():

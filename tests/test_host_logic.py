@@ -40,7 +40,14 @@ def test_registration_counts_up_block_layers_and_gate_matches_reference():
     assert [h.side for h in store] == [4, 4, 4, 8]
     assert [h.heads for h in store] == [8, 8, 8, 4]
     h0 = store[0]
-    assert h0.q.shape == (2, 16, 128) and h0.k.shape == (2, 7, 128) and h0.shape == (2 * 8, 32 * 32, 7)
+    # the batch shares one context (context.expand): k is projected once; the handle still reports the reference's shape
+    assert h0.q.shape == (2, 16, 128) and h0.k.shape == (1, 7, 128) and h0.k_shared and h0.shape == (2 * 8, 32 * 32, 7)
+    ctl.reset()
+    # a genuinely per-sample context through the same controller is never collapsed to sample 0's
+    with torch.no_grad():
+        unet(torch.randn(2, 4, cfg.latent_side, cfg.latent_side), torch.zeros(2, dtype=torch.int64), torch.randn(2, 7, cfg.context_dim))
+    h1 = ctl.step_store["attn"][0]
+    assert h1.k.shape == (2, 7, 128) and not h1.k_shared
     ctl.reset()
     assert ctl.step_store == {"attn": []}
 
@@ -54,7 +61,6 @@ def test_gate_is_parameterised_for_the_64x64_extension_and_early_stop():
     assert [h.side for h in ctl.step_store["attn"]] == [4, 4, 4, 8, 8, 8, 16, 16, 16]
     ctl2 = ptp_utils.AttentionStore()
     ctl2.stop_after_capture = True
-    ctl2.context_shared = True
     ptp_utils.register_attention_control(unet, ctl2, feature_upsample_res=32)
     with torch.no_grad():
         assert _run(unet, cfg, ctl2, B=3)              # raised StopForward after the 4th captured layer
