@@ -61,3 +61,14 @@ def gaussian_circle(pos, size=64, sigma=16, device="cuda"):
 def gaussian_circles(pos, size=64, sigma=16, device="cuda"):
     """`optimize_token.py:226-242`: pos (S,N,2); mean over the S subjects -> (N,size,size)."""
     return ops.gaussian_circles(pos.to(device=device, dtype=torch.float32).contiguous(), int(size), float(sigma))
+
+
+def to_channels_last(ldm):
+    """Stores the UNet's / VAE's convolution weights in NHWC (`torch.channels_last`); activations follow from the first
+    convolution on.  cuDNN's tensor-core convolutions compute in NHWC: with the default NCHW tensors every convolution
+    of the stock trunk is bracketed by `nchwToNhwc` / `nhwcToNchw` copies (7.2 % of the device time of an optimisation
+    step, profiles/r1e_launches.txt).  A memory-layout setting of stock PyTorch: no arithmetic changes (SURVEY.md §8(f)
+    rank 1, caller-side UNet economy; the reference itself runs NCHW, `optimize_token.py:36-44`)."""
+    for m in (ldm.unet, ldm.vae):
+        m.to(memory_format=torch.channels_last)
+    return ldm
