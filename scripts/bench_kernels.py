@@ -11,10 +11,11 @@ dev = "cuda:0"
 spec = [(16, 1280, 20), (16, 1280, 20), (16, 1280, 20), (32, 640, 10)]
 g = torch.Generator().manual_seed(0)
 qs = [(torch.randn(B, s * s, C, generator=g) * 1.5).to(dev).requires_grad_(True) for s, C, h in spec]
-ks = [torch.randn(1, 500, C, generator=g).to(dev).requires_grad_(True) for s, C, h in spec]
+T = int(os.environ.get("BK_T", "500"))
+ks = [torch.randn(1, T, C, generator=g).to(dev).requires_grad_(True) for s, C, h in spec]
 heads = [h for _, _, h in spec]
 sc = [(C // h) ** -0.5 for _, C, h in spec]
-idx = torch.stack([torch.randperm(500, generator=g)[:10] for _ in range(B)]).to(dev)
+idx = torch.stack([torch.randperm(T, generator=g)[:10] for _ in range(B)]).to(dev)
 w = torch.randn(B, 10, 128, 128, generator=g).to(dev)
 
 
@@ -31,7 +32,7 @@ _lib.timing_start()
 for _ in range(10):
     run()
 t = _lib.timing_summary()
-flops = 2 * 128 * 128 * 500 * (3 * 1280 + 640) * B
+flops = 2 * 128 * 128 * T * (3 * 1280 + 640) * B
 for k, v in t.items():
     ms = v["ms"] / v["calls"]
     mult = 1 if "fwd" in k else 2

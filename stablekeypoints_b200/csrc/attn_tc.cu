@@ -182,18 +182,32 @@ __global__ void tc_prep_k_kernel(const float* __restrict__ k, int T, int C, int 
 namespace skp {
 
 // shared-memory carve-up (offsets from a 1024-byte aligned base)
-template <int NPROD>
+template <int NPROD, int BN = TC_BN, bool LR = false>
 struct TcSmem {
-  static constexpr int kStages = NPROD == 3 ? 2 : 4;
-  static constexpr int kStageBytes = (NPROD == 3 ? 2 : 1) * (TC_A_BYTES + TC_B_BYTES);
-  static constexpr int kTiles = kStages * kStageBytes;                 // 192 KB either way
-  static constexpr int kBarOff = kTiles;                               // full[], empty[], tfull[2][2], tempty[2][2], xfull[2]
-  static constexpr int kNumBars = 2 * kStages + 10;
+  // BN = 256: one CTA per SM, 192 KB of operand stages.  BN = 128: TWO CTAs per SM (each 256 TMEM columns, <= 113 KB of
+  // shared memory): one stage -- the other CTA of the SM fills the bubbles a single stage leaves.
+  // LR ("upsample after the logits"): the A operand is the interpolation table of the CTA's pixel tile, which depends on
+  // the layer's source size only: it stays RESIDENT (up to 128 taps = two 64-tap blocks, hi + lo = 64 KB) and is reloaded
+  // when the source size changes (once per CTA for the SD capture sets) instead of once per (layer, head) unit; the ring
+  // then only carries the B operand (the window of native-resolution logits).  The kernel is co-limited by the L2 -> SM
+  // operand traffic (13.8 GB per 8-image call with A in the ring = 5.6 TB/s at 2.44 ms): 96 -> 64 KB per unit.
+  static constexpr int kBBytes = BN * TC_BK * 2;
+  static constexpr int kAResident = LR ? 4 * TC_A_BYTES : 0;           // [k-block 0: hi, lo][k-block 1: hi, lo]
+  static constexpr int kStages = BN == 128 ? 1 : (NPROD == 3 ? 2 : 4);
+  static constexpr int kStageBytes = (NPROD == 3 ? 2 : 1) * ((LR ? 0 : TC_A_BYTES) + kBBytes);
+  static constexpr int kRingOff = kAResident;
+  static constexpr int kTiles = kAResident + kStages * kStageBytes;    // 192 KB (BN = 256); 64 / 96 KB (BN = 128)
+  static constexpr int kBarOff = kTiles;                               // full[], empty[], tfull[2][2], tempty[2][2], xfull[2], afull
+  static constexpr int kNumBars = 2 * kStages + 11;
   static constexpr int kTmemPtrOff = kBarOff + 8 * kNumBars;
   static constexpr int kTokOff = kTmemPtrOff + 8;                      // int tok[TC_MAX_SEL]
-  static constexpr int kStatsOff = kTokOff + 4 * TC_MAX_SEL;           // float2 stats[2 buf][8 part][128 row]
+  static constexpr int kAmaxOff = kTokOff + 4 * TC_MAX_SEL;            // float amax[FW_MAX_UNITS]: max |s_low| of every unit's (image, head)
+  static constexpr int kStatsOff = kAmaxOff + 4 * 128;                 // float2 stats[2 buf][8 part][128 row]
   static constexpr int kTotal = kStatsOff + 2 * 8 * TC_BM * 8;
-  static constexpr int kDynamic = kTotal + 1024;                       // slack for manual 1024 B alignment
+  // slack for the manual 1024 B alignment of the tiles.  Two CTAs per SM leave 115712 B each: the BN = 128 / LR layout
+  // (115440 B) keeps 256 B of slack -- the dynamic window starts 1 KB-aligned on sm_100 and the kernel traps if not
+  static constexpr int kSlack = (BN == 128 && LR) ? 256 : 1024;
+  static constexpr int kDynamic = kTotal + kSlack;
 };
 
 // Phase profiler of the softmax warps (diagnostic builds only: nvcc -DSKP_FWD_PROF): cycles per phase averaged
@@ -235,29 +249,55 @@ __device__ __forceinline__ float exp2_poly(float x) {
 // (setmaxnreg.dec), warpgroups 1-4 = 16 softmax warps take them (setmaxnreg.inc): 64 fp32 accumulators + one
 // 32-column TMEM chunk per thread.  The softmax side is latency bound (dependent FMNMX / FADD chains, MUFU and
 // tcgen05.ld round trips), so it runs four warps per scheduler rather than two wide ones.
+//
+// BN = tokens per CTA.  256 (default): one CTA per SM, a cluster of two covers T <= 512.  128 (SKP_FWD_BN=128, A/B only):
+// the same work as TWO CTAs per SM (cluster of four), written to test whether a second resident CTA, out of phase with
+// the first, would fill the MUFU pipe while the first is in its latency-bound phases.  Measured on B200 (round 2): it does
+// NOT -- 2.91 ms against 2.63 ms per 8-image call, and the same holds for fully independent CTAs (T = 128, no cluster:
+// 0.77 ms = 3.1 ms per 512 tokens) with or without a half-unit start skew between the CTAs of an SM.  Each softmax warp
+// needs ~5 k cycles per unit for its 64 columns whatever else is resident (a dependent-latency chain: 6 TMEM round trips,
+// the statistics exchange, 64-element FMNMX / FADD / FFMA chains), so throughput = resident warps / that latency, and the
+// resident warps are capped by the register file (128 x 256 fp32 accumulators per SM = half of it).  An M=128 K=16 SS-mode
+// MMA takes 64 cycles at N = 128 and 128 at N = 256 (scripts/mma_rate_probe.cu): the tensor time per token is the same.
 constexpr int FW_SOFTMAX_WARP0 = 4;
-constexpr int FW_PARTS = 4;                                   // column quarters per CTA
-constexpr int FW_MAX_PARTS = 2 * FW_PARTS;                    // parts of a cluster of two
-constexpr int FW_QCOLS = TC_BN / FW_PARTS;                    // 64 tokens per thread
-constexpr int FW_SOFTMAX_THREADS = 128 * FW_PARTS;            // 16 warps
-constexpr int FW_THREADS = 32 * FW_SOFTMAX_WARP0 + FW_SOFTMAX_THREADS;   // 640
+constexpr int FW_QCOLS = 64;                                  // tokens per softmax thread
+constexpr int FW_MAX_PARTS = 8;                               // 64-token column parts of a cluster (2 x 4 or 4 x 2)
 constexpr int FW_NH = 1;                                      // column groups a TMEM buffer is handed over in (1 or 2)
-constexpr int FW_SOFTMAX_REGS = 112;   // 128*32 + 512*112 == 640*96: setmaxnreg.inc only draws from what .dec released
-template <int NPROD, int NSPLIT, bool SELECT>
-__global__ void __launch_bounds__(FW_THREADS, 1)
+// LR: when max |s_low| of a unit's (image, head) is below this, every logit of the unit lies in +-1.9 x 50 = +-95 (log2
+// units) and exp2 of the RAW logits can neither overflow (512 x 2^95 < 2^127) nor lose a row (2^-95 is a normal float):
+// the softmax is shift invariant, so the row-max pass (a TMEM round trip per chunk + 64 compares per thread + the exchange
+// of maxima) is skipped and the unit's statistics are (m = 0, l = sum exp2 S).  Larger logits take the max-subtracted path.
+constexpr float FW_FAST_ABSMAX = 50.0f;
+constexpr int FW_MAX_UNITS = 128;                             // units (heads of all captured layers) the flag table holds
+template <int BN>
+struct FwCfg {
+  static constexpr int kParts = BN / FW_QCOLS;                // column parts per CTA: 4 or 2
+  static constexpr int kSoftmaxThreads = 128 * kParts;        // 16 or 8 warps
+  static constexpr int kThreads = 32 * FW_SOFTMAX_WARP0 + kSoftmaxThreads;   // 640 or 384
+  static constexpr int kMinCtas = BN == 128 ? 2 : 1;
+  // setmaxnreg.inc only draws from what .dec released: 128*32 + 512*112 == 640*96 (BN 256); 128*32 + 256*104 == 384*80 (BN 128)
+  static constexpr int kSoftmaxRegs = BN == 128 ? 104 : 112;
+};
+template <int NPROD, int NSPLIT, bool SELECT, int BN, bool LR>
+__global__ void __launch_bounds__(FwCfg<BN>::kThreads, FwCfg<BN>::kMinCtas)
 attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
-  using SM = TcSmem<NPROD>;
+  using SM = TcSmem<NPROD, BN, LR>;
+  static_assert(!LR || NPROD == 3, "the upsample-after-logits operands are hi + lo pairs");
+  constexpr int FW_PARTS = FwCfg<BN>::kParts;
+  constexpr int FW_SOFTMAX_THREADS = FwCfg<BN>::kSoftmaxThreads;
+  constexpr int TC_BNk = BN;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = ptx::smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
   uint8_t* base_ptr = smem_raw + (base - raw);
+  if (base - raw > static_cast<uint32_t>(SM::kSlack)) __trap();
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t cta_rank = NSPLIT > 1 ? ptx::cluster_ctarank() : 0u;
   const int tile = blockIdx.x / NSPLIT;
   const int b = blockIdx.y;
   const int p0 = tile * TC_BM;
-  const int tok0 = static_cast<int>(cta_rank) * TC_BN;
+  const int tok0 = static_cast<int>(cta_rank) * TC_BNk;
 
   auto bar_full = [&](int s) { return base + SM::kBarOff + 8u * s; };
   auto bar_empty = [&](int s) { return base + SM::kBarOff + 8u * (SM::kStages + s); };
@@ -265,8 +305,10 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
   auto bar_tfull = [&](int i, int hf) { return base + SM::kBarOff + 8u * (2 * SM::kStages + 2 * i + hf); };
   auto bar_tempty = [&](int i, int hf) { return base + SM::kBarOff + 8u * (2 * SM::kStages + 4 + 2 * i + hf); };
   auto bar_xfull = [&](int i) { return base + SM::kBarOff + 8u * (2 * SM::kStages + 8 + i); };
+  const uint32_t bar_afull = base + SM::kBarOff + 8u * (2 * SM::kStages + 10);
   volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(base_ptr + SM::kTmemPtrOff);
   int* tok_s = reinterpret_cast<int*>(base_ptr + SM::kTokOff);
+  float* amax_s = reinterpret_cast<float*>(base_ptr + SM::kAmaxOff);
   float2* stats = reinterpret_cast<float2*>(base_ptr + SM::kStatsOff);
 
   // ---- one-time setup ---------------------------------------------------------------------
@@ -282,11 +324,23 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
       }
       ptx::mbar_init(bar_xfull(i), FW_SOFTMAX_THREADS);
     }
+    ptx::mbar_init(bar_afull, 1);
     ptx::fence_barrier_init();
+  }
+  if (LR && threadIdx.x < FW_MAX_UNITS) {
+    // unit u = global head index -> (layer, head); +inf (slow path) for units past the table or without a bound
+    float v = INFINITY;
+    const int u = threadIdx.x;
+    if (u < P.ops.total_heads && P.ops.total_heads <= FW_MAX_UNITS) {
+      int l = 0;
+      while (l + 1 < P.ops.n_layers && u >= P.ops.head_base[l + 1]) ++l;
+      if (P.ops.absmax[l]) v = __int_as_float(P.ops.absmax[l][blockIdx.y * P.ops.heads[l] + (u - P.ops.head_base[l])]);
+    }
+    amax_s[u] = v;
   }
   if (SELECT && threadIdx.x < TC_MAX_SEL) tok_s[threadIdx.x] = threadIdx.x < P.n_idx ? static_cast<int>(P.token_idx[blockIdx.y * P.idx_stride + threadIdx.x]) : -1;
   if (warp == 1) {
-    ptx::tmem_alloc(ptx::smem_u32(const_cast<uint32_t*>(tmem_ptr)), 512);
+    ptx::tmem_alloc(ptx::smem_u32(const_cast<uint32_t*>(tmem_ptr)), 2 * BN);
     ptx::tmem_relinquish();
   }
   ptx::tc_fence_before();
@@ -309,28 +363,44 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
         }
       }
       uint32_t it = 0;
+      int a_key = -1;                     // LR: source size of the interpolation table resident in the A region
       for (int l = 0; l < P.ops.n_layers; ++l) {
         const int h = P.ops.heads[l], d = P.ops.d[l];
         const int nkb = (d + TC_BK - 1) / TC_BK;
+        // LR: the window of native-resolution logits the tile interpolates from starts at this source pixel
+        const int b_k0 = LR ? lr_window_row0(tile, P.ops.win_s[l], P.ops.R, P.ops.win_nr[l]) * P.ops.win_s[l] : 0;
+        if (LR && P.ops.win_s[l] != a_key) {
+          // new interpolation table: every MMA issued so far read the old one -- wait for the last ring slot's release
+          // (tcgen05.commit covers all earlier MMAs of the issuing thread), then load all k-blocks on their own barrier
+          if (it > 0) ptx::mbar_wait_hint(bar_empty((it - 1) % SM::kStages), ((it - 1) / SM::kStages) & 1u, 2000u);
+          ptx::mbar_arrive_expect_tx(bar_afull, nkb * 2 * TC_A_BYTES);
+          for (int kb = 0; kb < nkb; ++kb) {
+            ptx::tma_load_3d(base + kb * 2 * TC_A_BYTES, &P.ops.q_map[l][0], bar_afull, kb * TC_BK, 0, tile);
+            ptx::tma_load_3d(base + kb * 2 * TC_A_BYTES + TC_A_BYTES, &P.ops.q_map[l][1], bar_afull, kb * TC_BK, 0, tile);
+          }
+          a_key = P.ops.win_s[l];
+        }
         for (int head = 0; head < h; ++head) {
           const int qz = b * h + head;
           const int kz = (P.ops.k_shared[l] ? 0 : b * h) + head;
-          // operand coordinates: (k offset, row, batch) of A and B.  Staged q' / k, or (lr) the interpolation table of
-          // this tile and the window of native-resolution logits it interpolates from
-          const bool lr = P.ops.lr != 0;
-          const int a_row = lr ? 0 : p0, a_z = lr ? tile : qz, b_z = lr ? qz : kz;
-          const int b_k0 = lr ? lr_window_row0(tile, P.ops.win_s[l], P.ops.R, P.ops.win_nr[l]) * P.ops.win_s[l] : 0;
+          // operand coordinates: (k offset, row, batch).  Staged: A = q' tile, B = k; LR: B = the logit window of (image, head)
+          const int b_z = LR ? qz : kz;
           for (int kb = 0; kb < nkb; ++kb, ++it) {
             const int s = it % SM::kStages;
             const uint32_t ph = (it / SM::kStages) & 1u;
             ptx::mbar_wait_hint(bar_empty(s), ph ^ 1u, 2000u);
             ptx::mbar_arrive_expect_tx(bar_full(s), SM::kStageBytes);
-            const uint32_t st = base + s * SM::kStageBytes;
-            ptx::tma_load_3d(st, &P.ops.q_map[l][0], bar_full(s), kb * TC_BK, a_row, a_z);
-            ptx::tma_load_3d(st + TC_A_BYTES, &P.ops.k_map[l][0], bar_full(s), b_k0 + kb * TC_BK, tok0, b_z);
-            if (NPROD == 3) {
-              ptx::tma_load_3d(st + TC_A_BYTES + TC_B_BYTES, &P.ops.q_map[l][1], bar_full(s), kb * TC_BK, a_row, a_z);
-              ptx::tma_load_3d(st + 2 * TC_A_BYTES + TC_B_BYTES, &P.ops.k_map[l][1], bar_full(s), b_k0 + kb * TC_BK, tok0, b_z);
+            const uint32_t st = base + SM::kRingOff + s * SM::kStageBytes;
+            if (LR) {
+              ptx::tma_load_3d(st, &P.ops.k_map[l][0], bar_full(s), b_k0 + kb * TC_BK, tok0, b_z);
+              ptx::tma_load_3d(st + SM::kBBytes, &P.ops.k_map[l][1], bar_full(s), b_k0 + kb * TC_BK, tok0, b_z);
+            } else {
+              ptx::tma_load_3d(st, &P.ops.q_map[l][0], bar_full(s), kb * TC_BK, p0, qz);
+              ptx::tma_load_3d(st + TC_A_BYTES, &P.ops.k_map[l][0], bar_full(s), kb * TC_BK, tok0, b_z);
+              if (NPROD == 3) {
+                ptx::tma_load_3d(st + TC_A_BYTES + SM::kBBytes, &P.ops.q_map[l][1], bar_full(s), kb * TC_BK, p0, qz);
+                ptx::tma_load_3d(st + 2 * TC_A_BYTES + SM::kBBytes, &P.ops.k_map[l][1], bar_full(s), kb * TC_BK, tok0, b_z);
+              }
             }
           }
         }
@@ -343,33 +413,45 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
       // groups half a unit out of phase).  Measured on B200: an SS-mode M=128 K=16 MMA costs ~130 cycles
       // whether N is 128 or 256 (the A tile is re-read from shared memory each time), so halving N doubles
       // the tensor time per unit (3400 vs 1700 cycles) and the stagger buys nothing: one N = 256 hand-over.
-      constexpr uint32_t idesc = ptx::umma_idesc_bf16(TC_BM, TC_BN / FW_NH);
-      constexpr uint32_t kHalfB = (TC_BN / FW_NH) * 128;     // byte offset of the second group's first token row in a K tile
-      uint32_t it = 0, u = 0;
+      constexpr uint32_t idesc = ptx::umma_idesc_bf16(TC_BM, TC_BNk / FW_NH);
+      constexpr uint32_t kHalfB = (TC_BNk / FW_NH) * 128;     // byte offset of the second group's first token row in a K tile
+      uint32_t it = 0, u = 0, a_cnt = 0;
+      int a_key = -1;
       for (int l = 0; l < P.ops.n_layers; ++l) {
         const int h = P.ops.heads[l], d = P.ops.d[l];
         const int nkb = (d + TC_BK - 1) / TC_BK;
+        if (LR && P.ops.win_s[l] != a_key) {      // the resident interpolation table of this source size has landed
+          ptx::mbar_wait_hint(bar_afull, a_cnt & 1u, 2000u);
+          ptx::tc_fence_after();
+          ++a_cnt;
+          a_key = P.ops.win_s[l];
+        }
         for (int head = 0; head < h; ++head, ++u) {
           const uint32_t buf = u & 1u;
           for (int kb = 0; kb < nkb; ++kb, ++it) {
             const int s = it % SM::kStages;
             ptx::mbar_wait_hint(bar_full(s), (it / SM::kStages) & 1u, 2000u);
             ptx::tc_fence_after();
-            const uint32_t st = base + s * SM::kStageBytes;
+            const uint32_t st = base + SM::kRingOff + s * SM::kStageBytes;
+            // operand tiles of this k-block: LR: A resident, ring = [B hi | B lo]; staged: ring = [A hi | B hi | A lo | B lo]
+            const uint32_t a_hi_s = LR ? base + kb * 2 * TC_A_BYTES : st;
+            const uint32_t a_lo_s = LR ? a_hi_s + TC_A_BYTES : st + TC_A_BYTES + SM::kBBytes;
+            const uint32_t b_hi_s = LR ? st : st + TC_A_BYTES;
+            const uint32_t b_lo_s = LR ? st + SM::kBBytes : st + 2 * TC_A_BYTES + SM::kBBytes;
             const int nk16 = (min(TC_BK, d - kb * TC_BK) + 15) / 16;
             for (int hf = 0; hf < FW_NH; ++hf) {
               if (kb == 0) {
                 ptx::mbar_wait_hint(bar_tempty(buf, hf), ((u >> 1) & 1u) ^ 1u, 2000u);   // softmax drained this half buffer
                 ptx::tc_fence_after();
               }
-              const uint32_t d_tmem = tmem_base + buf * TC_BN + hf * (TC_BN / FW_NH);
+              const uint32_t d_tmem = tmem_base + buf * TC_BNk + hf * (TC_BNk / FW_NH);
               for (int kk = 0; kk < nk16; ++kk) {
-                const uint64_t a_hi = ptx::umma_desc_sw128(st + kk * 32);
-                const uint64_t b_hi = ptx::umma_desc_sw128(st + TC_A_BYTES + hf * kHalfB + kk * 32);
+                const uint64_t a_hi = ptx::umma_desc_sw128(a_hi_s + kk * 32);
+                const uint64_t b_hi = ptx::umma_desc_sw128(b_hi_s + hf * kHalfB + kk * 32);
                 const uint32_t first = (kb | kk) != 0;
                 if (NPROD == 3) {
-                  const uint64_t a_lo = ptx::umma_desc_sw128(st + TC_A_BYTES + TC_B_BYTES + kk * 32);
-                  const uint64_t b_lo = ptx::umma_desc_sw128(st + 2 * TC_A_BYTES + TC_B_BYTES + hf * kHalfB + kk * 32);
+                  const uint64_t a_lo = ptx::umma_desc_sw128(a_lo_s + kk * 32);
+                  const uint64_t b_lo = ptx::umma_desc_sw128(b_lo_s + hf * kHalfB + kk * 32);
                   ptx::umma_bf16(d_tmem, a_hi, b_lo, idesc, first);
                   ptx::umma_bf16(d_tmem, a_lo, b_hi, idesc, 1u);
                   ptx::umma_bf16(d_tmem, a_hi, b_hi, idesc, 1u);
@@ -386,7 +468,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
     }
     }
   } else {
-    ptx::setmaxnreg_inc<FW_SOFTMAX_REGS>();
+    ptx::setmaxnreg_inc<FwCfg<BN>::kSoftmaxRegs>();
     // =========================== softmax / accumulate warps =================================
     // Thread = (pixel row, 64-token quarter of the CTA's 256 tokens): four warps per scheduler hide the
     // MUFU / TMEM latencies of each other.  Per unit u = (layer, head) the order is
@@ -409,19 +491,31 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
 
     // normalise + accumulate unit uu, whose exponentials this thread parked in TMEM one iteration ago
     FW_PROF_DECL
-    auto pass_c = [&](uint32_t uu, float m_own, float wgt_u) {
+    auto pass_c = [&](uint32_t uu, float m_own, float wgt_u, bool fast_uu) {
       const uint32_t buf = uu & 1u, par = (uu >> 1) & 1u;
-      const uint32_t taddr = t_lane + buf * TC_BN + col0;
+      const uint32_t taddr = t_lane + buf * TC_BNk + col0;
       ptx::mbar_wait_hint(bar_xfull(buf), par, 500u);
       FW_PROF(3)
-      float mg = -INFINITY;
+      float mg = 0.0f, total = 0.0f;
+      if (fast_uu) {
+        // every part posted (0, sum exp2 S): the row's statistics are the plain sum, four independent adds deep
+        float tq[NPART];
 #pragma unroll
-      for (int q = 0; q < NPART; ++q) mg = fmaxf(mg, stats[(buf * FW_MAX_PARTS + q) * TC_BM + row].x);
-      float total = 0.0f;
+        for (int q = 0; q < NPART; ++q) tq[q] = stats[(buf * FW_MAX_PARTS + q) * TC_BM + row].y;
 #pragma unroll
-      for (int q = 0; q < NPART; ++q) {
-        const float2 sq = stats[(buf * FW_MAX_PARTS + q) * TC_BM + row];
-        total += sq.y * pow2_int(sq.x - mg);
+        for (int st = 1; st < NPART; st <<= 1)
+#pragma unroll
+          for (int q = 0; q + st < NPART; q += 2 * st) tq[q] += tq[q + st];
+        total = tq[0];
+      } else {
+        mg = -INFINITY;
+#pragma unroll
+        for (int q = 0; q < NPART; ++q) mg = fmaxf(mg, stats[(buf * FW_MAX_PARTS + q) * TC_BM + row].x);
+#pragma unroll
+        for (int q = 0; q < NPART; ++q) {
+          const float2 sq = stats[(buf * FW_MAX_PARTS + q) * TC_BM + row];
+          total += sq.y * pow2_int(sq.x - mg);
+        }
       }
       if (P.row_stats != nullptr && part == 0)
         reinterpret_cast<float2*>(P.row_stats)[(static_cast<int64_t>(b) * P.ops.total_heads + uu) * P.R2 + p0 + row] =
@@ -462,6 +556,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
 
     uint32_t u = 0;
     float m_prev = 0.0f, wgt_prev = 0.0f;
+    bool fast_prev = false;
     for (int l = 0; l < P.ops.n_layers; ++l) {
       const int h = P.ops.heads[l];
       const float wgt = P.ops.weight[l];
@@ -470,12 +565,14 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
         ptx::mbar_wait_hint(bar_tfull(buf, hf), par, 500u);
         ptx::tc_fence_after();
         FW_PROF(0)
-        const uint32_t taddr = t_lane + buf * TC_BN + col0;
+        const uint32_t taddr = t_lane + buf * TC_BNk + col0;
+        // bounded logits (see FW_FAST_ABSMAX): no row-max pass, m = 0.  Uniform over the cluster: one flag per (image, head)
+        const bool fast = LR && amax_s[u < FW_MAX_UNITS ? u : 0] <= FW_FAST_ABSMAX && u < FW_MAX_UNITS;
         // ---- pass A: row max over my columns (four independent chains)
         float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
 #pragma unroll
         for (int c = 0; c < NCH; ++c) {
-          if (32 * c < ncol) {
+          if (!fast && 32 * c < ncol) {
             uint32_t v[32];
             ptx::tmem_ld32(taddr + 32 * c, v);
             ptx::tmem_ld_wait();
@@ -497,10 +594,10 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
         }
         // Rounded up to an integer: any m >= the true max stabilises the exponentials equally well, and
         // integer-valued maxima make every rescale 2^(m_part - m_row) an exponent-field add, not a MUFU.
-        const float m = ceilf(fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)));
+        const float m = fast ? 0.0f : ceilf(fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)));
         FW_PROF(2)
         // ---- pass C of the previous unit
-        if (u > 0) pass_c(u - 1, m_prev, wgt_prev);
+        if (u > 0) pass_c(u - 1, m_prev, wgt_prev, fast_prev);
         // ---- pass B: exponentials (parked back in TMEM) and their sum
         float s0 = 0.0f, s1 = 0.0f, s2 = 0.0f, s3 = 0.0f;
 #pragma unroll
@@ -554,6 +651,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
         }
         m_prev = m;
         wgt_prev = wgt;
+        fast_prev = fast;
         FW_PROF(10)
       }
     }
@@ -563,7 +661,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
              blockIdx.x, warp, pf_acc[0] / u, pf_acc[1] / u, pf_acc[2] / u, pf_acc[3] / u, pf_acc[4] / u, pf_acc[5] / u, pf_acc[6] / u,
              pf_acc[7] / u, pf_acc[8] / u, pf_acc[9] / u, pf_acc[10] / u);
 #endif
-    if (u > 0) pass_c(u - 1, m_prev, wgt_prev);
+    if (u > 0) pass_c(u - 1, m_prev, wgt_prev, fast_prev);
     // ---- write-out: lanes hold consecutive pixels -> 128 B coalesced stores per token
     if (!SELECT) {
       float* out = P.maps + (static_cast<int64_t>(b) * P.T + tok0 + col0) * P.R2 + p0 + row;
@@ -586,7 +684,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
   if (NSPLIT > 1) ptx::cluster_sync();   // nobody exits while a peer may still store into its smem
   if (warp == 1) {
     ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem_base, 512);
+    ptx::tmem_dealloc(tmem_base, 2 * BN);
   }
 }
 
@@ -671,14 +769,14 @@ size_t attn_map_tc_workspace(const skp_attn_layer* h_layers, int n_layers, int B
   return attn_map_staged_workspace(h_layers, n_layers, B, T, R, precision);
 }
 
-template <int NPROD, int NSPLIT, bool SELECT>
+template <int NPROD, int NSPLIT, bool SELECT, int BN = TC_BN, bool LR = false>
 static int launch_tc(const TcParams& P, int B, int R2, cudaStream_t st) {
-  using SM = TcSmem<NPROD>;
-  auto kern = attn_map_fwd_tc_kernel<NPROD, NSPLIT, SELECT>;
+  using SM = TcSmem<NPROD, BN, LR>;
+  auto kern = attn_map_fwd_tc_kernel<NPROD, NSPLIT, SELECT, BN, LR>;
   SKP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::kDynamic));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(static_cast<unsigned>(R2 / TC_BM * NSPLIT), static_cast<unsigned>(B), 1);
-  cfg.blockDim = dim3(FW_THREADS, 1, 1);
+  cfg.blockDim = dim3(FwCfg<BN>::kThreads, 1, 1);
   cfg.dynamicSmemBytes = SM::kDynamic;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
@@ -761,14 +859,25 @@ int attn_map_fwd_tc(const skp_attn_layer* h_layers, int n_layers, int B, int T, 
   TcParams P;
   memset(&P, 0, sizeof(P));
   const bool lr = fwd_uses_lr(h_layers, n_layers, B, T, R, token_idx ? n_idx : 0, precision);
-  int rc = lr ? tc_prepare_lr(h_layers, n_layers, B, T, R, workspace, st, &P.ops, nullptr)
+  // SKP_FWD_BN=128: 128-token CTAs, two per SM (cluster of four) -- measured slower, kept for A/B runs (see FwCfg)
+  const char* ebn = getenv("SKP_FWD_BN");
+  const bool bn128 = lr && x3 && T > TC_BN && ebn && atoi(ebn) == 128;
+  int rc = lr ? tc_prepare_lr(h_layers, n_layers, B, T, R, workspace, st, &P.ops, nullptr, bn128 ? 128 : TC_BN)
               : tc_prepare(h_layers, n_layers, B, T, R, x3, workspace, st, &P.ops, nullptr);
   if (rc != SKP_OK) return rc;
+  if (const char* ef = getenv("SKP_FWD_FAST"))      // SKP_FWD_FAST=0: always the max-subtracted path (A/B runs, tests)
+    if (atoi(ef) == 0)
+      for (int l = 0; l < TC_MAX_LAYERS; ++l) P.ops.absmax[l] = nullptr;
   P.T = T; P.R2 = R2;
   P.n_idx = token_idx ? n_idx : 0;
   P.token_idx = token_idx; P.maps = maps; P.idx_stride = idx_stride; P.row_stats = row_stats;
   const bool sel = token_idx != nullptr;
   const bool split = T > TC_BN;
+  if (bn128) return sel ? launch_tc<3, 4, true, 128, true>(P, B, R2, st) : launch_tc<3, 4, false, 128, true>(P, B, R2, st);
+  if (lr) {
+    if (split) return sel ? launch_tc<3, 2, true, TC_BN, true>(P, B, R2, st) : launch_tc<3, 2, false, TC_BN, true>(P, B, R2, st);
+    return sel ? launch_tc<3, 1, true, TC_BN, true>(P, B, R2, st) : launch_tc<3, 1, false, TC_BN, true>(P, B, R2, st);
+  }
   if (x3) {
     if (split) return sel ? launch_tc<3, 2, true>(P, B, R2, st) : launch_tc<3, 2, false>(P, B, R2, st);
     return sel ? launch_tc<3, 1, true>(P, B, R2, st) : launch_tc<3, 1, false>(P, B, R2, st);

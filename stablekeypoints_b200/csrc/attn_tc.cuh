@@ -35,6 +35,10 @@ struct TcOperands {
   // lr_window_row0(tile) * s + 64 kb
   int lr, R;
   int win_s[TC_MAX_LAYERS], win_nr[TC_MAX_LAYERS];
+  // lr: bit pattern of max |s_low| over all tokens and source pixels of every (image, head): [layer][b * heads + head].
+  // Bounds the logits of that (image, head) at every feature pixel (|S| <= 1.9 max |s_low|: bicubic weights, A = -0.75,
+  // sum |w| <= 1.375 per axis), which lets the forward skip the row-max pass when exp2 cannot over/underflow.
+  const int* absmax[TC_MAX_LAYERS];
 };
 
 // window of source rows [r0, r0 + nr) a 128-pixel tile of the R x R output interpolates from (s x s source)
@@ -52,7 +56,7 @@ LrGeom lr_geometry(int s, int R);
 bool attn_map_lr_supported(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int n_idx);
 size_t attn_map_lr_workspace(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R);
 int tc_prepare_lr(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, void* workspace, cudaStream_t st,
-                  TcOperands* out, char** ws_end);
+                  TcOperands* out, char** ws_end, int bn = TC_BN);   // bn: token rows per TMA box of the logit window (k_map)
 
 bool attn_map_tc_supported(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int n_idx);
 size_t attn_map_tc_workspace(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int precision);

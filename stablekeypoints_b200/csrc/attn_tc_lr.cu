@@ -37,6 +37,7 @@ struct LrGemmParams {
   CUtensorMap q_map[2];   // (d, s*s, B*h), box (64, 256, 1)
   __nv_bfloat16* out_hi;  // [B*h][T][s*s]
   __nv_bfloat16* out_lo;
+  int* absmax;            // [B*h]: bit pattern of max |s_low| of the (image, head) (atomicMax on non-negative floats)
   int T, s2, d, heads, k_shared;
 };
 
@@ -77,6 +78,7 @@ size_t attn_map_lr_workspace(const skp_attn_layer* h_layers, int n_layers, int B
     total += 2 * tc_align_up(static_cast<size_t>(a.k_shared ? 1 : B) * T * a.C * 2, 1024);     // k hi, lo
     total += 2 * tc_align_up(static_cast<size_t>(B) * a.heads * T * s2 * 2, 1024);             // s_low hi, lo
     total += 2 * tc_align_up(tiles * TC_BM * lr_geometry(a.s, R).kw * 2, 1024);                // W hi, lo
+    total += tc_align_up(static_cast<size_t>(B) * a.heads * sizeof(int), 1024);                // max |s_low| per (image, head)
   }
   return total + 1024;
 }
@@ -220,6 +222,7 @@ __global__ void __launch_bounds__(LRG_THREADS) lr_logits_kernel(const __grid_con
     uint8_t* stg_hi = base_ptr + (warp - 2) * (2 * LRG_STG_BYTES);
     uint8_t* stg_lo = stg_hi + LRG_STG_BYTES;
     const int t0 = tt * LRG_BM + quad * 32;
+    float amax = 0.0f;          // rows / columns past T / s*s hold zeros (TMA zero fill): they cannot raise the maximum
 #pragma unroll 1
     for (int half = 0; half < 2; ++half) {
       const int col0 = st * LRG_BN + half * 128;
@@ -235,6 +238,7 @@ __global__ void __launch_bounds__(LRG_THREADS) lr_logits_kernel(const __grid_con
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const float f0 = __uint_as_float(v[8 * q + 2 * j]), f1 = __uint_as_float(v[8 * q + 2 * j + 1]);
+            amax = fmaxf(amax, fmaxf(fabsf(f0), fabsf(f1)));
             const __nv_bfloat16 h0 = __float2bfloat16_rn(f0), h1 = __float2bfloat16_rn(f1);
             const __nv_bfloat162 hh = __halves2bfloat162(h0, h1);
             const __nv_bfloat162 ll = __halves2bfloat162(__float2bfloat16_rn(f0 - __bfloat162float(h0)),
@@ -260,6 +264,8 @@ __global__ void __launch_bounds__(LRG_THREADS) lr_logits_kernel(const __grid_con
       }
       __syncwarp();
     }
+    amax = warp_max(amax);
+    if (lane == 0 && P.absmax) atomicMax(P.absmax + z, __float_as_int(amax));   // non-negative floats order like their bit patterns
   }
   __syncwarp();
   ptx::tc_fence_before();
@@ -273,7 +279,7 @@ __global__ void __launch_bounds__(LRG_THREADS) lr_logits_kernel(const __grid_con
 // Stages the operands of the "upsample after the logits" formulation in `workspace` (launches on `st`) and fills
 // `O` so that the main kernels see A = W tables (q_map) and B = s_low (k_map) with d[l] = taps per tile.
 int tc_prepare_lr(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, void* workspace, cudaStream_t st,
-                  TcOperands* O, char** ws_end) {
+                  TcOperands* O, char** ws_end, int bn) {
   char* ws = reinterpret_cast<char*>(tc_align_up(reinterpret_cast<size_t>(workspace), 1024));
   const int tiles = R * R / TC_BM;
   __nv_bfloat16* w_tab[TC_MAX_LAYERS][2];
@@ -293,6 +299,8 @@ int tc_prepare_lr(const skp_attn_layer* h_layers, int n_layers, int B, int T, in
     const size_t sb = static_cast<size_t>(B) * a.heads * T * s2 * 2, wb = static_cast<size_t>(tiles) * TC_BM * g.kw * 2;
     __nv_bfloat16 *q_hi = take(qb), *q_lo = take(qb), *k_hi = take(kb), *k_lo = take(kb), *s_hi = take(sb), *s_lo = take(sb);
     __nv_bfloat16 *w_hi = take(wb), *w_lo = take(wb);   // reserved even when an earlier layer's table is reused
+    int* absmax = reinterpret_cast<int*>(take(static_cast<size_t>(B) * a.heads * sizeof(int)));
+    SKP_CUDA(cudaMemsetAsync(absmax, 0, static_cast<size_t>(B) * a.heads * sizeof(int), st));
     const float mult = a.scale * 1.4426950408889634f;
     lr_split_heads_kernel<<<(::skp::note_launch(), dim3(s2, B)), 256, 0, st>>>(a.q, s2, a.C, a.heads, mult, q_hi, q_lo);
     lr_split_heads_kernel<<<(::skp::note_launch(), dim3(T, Bk)), 256, 0, st>>>(a.k, T, a.C, a.heads, 1.0f, k_hi, k_lo);
@@ -315,20 +323,20 @@ int tc_prepare_lr(const skp_attn_layer* h_layers, int n_layers, int B, int T, in
     if (rc == SKP_OK) rc = tc_encode_map(&G.q_map[0], q_hi, d, s2, B * a.heads, LRG_BN);
     if (rc == SKP_OK) rc = tc_encode_map(&G.q_map[1], q_lo, d, s2, B * a.heads, LRG_BN);
     if (rc != SKP_OK) return rc;
-    G.out_hi = s_hi; G.out_lo = s_lo; G.T = T; G.s2 = s2; G.d = d; G.heads = a.heads; G.k_shared = a.k_shared;
+    G.out_hi = s_hi; G.out_lo = s_lo; G.absmax = absmax; G.T = T; G.s2 = s2; G.d = d; G.heads = a.heads; G.k_shared = a.k_shared;
     dim3 grid((T + LRG_BM - 1) / LRG_BM, (s2 + LRG_BN - 1) / LRG_BN, B * a.heads);
     lr_logits_kernel<<<(::skp::note_launch(), grid), LRG_THREADS, LRG_DYNAMIC, st>>>(G);
     SKP_LAUNCH_CHECK();
     rc = tc_encode_map(&O->q_map[l][0], w_hi, g.kw, TC_BM, tiles, TC_BM);
     if (rc == SKP_OK) rc = tc_encode_map(&O->q_map[l][1], w_lo, g.kw, TC_BM, tiles, TC_BM);
-    if (rc == SKP_OK) rc = tc_encode_map(&O->k_map[l][0], s_hi, s2, T, B * a.heads, TC_BN);
-    if (rc == SKP_OK) rc = tc_encode_map(&O->k_map[l][1], s_lo, s2, T, B * a.heads, TC_BN);
+    if (rc == SKP_OK) rc = tc_encode_map(&O->k_map[l][0], s_hi, s2, T, B * a.heads, bn);
+    if (rc == SKP_OK) rc = tc_encode_map(&O->k_map[l][1], s_lo, s2, T, B * a.heads, bn);
     if (rc != SKP_OK) return rc;
     O->k_ptr[l][0] = k_hi; O->k_ptr[l][1] = k_lo;
     O->s_ptr[l][0] = s_hi; O->s_ptr[l][1] = s_lo;
     O->heads[l] = a.heads; O->d[l] = g.kw; O->k_shared[l] = 0; O->head_base[l] = base;
     O->weight[l] = a.weight / a.heads; O->scale[l] = a.scale;
-    O->win_s[l] = a.s; O->win_nr[l] = g.nr;
+    O->win_s[l] = a.s; O->win_nr[l] = g.nr; O->absmax[l] = absmax;
     base += a.heads;
   }
   O->n_layers = n_layers; O->total_heads = base; O->lr = 1; O->R = R;

@@ -85,7 +85,10 @@ class AttentionStore(AttentionControl):
 
     def forward(self, attn, is_cross: bool, place_in_unet: str):
         key = f"{place_in_unet}_{'cross' if is_cross else 'self'}"
-        if attn.shape[1] <= self.max_query_tokens:      # the reference's memory gate (`:58`)
+        # the reference's memory gate (`:58`) is on the QUERY positions of the layer; a handle reports the upsampled
+        # (B*h, R^2, T) shape of the tensor it stands for, so its native side is what the gate sees
+        n_query = attn.side ** 2 if isinstance(attn, CapturedAttention) else attn.shape[1]
+        if n_query <= self.max_query_tokens:
             self.step_store[key].append(attn)
         return attn
 

@@ -96,6 +96,33 @@ def test_attention_maps_vs_oracle_unequal_heads(ops, monkeypatch, precision, spe
         assert torch.allclose(got[b], want, rtol=1e-3, atol=1e-7)
 
 
+@pytest.mark.parametrize("fast", ["1", "0"])
+@pytest.mark.parametrize("qscale", [1.0, 6.0])
+def test_attention_maps_bounded_and_unbounded_logit_paths(ops, monkeypatch, fast, qscale):
+    """The forward skips the row-max pass when max |native-resolution logit| of an (image, head) bounds exp2 away from
+    over/underflow (attn_tc.cu FW_FAST_ABSMAX), else subtracts the row max: both against the fp64 oracle, with small
+    logits (bounded path unless SKP_FWD_FAST=0) and a mix of both in one call: the second layer's q is scaled so that its
+    native-resolution logits exceed the bound (max |s_low| ~ 65 > 50 log2 units; much larger logits leave the 1e-3 bar of
+    ANY bf16x3 product: the split drops the lo x lo term, 2^-17 relative to |S|).  Also: the statistics handed to the backward give the same gradients."""
+    monkeypatch.setenv("SKP_FWD_FAST", fast)
+    spec, T, R, B = [(16, 128, 2), (32, 64, 1)], 300, 128, 2
+    qs, ks, heads, sc = _random_layers(spec, T, B, 17, True)
+    qs[1] = qs[1] * qscale
+    qc, kc = [_cu(q) for q in qs], [_cu(k) for k in ks]
+    got, stats = ops.attention_maps(qc, kc, heads, sc, R, precision="auto", return_stats=True)
+    g = torch.Generator().manual_seed(3)
+    pix = torch.randperm(R * R, generator=g)[:96]
+    for b in range(B):
+        want, lse2 = O.attention_maps_at_pixels([q[b] for q in qs], [k[0] for k in ks], heads, sc, R, pix, return_lse2=True)
+        have = got[b].reshape(T, -1)[:, pix].cpu().double()
+        assert torch.allclose(have, want, rtol=1e-3, atol=1e-9), f"max rel {((have - want).abs() / (want + 1e-9)).max():.2e}"
+        st = stats[b][:, pix].cpu().double()
+        assert (st[..., 0] + torch.log2(st[..., 1]) - lse2).abs().max().item() < 1e-3
+        if qscale > 1.0:
+            assert float(stats[b][heads[0]:, pix, 0].abs().max()) > 0 and float(stats[b][:heads[0], pix, 0].abs().max()) == (0.0 if fast == "1" else float(stats[b][:heads[0], pix, 0].abs().max()))
+    assert torch.allclose(got.sum(1), torch.ones(B, R, R, device=DEV), atol=2e-5)
+
+
 def test_attention_maps_backward_matches_oracle_autograd(ops):
     spec, T, R, B = [(4, 64, 4), (8, 32, 2)], 40, 16, 2
     qs, ks, heads, sc = _random_layers(spec, T, B, 5, True)
