@@ -417,6 +417,9 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
       constexpr uint32_t kHalfB = (TC_BNk / FW_NH) * 128;     // byte offset of the second group's first token row in a K tile
       uint32_t it = 0, u = 0, a_cnt = 0;
       int a_key = -1;
+#ifdef SKP_FWD_PROF
+      long long mp_full = 0, mp_tempty = 0, mp_issue = 0, mp_t0 = clock64(), mp_t;
+#endif
       for (int l = 0; l < P.ops.n_layers; ++l) {
         const int h = P.ops.heads[l], d = P.ops.d[l];
         const int nkb = (d + TC_BK - 1) / TC_BK;
@@ -430,8 +433,14 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
           const uint32_t buf = u & 1u;
           for (int kb = 0; kb < nkb; ++kb, ++it) {
             const int s = it % SM::kStages;
+#ifdef SKP_FWD_PROF
+            mp_t = clock64();
+#endif
             ptx::mbar_wait_hint(bar_full(s), (it / SM::kStages) & 1u, 2000u);
             ptx::tc_fence_after();
+#ifdef SKP_FWD_PROF
+            mp_full += clock64() - mp_t;
+#endif
             const uint32_t st = base + SM::kRingOff + s * SM::kStageBytes;
             // operand tiles of this k-block: LR: A resident, ring = [B hi | B lo]; staged: ring = [A hi | B hi | A lo | B lo]
             const uint32_t a_hi_s = LR ? base + kb * 2 * TC_A_BYTES : st;
@@ -441,8 +450,15 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
             const int nk16 = (min(TC_BK, d - kb * TC_BK) + 15) / 16;
             for (int hf = 0; hf < FW_NH; ++hf) {
               if (kb == 0) {
+#ifdef SKP_FWD_PROF
+                mp_t = clock64();
+#endif
                 ptx::mbar_wait_hint(bar_tempty(buf, hf), ((u >> 1) & 1u) ^ 1u, 2000u);   // softmax drained this half buffer
                 ptx::tc_fence_after();
+#ifdef SKP_FWD_PROF
+                mp_tempty += clock64() - mp_t;
+                mp_t = clock64();
+#endif
               }
               const uint32_t d_tmem = tmem_base + buf * TC_BNk + hf * (TC_BNk / FW_NH);
               for (int kk = 0; kk < nk16; ++kk) {
@@ -462,9 +478,17 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
               if (kb == nkb - 1) ptx::umma_commit(bar_tfull(buf, hf));   // this half's logits are in TMEM
             }
             ptx::umma_commit(bar_empty(s));      // smem slot free once these MMAs retire
+#ifdef SKP_FWD_PROF
+            mp_issue += clock64() - mp_t;
+#endif
           }
         }
       }
+#ifdef SKP_FWD_PROF
+      if (blockIdx.x < 2 && blockIdx.y == 0)
+        printf("cta %d mma thread: per unit: wait operands %lld, wait tempty %lld, issue %lld, total %lld\n", blockIdx.x,
+               mp_full / u, mp_tempty / u, mp_issue / u, (clock64() - mp_t0) / u);
+#endif
     }
     }
   } else {
