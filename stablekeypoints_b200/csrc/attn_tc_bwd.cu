@@ -22,6 +22,18 @@
 
 namespace skp {
 
+// Diagnostic builds only (nvcc -DSKP_DIAG): the SKP_BWD_DBG environment switches (bits 1 / 2 / 4 skip the reductions, the
+// adjoint, the drain -- WRONG gradients by design, for phase timing; 8 prints the in-kernel phase profile, which allocates
+// and synchronises; 32 / 128 / 256 change the MMA issue order) and the clock reads behind them.  The product library is
+// built without them: no debug switch can change a result, nothing allocates or synchronises (header contract).
+#ifdef SKP_DIAG
+#define BW_CLK() clock64()
+#define BW_DBG(P) ((P).dbg)
+#else
+#define BW_CLK() 0ll
+#define BW_DBG(P) 0
+#endif
+
 constexpr int BW_SEL = 16;            // selected tokens per launch (UMMA N of the S_sel product)
 constexpr int BW_KSEL_BYTES = BW_SEL * 128;   // 16 rows x 128 B
 constexpr int BW_DS_BYTES = TC_BM * TC_BN * 2;   // 64 KB: dS tile, 4 slabs of [128 px][64 tok] bf16
@@ -38,7 +50,6 @@ struct BwdParams {
   // "upsample after the logits" launches (template LR; ops then holds W tables / native-resolution logits, ksel_map the
   // selected tokens' logit rows): fp32 accumulator of the logit gradient dz[b*h + head][token][s*s] of every layer
   float* dz[TC_MAX_LAYERS];
-  CUtensorMap s128_map[TC_MAX_LAYERS][2];   // native-resolution logits with a 128-token box (attn_map_bwd_lr128_kernel)
   const unsigned char* wr0[TC_MAX_LAYERS];  // first source row of every tile's window (lr_window_row0 costs two divisions
                                             // and a float->int chain, ~700 cycles of dependent latency per call)
   int ghead[TC_MAX_LAYERS];                 // first head of the layer among ALL captured layers (row_stats index)
@@ -50,7 +61,7 @@ struct BwdParams {
   const float* dpT;                         // pixel-major copy (B, R2, 16), planes j >= n_idx zero
   const float* row_stats;                   // (B, total_heads, R2, 2)
   unsigned long long* prof;                 // SKP_BWD_DBG & 8: per-phase cycle counters of CTA 0
-  int dbg;                                  // SKP_BWD_DBG bits (profiling experiments only): 1 no reductions, 2 no adjoint, 4 no drain
+  int dbg;                                  // SKP_DIAG builds: SKP_BWD_DBG bits (profiling experiments only): 1 no reductions, 2 no adjoint, 4 no drain
 };
 
 // k_sel[(b*h + head)][j][dd] = k[bk][token_idx[b][j]][head*d + dd]  (rows j >= n_idx are zero)
@@ -308,11 +319,11 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       auto issue_S = [&](int l, uint32_t jt, int mode) {
         const uint32_t qs = base + SM::kQOff + (jt & 1) * SM::kQStage;
         const uint32_t tsel = tm_sel(jt), selbar = bar_selfull(jt);
-        long long c0 = clock64();
+        long long c0 = BW_CLK();
         ptx::mbar_wait_hint(bar_qfull(jt & 1), (jt >> 1) & 1u, 2000u);
         ptx::tc_fence_after();
-        pf_q += clock64() - c0;
-        c0 = clock64();
+        pf_q += BW_CLK() - c0;
+        c0 = BW_CLK();
         const uint32_t id_S = bw_idesc(TC_BM, TC_BN, 0, 0), id_sel = bw_idesc(TC_BM, BW_SEL, 0, 0);
         // LR: the K dimension is the 64-tap window (the launcher only sends such layers here): fixed trip count, the
         // descriptors of the unrolled loops are the stage's base descriptors plus constants
@@ -332,7 +343,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
             }
           }
           ptx::umma_commit(selbar);
-          pf_is += clock64() - c0;
+          pf_is += BW_CLK() - c0;
           return;
         }
         if (mode == 2) {
@@ -350,7 +361,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
             }
           }
           ptx::umma_commit(bar_sfull);
-          pf_is += clock64() - c0;
+          pf_is += BW_CLK() - c0;
           return;
         }
         // The selected tokens' logits go out two per 256-token MMA during the first half of the product and get their
@@ -391,7 +402,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
           if (kk + 1 == n_selblk) ptx::umma_commit(selbar);
         }
         ptx::umma_commit(bar_sfull);
-        pf_is += clock64() - c0;
+        pf_is += BW_CLK() - c0;
       };
       bool s_issued = false;       // S of this unit went out early, in the previous iteration
       for (int u = u_begin; u < u_end; ++u, ++it) {
@@ -403,25 +414,25 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         s_issued = false;
         // LR, next tile in the same window (no k / k_sel reload, whose TMA would wait for this unit's MMAs): its S_sel only
         // needs the next W tile, so it runs on the idle tensor pipe while the softmax warps are in this unit's dS pass
-        const bool early = LR && u + 1 < u_end && nxu.hg == x.hg && nxu.b == x.b && nxu.r0 == x.r0 && !(P.dbg & 32);
-        const bool sel_early = early && !(P.dbg & 128);
+        const bool early = LR && u + 1 < u_end && nxu.hg == x.hg && nxu.b == x.b && nxu.r0 == x.r0 && !(BW_DBG(P) & 32);
+        const bool sel_early = early && !(BW_DBG(P) & 128);
         if (sel_early) issue_S(nxu.l, it + 1, 1);
         // ... and its S as soon as every softmax thread holds the last chunk of S(u) in registers (s_free), one chunk of
         // exponentials + the corrections ahead of ds_full
-        const bool s_ahead = early && !(P.dbg & 256);
+        const bool s_ahead = early && !(BW_DBG(P) & 256);
         if (s_ahead) {
-          long long c9 = clock64();
+          long long c9 = BW_CLK();
           ptx::mbar_wait_hint(bar_sfree, it & 1u, 1000u);
           ptx::tc_fence_after();
-          pf_ds += clock64() - c9;
+          pf_ds += BW_CLK() - c9;
           issue_S(nxu.l, it + 1, sel_early ? 2 : 0);
           s_issued = true;
         }
         // ---- wait for dS (bf16, [px][tok]) in shared memory
-        long long c0 = clock64();
+        long long c0 = BW_CLK();
         ptx::mbar_wait_hint(bar_dsfull, it & 1u, 2000u);
         ptx::tc_fence_after();
-        pf_ds += clock64() - c0;
+        pf_ds += BW_CLK() - c0;
         // LR: the softmax warps are done with S(u), so S(u+1) can run AHEAD of the dz product of this unit (they start
         // on the next unit ~1200 cycles earlier and only need dz(u) retired before their first dS store).  Not when
         // the next unit reloads k / k_sel: those single buffers are only refilled after this unit's MMAs retire.
@@ -429,7 +440,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
           issue_S(nxu.l, it + 1, sel_early ? 2 : 0);
           s_issued = true;
         }
-        c0 = clock64();
+        c0 = BW_CLK();
         if (!LR) {
           // dQ' (128 px x d) = dS (K-major A, K = 256 tokens) * K_hi (MN-major B: rows = tokens)
           const uint32_t id_dq = bw_idesc(TC_BM, d, 0, 1);
@@ -454,11 +465,11 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         }
         ptx::umma_commit(bar_mmadone);
         ptx::umma_commit(bar_qempty(st));
-        pf_id += clock64() - c0;
+        pf_id += BW_CLK() - c0;
         dk_fresh = bw_flush_between<LR>(P, x, nxu, u + 1 >= u_end);
         x = nxu;
       }
-      if (P.prof && blockIdx.x == ((P.dbg >> 6) & 1)) {
+      if (P.prof && blockIdx.x == ((BW_DBG(P) >> 6) & 1)) {
         P.prof[0] = pf_q; P.prof[1] = pf_ds; P.prof[8] = pf_is; P.prof[9] = pf_id;
       }
     }
@@ -493,7 +504,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         dpr[4 * q] = g.x; dpr[4 * q + 1] = g.y; dpr[4 * q + 2] = g.z; dpr[4 * q + 3] = g.w;
       }
     };
-    long long pf[6] = {0, 0, 0, 0, 0, 0}, c_end = clock64();   // profiler (SKP_BWD_DBG & 8), kept in registers
+    long long pf[6] = {0, 0, 0, 0, 0, 0}, c_end = BW_CLK();   // profiler (SKP_BWD_DBG & 8), kept in registers
     bool mma_pending = false;      // LR: the wait for the previous unit's dz product is deferred to the first dS store
     BwUnit x = bw_decode(P, u_begin), nxu = x;
     for (int u = u_begin; u < u_end; ++u, ++it, x = nxu) {
@@ -539,12 +550,12 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       // registers right behind it, i.e. wait for the whole memory round trip at the loop top (780 cycles per unit).
       if (LR) load_row(u + 1 < u_end ? nxu : x, nx_ml, nx_dp);
 
-      long long c1 = clock64();
+      long long c1 = BW_CLK();
       pf[5] += c1 - c_end;                      // loop top: decode, prefetch issue, table rebuilds
       ptx::mbar_wait(bar_selfull(it), (it >> 1) & 1u);
       ptx::tc_fence_after();
-      pf[0] += clock64() - c1;
-      c1 = clock64();
+      pf[0] += BW_CLK() - c1;
+      c1 = BW_CLK();
       float delta = 0.0f;
       {
         uint32_t sv[BW_SEL];
@@ -561,10 +572,10 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       // ---- dS = P * (dP - delta): dense part -P*delta for my 128 columns, then the n_idx corrections
       const float nd = -delta * inv_l;
       {
-        long long c2 = clock64();
+        long long c2 = BW_CLK();
         ptx::mbar_wait(bar_sfull, it & 1u);
         ptx::tc_fence_after();
-        const long long c3 = clock64();
+        const long long c3 = BW_CLK();
         pf[0] += c3 - c2;
         c1 += c3 - c2;                          // the dS slot of the profile excludes this wait
       }
@@ -634,13 +645,13 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
           *e = __float2bfloat16_rn(__bfloat162float(*e) + dp[j]);
         }
       }
-      pf[1] += clock64() - c1;
-      c1 = clock64();
+      pf[1] += BW_CLK() - c1;
+      c1 = BW_CLK();
       ptx::fence_proxy_async();
       ptx::tc_fence_before();
       ptx::mbar_arrive(bar_dsfull);
-      pf[2] += clock64() - c1;
-      c1 = clock64();
+      pf[2] += BW_CLK() - c1;
+      c1 = BW_CLK();
 
       // next unit's row statistics / upstream gradients: issued here, where this thread would only spin
       // on the dQ/dK MMAs, they are back long before the next loop top
@@ -653,9 +664,9 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       } else {
         mma_pending = true;
       }
-      pf[3] += clock64() - c1;
-      c1 = clock64();
-      if (!LR && ch * 32 < d && !(P.dbg & 4)) {
+      pf[3] += BW_CLK() - c1;
+      c1 = BW_CLK();
+      if (!LR && ch * 32 < d && !(BW_DBG(P) & 4)) {
         uint32_t v[32];
         ptx::tmem_ld32(tm_dQ + lane_off + ch * 32, v);
         ptx::tmem_ld_wait();
@@ -683,7 +694,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         const int n_out = rows_per_tile * s * n_c4;
         const float ratio = static_cast<float>(s) / R;
         float* dq = P.dq[x.l] + static_cast<int64_t>(x.b) * s * s * C + x.head * d;
-        for (int o = stid; o < ((P.dbg & 2) ? 0 : n_out); o += TC_SOFTMAX_THREADS) {
+        for (int o = stid; o < ((BW_DBG(P) & 2) ? 0 : n_out); o += TC_SOFTMAX_THREADS) {
           const int c4 = p2 ? o & (n_c4 - 1) : o % n_c4;
           const int sx = p2 ? (o >> lg_c4) & (s - 1) : (o / n_c4) % s;
           const int yy = p2 ? o >> (lg_c4 + lg_s) : o / (n_c4 * s);
@@ -738,14 +749,14 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
 #pragma unroll
           for (int a = 0; a < 4; ++a) {
             const int sy = min(max(iy - 1 + a, 0), s - 1);
-            if (!(P.dbg & 1)) red_add_v4(dq + static_cast<int64_t>(sy * s + sx) * C + c4 * 4, wy[a] * acc.x, wy[a] * acc.y, wy[a] * acc.z, wy[a] * acc.w);
+            if (!(BW_DBG(P) & 1)) red_add_v4(dq + static_cast<int64_t>(sy * s + sx) * C + c4 * 4, wy[a] * acc.x, wy[a] * acc.y, wy[a] * acc.z, wy[a] * acc.w);
           }
         }
       }
       named_bar_sync(2, TC_SOFTMAX_THREADS);
       }
-      pf[4] += clock64() - c1;
-      c_end = clock64();
+      pf[4] += BW_CLK() - c1;
+      c_end = BW_CLK();
       if (LR) {
         // ---- dz: flush the window accumulator (token rows x 64 taps) when the next tile leaves this window
         if (lr_flush && ch < n_mh) {
@@ -759,7 +770,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
             uint32_t v[32];
             ptx::tmem_ld32(tm_dK + lane_off + ch * 64 + c * 32, v);
             ptx::tmem_ld_wait();
-            if (t < P.T && !(P.dbg & 1)) {
+            if (t < P.T && !(BW_DBG(P) & 1)) {
 #pragma unroll
               for (int q = 0; q < 8; ++q)
                 if (c * 32 + q * 4 < nvalid)
@@ -793,353 +804,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         ptx::tc_fence_before();
       }
     }
-    if (P.prof && blockIdx.x == ((P.dbg >> 6) & 1) && stid == 0) {
-      for (int i = 0; i < 5; ++i) P.prof[2 + i] = pf[i];
-      P.prof[7] = it;
-      P.prof[10] = pf[5];
-    }
-  }
-
-  // ---- teardown -------------------------------------------------------------------------------
-  __syncwarp();
-  ptx::tc_fence_before();
-  __syncthreads();
-  if (warp == 1) {
-    ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem_base, 512);
-  }
-}
-
-// ==========================================================================================
-// Pipelined upsample-after-logits backward: 128 tokens per CTA.
-//
-// The 256-token kernel above runs S -> dS -> dz serially through ONE S accumulator (256 of the 512 TMEM columns) and ONE
-// 64 KB dS tile.  With 128 tokens per CTA both are double-buffered (S 2 x 128 + dz 64 + S_sel 2 x 16 columns; dS 2 x 32 KB),
-// so the S product of unit u+2 and the dz product of unit u run on the tensor pipe while the softmax warps work on unit
-// u+1.  Operands: W_hi in a 3-stage ring (it is read twice: S(u) and, a unit later, dz(u)), W_lo in a 2-stage ring, the
-// window of native-resolution logits of the CTA's 128 tokens (+ the selected tokens' rows) double-buffered.
-// bf16x3 only, layers with 64-tap windows only (the launcher sends everything else to the kernel above).
-// ==========================================================================================
-struct Bw128Smem {
-  static constexpr int kWhiOff = 0;                                   // 3 x 16 KB
-  static constexpr int kWloOff = kWhiOff + 3 * TC_A_BYTES;            // 2 x 16 KB
-  static constexpr int kWinBytes = 2 * TC_A_BYTES + 2 * BW_KSEL_BYTES;  // s_low window hi | lo (128 tok x 64 taps), s_sel hi | lo
-  static constexpr int kWinOff = kWloOff + 2 * TC_A_BYTES;            // 2 buffers
-  static constexpr int kDsOff = kWinOff + 2 * kWinBytes;              // 2 x 32 KB: [128 px][128 tok] bf16 as two 64-token slabs
-  static constexpr int kDsBytes = TC_BM * 128 * 2;
-  static constexpr int kBarOff = kDsOff + 2 * kDsBytes;               // whfull[3] whempty[3] wlfull[2] wlempty[2] kfull[2] kempty[2] sfull[2] dsfull[2] dzdone[2]
-  static constexpr int kTmemPtrOff = kBarOff + 8 * 20;
-  static constexpr int kTokOff = kTmemPtrOff + 8;
-  static constexpr int kTotal = kTokOff + 4 * BW_SEL;
-  static constexpr int kDynamic = kTotal + 1024;
-};
-static_assert(Bw128Smem::kDynamic <= 232448, "shared memory budget");
-static_assert(Bw128Smem::kWinOff % 1024 == 0 && Bw128Smem::kWinBytes % 1024 == 0 && Bw128Smem::kDsOff % 1024 == 0, "swizzle atoms");
-
-__global__ void __launch_bounds__(BW_THREADS, 1)
-attn_map_bwd_lr128_kernel(const __grid_constant__ BwdParams P) {
-  using SM = Bw128Smem;
-  extern __shared__ uint8_t smem_raw[];
-  const uint32_t raw = ptx::smem_u32(smem_raw);
-  const uint32_t base = (raw + 1023u) & ~1023u;
-  uint8_t* base_ptr = smem_raw + (base - raw);
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nq = (P.T + 127) / 128;
-  const int quarter = blockIdx.x % nq, chunk = blockIdx.x / nq;
-  const int u_begin = static_cast<int>(static_cast<int64_t>(chunk) * P.n_units / P.n_chunks);
-  const int u_end = static_cast<int>(static_cast<int64_t>(chunk + 1) * P.n_units / P.n_chunks);
-  const int tok0 = quarter * 128;
-  const int ntok = max(0, min(128, P.T - tok0));
-
-  auto bar = [&](int i) { return base + SM::kBarOff + 8u * i; };
-  auto bar_whfull = [&](int s) { return bar(s); };
-  auto bar_whempty = [&](int s) { return bar(3 + s); };
-  auto bar_wlfull = [&](int s) { return bar(6 + s); };
-  auto bar_wlempty = [&](int s) { return bar(8 + s); };
-  auto bar_kfull = [&](int s) { return bar(10 + s); };
-  auto bar_kempty = [&](int s) { return bar(12 + s); };
-  auto bar_sfull = [&](int s) { return bar(14 + s); };
-  auto bar_dsfull = [&](int s) { return bar(16 + s); };
-  auto bar_dzdone = [&](int s) { return bar(18 + s); };
-  volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(base_ptr + SM::kTmemPtrOff);
-  volatile int* tok_s = reinterpret_cast<volatile int*>(base_ptr + SM::kTokOff);
-
-  if (threadIdx.x == 0) {
-    for (int i = 0; i < 20; ++i) ptx::mbar_init(bar(i), (i == 16 || i == 17) ? TC_SOFTMAX_THREADS : 1);
-    ptx::fence_barrier_init();
-  }
-  if (warp == 1) {
-    ptx::tmem_alloc(ptx::smem_u32(const_cast<uint32_t*>(tmem_ptr)), 512);
-    ptx::tmem_relinquish();
-  }
-  ptx::tc_fence_before();
-  __syncthreads();
-  ptx::tc_fence_after();
-  const uint32_t tmem_base = *tmem_ptr;
-  const uint32_t tm_dz = tmem_base + 256;
-  auto tm_S = [&](uint32_t i) { return tmem_base + 128u * (i & 1u); };
-  auto tm_sel = [&](uint32_t i) { return tmem_base + 320u + 16u * (i & 1u); };
-  // does unit nx interpolate from another window (or belong to another image / head) than unit x?
-  auto new_window = [&](const BwUnit& x, const BwUnit& nx) {
-    return nx.hg != x.hg || nx.b != x.b || nx.r0 != x.r0;
-  };
-
-  if (warp < BW_SOFTMAX_WARP0) {
-    ptx::setmaxnreg_dec<56>();
-    if (warp == 0) {
-      // =========================== TMA producer (one lane) ===================================
-      if (lane == 0) {
-        uint32_t it = 0, wc = 0;
-        BwUnit x = bw_decode(P, u_begin), px = x;
-        for (int u = u_begin; u < u_end; ++u, ++it, px = x, x = bw_next(P, x)) {
-          const uint32_t hs = it % 3, ls = it & 1;
-          ptx::mbar_wait_hint(bar_whempty(hs), ((it / 3) & 1u) ^ 1u, 2000u);
-          ptx::mbar_arrive_expect_tx(bar_whfull(hs), TC_A_BYTES);
-          ptx::tma_load_3d(base + SM::kWhiOff + hs * TC_A_BYTES, &P.ops.q_map[x.l][0], bar_whfull(hs), 0, 0, x.tile);
-          ptx::mbar_wait_hint(bar_wlempty(ls), ((it >> 1) & 1u) ^ 1u, 2000u);
-          ptx::mbar_arrive_expect_tx(bar_wlfull(ls), TC_A_BYTES);
-          ptx::tma_load_3d(base + SM::kWloOff + ls * TC_A_BYTES, &P.ops.q_map[x.l][1], bar_wlfull(ls), 0, 0, x.tile);
-          if (it == 0 || new_window(px, x)) {
-            const uint32_t kb = wc & 1;
-            ptx::mbar_wait_hint(bar_kempty(kb), ((wc >> 1) & 1u) ^ 1u, 2000u);
-            ptx::mbar_arrive_expect_tx(bar_kfull(kb), SM::kWinBytes);
-            const uint32_t wb = base + SM::kWinOff + kb * SM::kWinBytes;
-            const int qz = x.b * P.ops.heads[x.l] + x.head, k0 = x.r0 * P.s[x.l];
-            ptx::tma_load_3d(wb, &P.s128_map[x.l][0], bar_kfull(kb), k0, tok0, qz);
-            ptx::tma_load_3d(wb + TC_A_BYTES, &P.s128_map[x.l][1], bar_kfull(kb), k0, tok0, qz);
-            ptx::tma_load_3d(wb + 2 * TC_A_BYTES, &P.ksel_map[x.l][0], bar_kfull(kb), k0, 0, qz);
-            ptx::tma_load_3d(wb + 2 * TC_A_BYTES + BW_KSEL_BYTES, &P.ksel_map[x.l][1], bar_kfull(kb), k0, 0, qz);
-            ++wc;
-          }
-        }
-      }
-    } else if (warp == 1) {
-      // =========================== MMA issuer (one lane) =====================================
-      if (lane == 0) {
-        const int n = u_end - u_begin;
-        long long pf_q = 0, pf_ds = 0, pf_is = 0, pf_id = 0;      // profiler (SKP_BWD_DBG & 8)
-        uint32_t wc = 0;                       // windows seen so far by issue_S
-        BwUnit xs = bw_decode(P, u_begin), pxs = xs;     // unit of the NEXT S product
-        uint32_t js = 0;
-        // S(j) = W(j) . window^T (128 px x 128 tokens) and S_sel(j) (128 px x 16 selected tokens), bf16x3
-        auto issue_S = [&]() {
-          if (js == 0 || new_window(pxs, xs)) {
-            if (js > 0) ptx::umma_commit(bar_kempty((wc - 1) & 1));    // every product on the previous window has been issued
-            ptx::mbar_wait_hint(bar_kfull(wc & 1), (wc >> 1) & 1u, 2000u);
-            ++wc;
-          }
-          const uint32_t kb = (wc - 1) & 1;
-          long long c0 = clock64();
-          ptx::mbar_wait_hint(bar_whfull(js % 3), (js / 3) & 1u, 2000u);
-          ptx::mbar_wait_hint(bar_wlfull(js & 1), (js >> 1) & 1u, 2000u);
-          ptx::tc_fence_after();
-          pf_q += clock64() - c0;
-          c0 = clock64();
-          const uint32_t a_hi0 = base + SM::kWhiOff + (js % 3) * TC_A_BYTES, a_lo0 = base + SM::kWloOff + (js & 1) * TC_A_BYTES;
-          const uint32_t b_hi0 = base + SM::kWinOff + kb * SM::kWinBytes, b_lo0 = b_hi0 + TC_A_BYTES;
-          const uint32_t s_hi0 = b_hi0 + 2 * TC_A_BYTES, s_lo0 = s_hi0 + BW_KSEL_BYTES;
-          const uint32_t id_S = bw_idesc(TC_BM, 128, 0, 0), id_sel = bw_idesc(TC_BM, BW_SEL, 0, 0);
-          for (int kk = 0; kk < TC_BK / 16; ++kk) {
-            const uint64_t a_hi = bw_desc(a_hi0 + kk * 32, 16, 1024), a_lo = bw_desc(a_lo0 + kk * 32, 16, 1024);
-            const uint64_t b_hi = bw_desc(b_hi0 + kk * 32, 16, 1024), b_lo = bw_desc(b_lo0 + kk * 32, 16, 1024);
-            const uint64_t s_hi = bw_desc(s_hi0 + kk * 32, 16, 1024), s_lo = bw_desc(s_lo0 + kk * 32, 16, 1024);
-            ptx::umma_bf16(tm_S(js), a_hi, b_lo, id_S, kk != 0);
-            ptx::umma_bf16(tm_S(js), a_lo, b_hi, id_S, 1u);
-            ptx::umma_bf16(tm_S(js), a_hi, b_hi, id_S, 1u);
-            ptx::umma_bf16(tm_sel(js), a_hi, s_lo, id_sel, kk != 0);
-            ptx::umma_bf16(tm_sel(js), a_lo, s_hi, id_sel, 1u);
-            ptx::umma_bf16(tm_sel(js), a_hi, s_hi, id_sel, 1u);
-          }
-          ptx::umma_commit(bar_sfull(js & 1));
-          ptx::umma_commit(bar_wlempty(js & 1));
-          pf_is += clock64() - c0;
-          pxs = xs;
-          xs = bw_next(P, xs);
-          ++js;
-        };
-        issue_S();
-        if (n > 1) issue_S();
-        bool dz_fresh = true;
-        BwUnit x = bw_decode(P, u_begin);
-        for (int i = 0; i < n; ++i) {
-          const BwUnit nxu = bw_next(P, x);
-          long long c0 = clock64();
-          ptx::mbar_wait_hint(bar_dsfull(i & 1), (i >> 1) & 1u, 2000u);
-          ptx::tc_fence_after();
-          pf_ds += clock64() - c0;
-          c0 = clock64();
-          // dz (128 tok x 64 taps) += dS^T (MN-major A: rows = pixels, two 64-token slabs) * W_hi (MN-major B: rows = pixels)
-          const uint32_t dsb = base + SM::kDsOff + (i & 1) * SM::kDsBytes, whi = base + SM::kWhiOff + (i % 3) * TC_A_BYTES;
-          const uint32_t id_dz = bw_idesc(128, TC_BK, 1, 1);
-          for (int k = 0; k < TC_BM / 16; ++k)
-            ptx::umma_bf16(tm_dz, bw_desc(dsb + k * 2048, 16384, 1024), bw_desc(whi + k * 2048, 16384, 1024), id_dz,
-                           (dz_fresh && k == 0) ? 0u : 1u);
-          ptx::umma_commit(bar_dzdone(i & 1));
-          ptx::umma_commit(bar_whempty(i % 3));
-          pf_id += clock64() - c0;
-          dz_fresh = i + 1 >= n || new_window(x, nxu);
-          if (i + 2 < n) issue_S();          // the softmax warps have read S(i): its accumulator takes S(i+2)
-          x = nxu;
-        }
-        if (P.prof && blockIdx.x == ((P.dbg >> 6) & 1)) {
-          P.prof[0] = pf_q; P.prof[1] = pf_ds; P.prof[8] = pf_is; P.prof[9] = pf_id;
-        }
-      }
-    }
-  } else {
-    ptx::setmaxnreg_inc<224>();
-    // =========================== softmax-recompute / dS warps ================================
-    const int quad = warp & 3;                 // TMEM lane quadrant this warp may access
-    const int ch = (warp - BW_SOFTMAX_WARP0) >> 2;   // 64-column half of the CTA's 128 tokens
-    const int row = quad * 32 + lane;
-    const int stid = threadIdx.x - BW_SOFTMAX_WARP0 * 32;   // 0..255
-    const int col0 = ch * 64;
-    const int ncol = max(0, min(64, ntok - col0));
-    const uint32_t lane_off = static_cast<uint32_t>(quad * 32) << 16;
-    uint32_t it = 0;
-    int prev_l = -1, prev_b = -1;
-    int tk[BW_SEL];                            // token ids of the selected planes of the current image
-    float2 nx_ml = make_float2(0.f, 1.f);
-    float nx_dp[BW_SEL];
-    auto load_row = [&](const BwUnit& y, float2& ml, float (&dpr)[BW_SEL]) {
-      const int pp = y.tile * TC_BM + row;
-      ml = __ldg(reinterpret_cast<const float2*>(P.row_stats) + (static_cast<int64_t>(y.b) * P.heads_all + P.ghead[y.l] + y.head) * P.R2 + pp);
-      // upstream gradients of the row: one 64-byte row of the pixel-major copy (4 x 16-byte loads instead of 16 scalar
-      // loads from 16 planes)
-      const float4* g4 = reinterpret_cast<const float4*>(P.dpT) + (static_cast<int64_t>(y.b) * P.R2 + pp) * (BW_SEL / 4);
-#pragma unroll
-      for (int q = 0; q < BW_SEL / 4; ++q) {
-        const float4 g = __ldg(g4 + q);
-        dpr[4 * q] = g.x; dpr[4 * q + 1] = g.y; dpr[4 * q + 2] = g.z; dpr[4 * q + 3] = g.w;
-      }
-    };
-    long long pf[6] = {0, 0, 0, 0, 0, 0}, c_end = clock64();
-    BwUnit x = bw_decode(P, u_begin), nxu = x;
-    for (int u = u_begin; u < u_end; ++u, ++it, x = nxu) {
-      nxu = bw_next(P, x);
-      const int s = P.s[x.l];
-      const float wgt = P.ops.weight[x.l];
-      if (x.l != prev_l || x.b != prev_b) {
-        named_bar_sync(1, TC_SOFTMAX_THREADS);
-        if (stid < BW_SEL) tok_s[stid] = stid < P.n_idx ? static_cast<int>(P.token_idx[x.b * P.idx_stride + stid]) : -1;
-        named_bar_sync(1, TC_SOFTMAX_THREADS);
-#pragma unroll
-        for (int j = 0; j < BW_SEL; ++j) tk[j] = tok_s[j];      // registers: the per-unit loops below read them 32 times
-        prev_l = x.l;
-        prev_b = x.b;
-      }
-      if (u == u_begin) load_row(x, nx_ml, nx_dp);
-      const float m = nx_ml.x, inv_l = 1.0f / nx_ml.y;
-      float dp[BW_SEL];
-#pragma unroll
-      for (int j = 0; j < BW_SEL; ++j) dp[j] = wgt * nx_dp[j];
-      load_row(u + 1 < u_end ? nxu : x, nx_ml, nx_dp);      // lands under this unit's dS pass; unconditional, see the serial kernel
-
-      long long c1 = clock64();
-      pf[5] += c1 - c_end;
-      ptx::mbar_wait(bar_sfull(it & 1), (it >> 1) & 1u);
-      ptx::tc_fence_after();
-      pf[0] += clock64() - c1;
-      c1 = clock64();
-      float delta = 0.0f;
-      {
-        uint32_t sv[BW_SEL];
-        ptx::tmem_ld16(tm_sel(it) + lane_off, sv);
-        ptx::tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < BW_SEL; ++j) {
-          const int t = tk[j];
-          const float ps = (t >= 0 && t < P.T) ? ptx::ex2(__uint_as_float(sv[j]) - m) * inv_l : 0.0f;
-          delta = fmaf(ps, dp[j], delta);
-          dp[j] *= ps;                          // dp[j] now holds P_sel[j] * dP[j]
-        }
-      }
-      // the dS buffer of this unit was last read by the dz product of unit it-2
-      pf[1] += clock64() - c1;
-      c1 = clock64();
-      if (it >= 2) ptx::mbar_wait(bar_dzdone(it & 1), ((it >> 1) & 1u) ^ 1u);
-      pf[2] += clock64() - c1;
-      c1 = clock64();
-      // ---- dS = P * (dP - delta): dense part -P*delta for my 64 columns, then the n_idx corrections
-      const float nd = -delta * inv_l;
-      uint8_t* ds_ptr = base_ptr + SM::kDsOff + (it & 1) * SM::kDsBytes;
-      {
-        uint32_t v[2][32];
-        const bool full = ncol == 64;
-        ptx::tmem_ld32(tm_S(it) + lane_off + col0, v[0]);
-        ptx::tmem_ld32(tm_S(it) + lane_off + col0 + 32, v[1]);
-        ptx::tmem_ld_wait();
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          uint32_t pk[16];
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            float e0 = ptx::ex2(__uint_as_float(v[c][2 * j]) - m) * nd;
-            float e1 = ptx::ex2(__uint_as_float(v[c][2 * j + 1]) - m) * nd;
-            if (!full) {
-              e0 = (32 * c + 2 * j < ncol) ? e0 : 0.0f;
-              e1 = (32 * c + 2 * j + 1 < ncol) ? e1 : 0.0f;
-            }
-            const __nv_bfloat162 h2 = __floats2bfloat162_rn(e0, e1);
-            pk[j] = *reinterpret_cast<const uint32_t*>(&h2);
-          }
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const int cc = 32 * c + 8 * q;         // column inside my 64-token slab
-            const uint32_t off = ch * 16384 + row * 128 + (((cc >> 3) ^ (row & 7)) << 4);
-            *reinterpret_cast<uint4*>(ds_ptr + off) = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
-          }
-        }
-      }
-#pragma unroll
-      for (int j = 0; j < BW_SEL; ++j) {
-        const int t = tk[j] - tok0;
-        if (j < P.n_idx && t >= col0 && t < col0 + ncol) {
-          const uint32_t off = (t >> 6) * 16384 + row * 128 + ((((t & 63) >> 3) ^ (row & 7)) << 4) + (t & 7) * 2;
-          __nv_bfloat16* e = reinterpret_cast<__nv_bfloat16*>(ds_ptr + off);
-          *e = __float2bfloat16_rn(__bfloat162float(*e) + dp[j]);
-        }
-      }
-      ptx::fence_proxy_async();
-      ptx::tc_fence_before();
-      ptx::mbar_arrive(bar_dsfull(it & 1));
-      pf[3] += clock64() - c1;
-      c1 = clock64();
-      // ---- dz: flush the window accumulator (token rows x 64 taps) when the next tile leaves this window
-      if (u + 1 >= u_end || new_window(x, nxu)) {
-        ptx::mbar_wait(bar_dzdone(it & 1), (it >> 1) & 1u);
-        ptx::tc_fence_after();
-        if (ch == 0) {
-          const int t = tok0 + row;
-          const int h = P.ops.heads[x.l];
-          const int r0 = x.r0;
-          const int nvalid = min(TC_BK, s * s - r0 * s);      // taps of the window inside the source image
-          float* dz = P.dz[x.l] + ((static_cast<int64_t>(x.b) * h + x.head) * P.T + t) * (s * s) + r0 * s;
-#pragma unroll
-          for (int c = 0; c < 2; ++c) {
-            uint32_t v[32];
-            ptx::tmem_ld32(tm_dz + lane_off + c * 32, v);
-            ptx::tmem_ld_wait();
-            if (t < P.T) {
-#pragma unroll
-              for (int q = 0; q < 8; ++q)
-                if (c * 32 + q * 4 < nvalid)
-                  red_add_v4(dz + c * 32 + q * 4, __uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]),
-                             __uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3]));
-            }
-          }
-        }
-        ptx::tc_fence_before();
-        // the next dz product (fresh accumulator) is only issued after every softmax thread has arrived on ds_full of
-        // the next unit, i.e. after these loads
-      }
-      pf[4] += clock64() - c1;
-      c_end = clock64();
-    }
-    if (P.prof && blockIdx.x == ((P.dbg >> 6) & 1) && stid == 0) {
-      // printed by the host under the 256-token kernel's labels: s_full wait, [dS] = S_sel part, [fence+arrive] = wait for
-      // dz(it-2), [wait mma_done] = dense dS + arrive, [drain+adjoint] = window test + flush
+    if (P.prof && blockIdx.x == ((BW_DBG(P) >> 6) & 1) && stid == 0) {
       for (int i = 0; i < 5; ++i) P.prof[2 + i] = pf[i];
       P.prof[7] = it;
       P.prof[10] = pf[5];
@@ -1240,9 +905,6 @@ static int bwd_launch_group(const skp_attn_layer* sub, const int* ghead, int n_s
     P.dq[l] = a.dq; P.dk[l] = a.dk; P.s[l] = a.s; P.C[l] = a.C; P.ghead[l] = ghead[l];
     if (lr) {
       const LrGeom geo = lr_geometry(a.s, R);
-      rc = tc_encode_map(&P.s128_map[l][0], P.ops.s_ptr[l][0], a.s * a.s, T, B * a.heads, 128);
-      if (rc == SKP_OK) rc = tc_encode_map(&P.s128_map[l][1], P.ops.s_ptr[l][1], a.s * a.s, T, B * a.heads, 128);
-      if (rc != SKP_OK) return rc;
       P.wr0[l] = reinterpret_cast<unsigned char*>(ws);
       bw_window_table_kernel<<<(::skp::note_launch(), 1), 256, 0, st>>>(a.s, R, geo.nr, tiles, reinterpret_cast<unsigned char*>(ws));
       SKP_LAUNCH_CHECK();
@@ -1259,6 +921,7 @@ static int bwd_launch_group(const skp_attn_layer* sub, const int* ghead, int n_s
   P.B = B; P.T = T; P.R = R; P.R2 = R * R; P.n_idx = n_idx; P.tiles = tiles;
   P.idx_stride = idx_stride; P.token_idx = token_idx; P.dmaps_sel = dmaps_sel; P.dpT = dpT; P.row_stats = row_stats;
   P.n_units = P.ops.total_heads * B * P.tiles;
+#ifdef SKP_DIAG
   if (const char* e = getenv("SKP_BWD_DBG")) P.dbg = atoi(e);
   static unsigned long long* d_prof = nullptr;
   if (P.dbg & 8) {
@@ -1266,21 +929,11 @@ static int bwd_launch_group(const skp_attn_layer* sub, const int* ghead, int n_s
     cudaMemsetAsync(d_prof, 0, 128, st);
     P.prof = d_prof;
   }
+#endif
   const int nh = T > TC_BN ? 2 : 1;
-  P.n_chunks = kNumSMs / nh < P.n_units ? kNumSMs / nh : P.n_units;
-  // SKP_BWD_LR128=1: the pipelined 128-token kernel.  Parity-tested, but measured SLOWER on B200 (7.65 vs 6.01 ms per
-  // 8-image call): the per-unit fixed cost of the softmax warps (statistics / gradient prefetch, S_sel, corrections,
-  // fences: ~3.5 k cycles) does not shrink with the token tile, so twice as many half-size units cost more than the
-  // overlap of S / dz with dS wins.  Kept for the next round (the fixed cost is the thing to cut), off by default.
-  const char* e128 = getenv("SKP_BWD_LR128");
-  if (lr && e128 && atoi(e128) == 1) {
-    const int nq = (T + 127) / 128;
-    P.n_chunks = kNumSMs / nq < P.n_units ? kNumSMs / nq : P.n_units;
-    SKP_CUDA(cudaFuncSetAttribute(attn_map_bwd_lr128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Bw128Smem::kDynamic));
-    attn_map_bwd_lr128_kernel<<<(::skp::note_launch(), P.n_chunks * nq), BW_THREADS, Bw128Smem::kDynamic, st>>>(P);
-    SKP_LAUNCH_CHECK();
-    rc = SKP_OK;
-  } else if (lr) {
+  const int sms = num_sms();      // persistent grid: one CTA per SM of the CURRENT device
+  P.n_chunks = sms / nh < P.n_units ? sms / nh : P.n_units;
+  if (lr) {
     if (x3) rc = nh == 2 ? launch_bwd<3, 2, true>(P, st) : launch_bwd<3, 1, true>(P, st);
     else rc = nh == 2 ? launch_bwd<1, 2, true>(P, st) : launch_bwd<1, 1, true>(P, st);
   } else {
@@ -1288,6 +941,7 @@ static int bwd_launch_group(const skp_attn_layer* sub, const int* ghead, int n_s
     else rc = nh == 2 ? launch_bwd<1, 2, false>(P, st) : launch_bwd<1, 1, false>(P, st);
   }
   if (rc != SKP_OK) return rc;
+#ifdef SKP_DIAG
   if (P.dbg & 8) {
     unsigned long long h[16];
     cudaStreamSynchronize(st);
@@ -1297,6 +951,7 @@ static int bwd_launch_group(const skp_attn_layer* sub, const int* ghead, int n_s
             "wait s_full %.0f, dS %.0f, fence+arrive %.0f, wait mma_done %.0f, drain+adjoint %.0f\n", lr ? " LR" : "", h[7], h[0] / n, h[8] / n, h[1] / n, h[9] / n,
             h[10] / n, h[2] / n, h[3] / n, h[4] / n, h[5] / n, h[6] / n);
   }
+#endif
   if (lr)
     for (int l = 0; l < n_sub; ++l) {
       rc = lr_bwd_post(sub[l], B, T, P.dz[l], post_ws[l], st);

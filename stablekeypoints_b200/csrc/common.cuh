@@ -39,7 +39,8 @@ int note_launch();
 
 inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
-constexpr int kNumSMs = 148;   // B200
+// SM count of the CURRENT device (queried once per device ordinal; 148 on B200): sizes persistent / machine-filling grids
+int num_sms();
 
 // ---- warp / block reductions ------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {

@@ -660,7 +660,7 @@ extern "C" int skp_plane_argmax(const float* maps, int N, int H, int W, int64_t*
   SKP_CUDA(cudaMemsetAsync(flat_idx, 0, sizeof(int64_t) * N, st));
   // enough CTAs to fill the machine even for a handful of large planes; chunk starts stay 16B aligned
   int chunks = static_cast<int>((plane + 16383) / 16384);
-  int want = (4 * kNumSMs + N - 1) / N;
+  int want = (4 * num_sms() + N - 1) / N;
   chunks = chunks < want ? chunks : want;
   chunks = chunks < 1 ? 1 : chunks;
   while (chunks > 1 && ((plane + chunks - 1) / chunks) % 4 != 0) --chunks;
