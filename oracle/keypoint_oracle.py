@@ -438,3 +438,48 @@ def attention_maps_at_pixels(q_lows: Sequence[Tensor], ks: Sequence[Tensor], hea
         if return_lse2:
             lse.append(torch.logsumexp(sim, dim=-1) * 1.4426950408889634)
     return (out, torch.cat(lse, dim=0)) if return_lse2 else out
+
+
+# ======================================================================================
+# rows 16 / f2: regressor application and the five dataset metrics of `evaluate` (eval.py:468-510)
+# ======================================================================================
+H36M_SWAPS = ((1, 6), (2, 7), (3, 8), (4, 9), (5, 10), (17, 25), (18, 26), (19, 27), (20, 28), (21, 28), (22, 30), (23, 31))
+
+
+def swap_points_h36m(points: Tensor) -> Tensor:
+    """`swap_points`, `eval.py:360-371`: left/right relabelling of Human3.6M keypoints, points (B, N, D).  The table —
+    including its (21, 28) entry, which overwrites the (20, 28) one — is the reference's."""
+    perm = list(range(points.shape[1]))
+    for a, b in H36M_SWAPS:
+        perm[a] = b
+        perm[b] = a
+    return points[:, perm, :]
+
+
+def evaluate_image(keypoints: Tensor, regressor: Tensor, gt_kpts: Tensor, evaluation_method: str = "inter_eye_distance",
+                   visible: Optional[Tensor] = None) -> Tensor:
+    """The per-image tail of `evaluate`, `eval.py:468-510`, restated line by line on CPU tensors.
+
+    keypoints (K, 2) in [0, 1] = readout / 512 (`:463-466`); regressor (2K, 2n); gt_kpts (n, 2) in [0, 1].
+    `:469`: estimated = ((keypoints.view(1,-1) - 0.5) @ regressor) + 0.5 -> (n, 2); `:475-477`: both scaled by 256 for
+    `mean_average_error` / `pck`; `:480`: per-keypoint L2; then per method (`:482-509`)."""
+    est = ((keypoints.reshape(1, -1) - 0.5) @ regressor + 0.5).reshape(-1, 2)
+    gt = gt_kpts.clone()
+    if evaluation_method in ("mean_average_error", "pck"):
+        est = est * 256
+        gt = gt * 256
+    l2 = (est - gt).norm(dim=-1)
+    if evaluation_method == "inter_eye_distance":
+        eye = torch.sqrt(torch.sum((gt[0] - gt[1]) ** 2, dim=-1))
+        return torch.mean(l2 / eye)
+    if evaluation_method in ("visible", "mean_average_error"):
+        vis = torch.ones_like(l2) if visible is None else visible.to(l2.dtype)
+        tot = (l2 * vis).sum()
+        return tot / vis.sum() if evaluation_method == "visible" else tot
+    if evaluation_method == "pck":
+        return (l2 < 6).to(torch.float32).mean()
+    if evaluation_method == "orientation_invariant":
+        m = l2.mean()
+        sw = (swap_points_h36m(est[None])[0] - gt).norm(dim=-1).mean()
+        return (sw if sw < m else m) * 128
+    raise NotImplementedError(evaluation_method)

@@ -90,6 +90,34 @@ def test_keypoint_error_known_answers():
 
 # ------------------------------------------------------------------ live reference (build container only)
 @pytest.mark.reference
+@pytest.mark.parametrize("method,n", [("inter_eye_distance", 5), ("visible", 7), ("mean_average_error", 7), ("pck", 9),
+                                      ("orientation_invariant", 32)])
+def test_keypoint_error_matches_oracle_restatement_of_evaluate(method, n):
+    """`eval.keypoint_error` + the regressor application of `evaluate` against the oracle's line-by-line restatement of
+    `eval.py:468-510`, random keypoints / regressors / visibility, all five metrics (32 keypoints: Human3.6M swap table)."""
+    from oracle import keypoint_oracle as O
+    g = torch.Generator().manual_seed(n)
+    for trial in range(6):
+        K = 10
+        kp = torch.rand(K, 2, generator=g)
+        W = torch.randn(2 * K, 2 * n, generator=g) * 0.2
+        gt = torch.rand(n, 2, generator=g)
+        vis = (torch.rand(n, generator=g) > 0.3).float() if method in ("visible", "mean_average_error") and trial % 2 else None
+        if vis is not None and vis.sum() == 0:
+            vis[0] = 1.0
+        want = O.evaluate_image(kp, W, gt, method, vis)
+        est = (((kp.reshape(1, -1) - 0.5) @ W) + 0.5).reshape(-1, 2)          # eval.evaluate's regressor application
+        got = keypoint_error(est, gt, method, vis)
+        assert torch.allclose(got, want, rtol=1e-6, atol=1e-7), (method, trial, float(got), float(want))
+
+
+def test_oracle_swap_table_matches_reference(ref):
+    from oracle import keypoint_oracle as O
+    pts = torch.arange(32 * 2, dtype=torch.float32).reshape(1, 32, 2)
+    assert torch.equal(O.swap_points_h36m(pts), ref.eval.swap_points(pts))
+    assert torch.equal(swap_points(pts), ref.eval.swap_points(pts))
+
+
 def test_regressors_match_reference(ref):
     X, Y, _ = _problem(seed=5)
     assert np.allclose(KR.return_regressor(X, Y), ref.keypoint_regressor.return_regressor(X, Y), atol=1e-10)
