@@ -64,6 +64,29 @@ s_, n_ = torch.zeros(10, 512, 512, device=dev), torch.zeros(10, 512, 512, device
 # read-modify-write (the unfused reference order would be 4 passes of 10.5 MB per augmentation: 2.7 GB)
 report("tta_accumulate (64 aug x 10 x 128^2 -> 10 x 512^2, fused)", timed(lambda: ops.tta_accumulate(fm, th, s_, n_)),
        64 * 10 * 128 * 128 * 4 + 4 * 10 * 512 * 512 * 4)
+rows[-1]["samples_per_s"] = 64 * 10 * 512 * 512 / (rows[-1]["ms"] * 1e-3)
+rows[-1]["note"] = ("gather-bound, not bandwidth-bound: every output pixel does 64 x (inverse warp + 4-tap un-warp, each tap a 4-tap bilinear "
+                    "read of an L2-resident 128^2 plane) = 16 reads per (augmentation, plane, pixel); report samples/s, not bytes")
+print(f"   = {rows[-1]['samples_per_s'] / 1e9:.2f} G (augmentation, plane, pixel) samples/s")
+# losses of the token optimisation, batched over the images of a step (one launch each way): 64 images x 10 selected planes of
+# the image and of its transformed copy (2 x 10 x 128^2 x 4 B read; backward reads the same and writes both gradients)
+sel = torch.rand(2 * 256, 10, 128, 128, device=dev, generator=g).requires_grad_(True)
+thl = torch.eye(2, 3, device=dev)[None].repeat(256, 1, 1)
+thl[:, 0, 2] = 0.03
+nbl = sel.numel() * 4
+report("keypoint_losses_batched fwd (256 x 2 x 10 x 128^2)", timed(lambda: ops.keypoint_losses_batched(sel.detach(), thl, 2.0)), nbl)
+out = ops.keypoint_losses_batched(sel, thl, 2.0)
+gsum = torch.ones_like(out)
+def _bwd():
+    sel.grad = None
+    out.backward(gsum, retain_graph=True)
+report("keypoint_losses_batched bwd (read planes, write both gradients)", timed(_bwd), 2 * nbl)
+del sel, out
+img = torch.rand(64, 3, 512, 512, device=dev, generator=g)
+tha = torch.eye(2, 3, device=dev)[None].repeat(64, 1, 1)
+tha[:, 0, 1] = 0.1
+report("affine_warp (64 x 3 x 512^2, read + write)", timed(lambda: ops.affine_warp(img, tha)), 2 * img.numel() * 4)
+del img
 # single-image latencies
 one = maps[:500].contiguous()
 for name, fn in [("plane_stats KL, one image (500 x 128^2)", lambda: ops.plane_stats(one, sigma=2.0, want_kl=True)),

@@ -329,7 +329,7 @@ plane_stats_reg_kernel(const float* __restrict__ maps, int W, float sigma, float
       ev[j] = e[j] * v[j];
     }
     s0f += (e[0] + e[1]) + (e[2] + e[3]);
-    s1f += (ev[0] + ev[1]) + (ev[2] + ev[3]);
+    if (ent_out) s1f += (ev[0] + ev[1]) + (ev[2] + ev[3]);     // sum e^v v feeds the entropy only (uniform branch)
     if (KL) svf += (v[0] + v[1]) + (v[2] + v[3]);
   }
   double s0 = static_cast<double>(s0f), s1 = static_cast<double>(s1f), sv = static_cast<double>(svf);
@@ -344,8 +344,11 @@ plane_stats_reg_kernel(const float* __restrict__ maps, int W, float sigma, float
     const int rlo = max(0, r_c - rad), rhi = min(H - 1, r_c + rad), clo = max(0, c_c - rad), chi = min(W - 1, c_c + rad);
     const int bw = chi - clo + 1, bn = (rhi - rlo + 1) * bw;
     const float* pl = maps + static_cast<int64_t>(blockIdx.x) * n;
+    const float inv_bw = 1.0f / static_cast<float>(bw);
     for (int i = threadIdx.x; i < bn; i += PS_THREADS) {
-      const int r = rlo + i / bw, c = clo + i % bw;
+      // i / bw without the ~40-instruction integer division: exact for i < 2^20, bw < 2^10 (error of the product << 0.5 / bw)
+      const int q = __float2int_rd((static_cast<float>(i) + 0.5f) * inv_bw);
+      const int r = rlo + q, c = clo + (i - q * bw);
       const float v = __ldg(pl + (r << lgw) + c) - mx;
       const float dr = (static_cast<float>(r) + 0.5f) - cr, dc = (static_cast<float>(c) + 0.5f) - cc;
       const float a = expf(-(dc * dc + dr * dr) * inv2s2) + eps;       // g * (1 / num_subjects) with one subject

@@ -41,18 +41,42 @@ __global__ void __launch_bounds__(256) bilinear_upsample_vec4_kernel(const float
     float lx[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) bilinear_coeffs(4 * x4 + j, rx, w, &x0[j], &x1[j], &lx[j]);
-    for (int yy = threadIdx.x / w4; yy < rows; yy += ystep) {
+    // ... and walks CONSECUTIVE output rows, keeping the x-interpolated values of the two source rows it last touched:
+    // at x2 / x4 upsampling a source row serves 2-4 output rows twice (as upper and as lower tap), so the 16 gathers per
+    // 16-byte store drop to ~4 (the kernel was LSU-bound at 55 % of the copy bandwidth, not store-bound)
+    const int per = (rows + ystep - 1) / ystep;
+    const int yb = (threadIdx.x / w4) * per, ye = min(rows, yb + per);
+    int cy0 = -1, cy1 = -1;
+    float a0[4], a1[4];
+    auto xrow = [&](int yy_src, float (&a)[4]) {
+      const float* r = p + yy_src * w;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) a[j] = (1.0f - lx[j]) * __ldg(r + x0[j]) + lx[j] * __ldg(r + x1[j]);
+    };
+    for (int yy = yb; yy < ye; ++yy) {
       int y0, y1;
       float ly;
       bilinear_coeffs(ybase + yy, ry, h, &y0, &y1, &ly);
-      const float* r0 = p + y0 * w;
-      const float* r1 = p + y1 * w;
-      float v[4];
+      if (y0 != cy0) {
+        if (y0 == cy1) {
 #pragma unroll
-      for (int j = 0; j < 4; ++j)
-        v[j] = (1.0f - ly) * ((1.0f - lx[j]) * __ldg(r0 + x0[j]) + lx[j] * __ldg(r0 + x1[j])) +
-               ly * ((1.0f - lx[j]) * __ldg(r1 + x0[j]) + lx[j] * __ldg(r1 + x1[j]));
-      o[yy * w4 + x4] = make_float4(v[0], v[1], v[2], v[3]);
+          for (int j = 0; j < 4; ++j) a0[j] = a1[j];
+        } else {
+          xrow(y0, a0);
+        }
+        cy0 = y0;
+      }
+      if (y1 != cy1) {
+        if (y1 == cy0) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) a1[j] = a0[j];
+        } else {
+          xrow(y1, a1);
+        }
+        cy1 = y1;
+      }
+      o[yy * w4 + x4] = make_float4((1.0f - ly) * a0[0] + ly * a1[0], (1.0f - ly) * a0[1] + ly * a1[1],
+                                    (1.0f - ly) * a0[2] + ly * a1[2], (1.0f - ly) * a0[3] + ly * a1[3]);
     }
     return;
   }
