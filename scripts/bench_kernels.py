@@ -8,7 +8,11 @@ from stablekeypoints_b200 import ops, _lib
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 8
 prec = sys.argv[2] if len(sys.argv) > 2 else "auto"
 dev = "cuda:0"
-spec = [(16, 1280, 20), (16, 1280, 20), (16, 1280, 20), (32, 640, 10)]
+SPECS = {"sd21": [(16, 1280, 20), (16, 1280, 20), (16, 1280, 20), (32, 640, 10)],          # BASELINE capture set
+         "sd15": [(16, 1280, 8), (16, 1280, 8), (16, 1280, 8), (32, 640, 8)],              # what the reference loads: d = 160 / 80
+         "sdxl": [(32, 1280, 20)] * 4,                                                     # configs[4]
+         "cub9": [(16, 1280, 20)] * 3 + [(32, 640, 10)] * 3 + [(64, 320, 5)] * 3}          # configs[3]
+spec = SPECS[os.environ.get("BK_MODEL", "sd21")]
 g = torch.Generator().manual_seed(0)
 qs = [(torch.randn(B, s * s, C, generator=g) * 1.5).to(dev).requires_grad_(True) for s, C, h in spec]
 T = int(os.environ.get("BK_T", "500"))
@@ -32,7 +36,7 @@ _lib.timing_start()
 for _ in range(10):
     run()
 t = _lib.timing_summary()
-flops = 2 * 128 * 128 * T * (3 * 1280 + 640) * B
+flops = 2 * 128 * 128 * T * sum(C for _, C, _ in spec) * B
 for k, v in t.items():
     ms = v["ms"] / v["calls"]
     mult = 1 if "fwd" in k else 2

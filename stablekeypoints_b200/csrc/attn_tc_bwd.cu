@@ -97,16 +97,29 @@ __global__ void bw_gather_ssel_kernel(const __nv_bfloat16* __restrict__ s_hi, co
   }
 }
 
-template <int NPROD>
+// WIDE (LR only): 128-tap interpolation windows (32^2 sources at R = 128) as TWO 64-tap k-blocks.  The logit gradient of a
+// window then needs 128 TMEM columns per 128 tokens, which only fits next to S when the CTA owns 128 tokens (S 128 + dz
+// 128 + S_sel 32 columns) instead of 256: four token quarters per tile, ONE operand stage (64 KB: both k-blocks, hi + lo),
+// strictly serial S -> dS -> dz per unit.  Slower per exponential than the staged dQ'/dK kernel, but it does not see
+// dim_head at all: it is the tensor-core path of wide-window layers with dim_head > 64 (SD-1.5: 80 at 32^2).
+template <int NPROD, bool WIDE = false>
 struct BwSmem {
-  static constexpr int kQStage = (NPROD == 3 ? 2 : 1) * TC_A_BYTES;
-  static constexpr int kQOff = 0;                                   // 2 stages
-  static constexpr int kKOff = kQOff + 2 * kQStage;                 // k hi (+ lo)
-  static constexpr int kKBytes = (NPROD == 3 ? 2 : 1) * TC_B_BYTES;
+  static constexpr int kNkb = WIDE ? 2 : 1;                         // 64-wide k-blocks of the S product
+  static constexpr int kBn = WIDE ? 128 : TC_BN;                    // tokens per CTA
+  static constexpr int kQStages = WIDE ? 1 : 2;
+  static constexpr int kAHalf = kNkb * TC_A_BYTES;                  // [hi k-block 0 (, 1)] then the same for lo
+  static constexpr int kQStage = (NPROD == 3 ? 2 : 1) * kAHalf;
+  static constexpr int kQOff = 0;
+  static constexpr int kKBlock = kBn * TC_BK * 2;                   // one k-block of the k / logit-window tile
+  static constexpr int kKHalf = kNkb * kKBlock;
+  static constexpr int kKOff = kQOff + kQStages * kQStage;          // k hi (+ lo)
+  static constexpr int kKBytes = (NPROD == 3 ? 2 : 1) * kKHalf;
   static constexpr int kKselOff = kKOff + kKBytes;
-  static constexpr int kKselBytes = (NPROD == 3 ? 2 : 1) * BW_KSEL_BYTES;
+  static constexpr int kKselHalf = kNkb * BW_KSEL_BYTES;
+  static constexpr int kKselBytes = (NPROD == 3 ? 2 : 1) * kKselHalf;
   static constexpr int kDsOff = kKselOff + kKselBytes;              // dS tile; aliased by the fp32 dQ' staging
-  static constexpr int kWxtOff = kDsOff + BW_DS_BYTES;
+  static constexpr int kDsBytes = TC_BM * kBn * 2;
+  static constexpr int kWxtOff = kDsOff + (WIDE ? kDsBytes : BW_DS_BYTES);
   static constexpr int kBarOff = kWxtOff + BW_WXT_FLOATS * 4;       // q_full[2], q_empty[2], s_full, ds_full, mma_done, sel_full[2], s_free
   static constexpr int kTmemPtrOff = kBarOff + 8 * 10;
   static constexpr int kTokOff = kTmemPtrOff + 8;                   // int tok[16]
@@ -211,10 +224,14 @@ constexpr int BW_SOFTMAX_WARP0 = 4;
 // dz += dS^T W (tokens x 64 taps, K = 128 pixels; same operand forms as the dK product with the W tile of this pixel
 // tile in place of Q'), accumulated in TMEM over the tiles that share a window of source rows and flushed with vector
 // reductions into dz[b*h + head][token][window]; attn_tc_bwd_lr.cu turns dz into dq / dk at native resolution.
-template <int NPROD, int NH, bool LR>
+template <int NPROD, int NH, bool LR, bool WIDE = false>
 __global__ void __launch_bounds__(BW_THREADS, 1)
 attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
-  using SM = BwSmem<NPROD>;
+  using SM = BwSmem<NPROD, WIDE>;
+  static_assert(!WIDE || (LR && NPROD == 3), "wide windows exist on the upsample-after-logits path only");
+  constexpr int NKB = SM::kNkb, BNT = SM::kBn, NST = SM::kQStages;
+  constexpr int CPT = BNT / 2;            // logit columns per softmax thread (row, column half): 128, WIDE: 64
+  constexpr int NCHUNK = CPT / 32;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = ptx::smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
@@ -224,8 +241,8 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
   const int half = blockIdx.x % NH, chunk = blockIdx.x / NH;
   const int u_begin = static_cast<int>(static_cast<int64_t>(chunk) * P.n_units / P.n_chunks);
   const int u_end = static_cast<int>(static_cast<int64_t>(chunk + 1) * P.n_units / P.n_chunks);
-  const int tok0 = half * TC_BN;
-  const int ntok = max(0, min(TC_BN, P.T - tok0));          // tokens this CTA owns
+  const int tok0 = half * BNT;
+  const int ntok = max(0, min(BNT, P.T - tok0));            // tokens this CTA owns
   const int n_mh = ntok > 128 ? 2 : 1;
 
   auto bar_qfull = [&](int s) { return base + SM::kBarOff + 8u * s; };
@@ -277,29 +294,40 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       BwUnit x = bw_decode(P, u_begin);
       for (int u = u_begin; u < u_end; ++u, ++it, x = bw_next(P, x)) {
         const int h = P.ops.heads[x.l];
-        const int st = it & 1;
-        ptx::mbar_wait_hint(bar_qempty(st), ((it >> 1) & 1u) ^ 1u, 2000u);
+        const int st = it % NST;
+        ptx::mbar_wait_hint(bar_qempty(st), ((it / NST) & 1u) ^ 1u, 2000u);
         const int r0 = LR ? x.r0 : 0;
         const bool need_k = LR ? (x.hg != prev_hg || x.b != prev_b || r0 != prev_r0)
                                : (x.hg != prev_hg || (!P.ops.k_shared[x.l] && x.b != prev_b));
         const bool need_ksel = need_k || x.b != prev_b;
-        if (need_ksel && it > 0) ptx::mbar_wait_hint(bar_qempty((it - 1) & 1), ((it - 1) >> 1) & 1u, 2000u);   // previous unit done with k / k_sel
+        if (need_ksel && it > 0) ptx::mbar_wait_hint(bar_qempty((it - 1) % NST), ((it - 1) / NST) & 1u, 2000u);   // previous unit done with k / k_sel
         const uint32_t bytes = SM::kQStage + (need_k ? SM::kKBytes : 0) + (need_ksel ? SM::kKselBytes : 0);
         ptx::mbar_arrive_expect_tx(bar_qfull(st), bytes);
         const int qz = x.b * h + x.head;
         const uint32_t qs = base + SM::kQOff + st * SM::kQStage;
         const int a_row = LR ? 0 : x.tile * TC_BM, a_z = LR ? x.tile : qz;     // (k, row, batch) of the A tile
         const int b_k0 = LR ? r0 * P.s[x.l] : 0;                              // first tap of the window in the s*s row
-        ptx::tma_load_3d(qs, &P.ops.q_map[x.l][0], bar_qfull(st), 0, a_row, a_z);
-        if (NPROD == 3) ptx::tma_load_3d(qs + TC_A_BYTES, &P.ops.q_map[x.l][1], bar_qfull(st), 0, a_row, a_z);
+#pragma unroll
+        for (int kb = 0; kb < NKB; ++kb) {
+          ptx::tma_load_3d(qs + kb * TC_A_BYTES, &P.ops.q_map[x.l][0], bar_qfull(st), kb * TC_BK, a_row, a_z);
+          if (NPROD == 3) ptx::tma_load_3d(qs + SM::kAHalf + kb * TC_A_BYTES, &P.ops.q_map[x.l][1], bar_qfull(st), kb * TC_BK, a_row, a_z);
+        }
         if (need_k) {
           const int kz = LR ? qz : (P.ops.k_shared[x.l] ? 0 : x.b * h) + x.head;
-          ptx::tma_load_3d(base + SM::kKOff, &P.ops.k_map[x.l][0], bar_qfull(st), b_k0, tok0, kz);
-          if (NPROD == 3) ptx::tma_load_3d(base + SM::kKOff + TC_B_BYTES, &P.ops.k_map[x.l][1], bar_qfull(st), b_k0, tok0, kz);
+#pragma unroll
+          for (int kb = 0; kb < NKB; ++kb) {
+            ptx::tma_load_3d(base + SM::kKOff + kb * SM::kKBlock, &P.ops.k_map[x.l][0], bar_qfull(st), b_k0 + kb * TC_BK, tok0, kz);
+            if (NPROD == 3)
+              ptx::tma_load_3d(base + SM::kKOff + SM::kKHalf + kb * SM::kKBlock, &P.ops.k_map[x.l][1], bar_qfull(st), b_k0 + kb * TC_BK, tok0, kz);
+          }
         }
         if (need_ksel) {
-          ptx::tma_load_3d(base + SM::kKselOff, &P.ksel_map[x.l][0], bar_qfull(st), b_k0, 0, qz);
-          if (NPROD == 3) ptx::tma_load_3d(base + SM::kKselOff + BW_KSEL_BYTES, &P.ksel_map[x.l][1], bar_qfull(st), b_k0, 0, qz);
+#pragma unroll
+          for (int kb = 0; kb < NKB; ++kb) {
+            ptx::tma_load_3d(base + SM::kKselOff + kb * BW_KSEL_BYTES, &P.ksel_map[x.l][0], bar_qfull(st), b_k0 + kb * TC_BK, 0, qz);
+            if (NPROD == 3)
+              ptx::tma_load_3d(base + SM::kKselOff + SM::kKselHalf + kb * BW_KSEL_BYTES, &P.ksel_map[x.l][1], bar_qfull(st), b_k0 + kb * TC_BK, 0, qz);
+          }
         }
         prev_hg = x.hg;
         prev_b = x.b;
@@ -317,24 +345,26 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       // ---- S = Q' K^T (256 tokens) and S_sel = Q' K_sel^T (16 tokens) of the unit in stage (jt & 1)
       // mode 0: both, S_sel interleaved into the first half of S; 1: S_sel only; 2: S only
       auto issue_S = [&](int l, uint32_t jt, int mode) {
-        const uint32_t qs = base + SM::kQOff + (jt & 1) * SM::kQStage;
+        const uint32_t qs = base + SM::kQOff + (jt % NST) * SM::kQStage;
         const uint32_t tsel = tm_sel(jt), selbar = bar_selfull(jt);
         long long c0 = BW_CLK();
-        ptx::mbar_wait_hint(bar_qfull(jt & 1), (jt >> 1) & 1u, 2000u);
+        ptx::mbar_wait_hint(bar_qfull(jt % NST), (jt / NST) & 1u, 2000u);
         ptx::tc_fence_after();
         pf_q += BW_CLK() - c0;
         c0 = BW_CLK();
-        const uint32_t id_S = bw_idesc(TC_BM, TC_BN, 0, 0), id_sel = bw_idesc(TC_BM, BW_SEL, 0, 0);
+        const uint32_t id_S = bw_idesc(TC_BM, BNT, 0, 0), id_sel = bw_idesc(TC_BM, BW_SEL, 0, 0);
+        // byte offset of 16-wide k-step kk inside an operand whose 64-wide k-blocks are `blk` bytes apart
+        auto ko = [](int kk, uint32_t blk) { return static_cast<uint32_t>(kk >> 2) * blk + static_cast<uint32_t>(kk & 3) * 32u; };
         // LR: the K dimension is the 64-tap window (the launcher only sends such layers here): fixed trip count, the
         // descriptors of the unrolled loops are the stage's base descriptors plus constants
-        const int nk16 = LR ? TC_BK / 16 : P.ops.d[l] / 16;
+        const int nk16 = LR ? NKB * (TC_BK / 16) : P.ops.d[l] / 16;
         if (mode == 1) {
 #pragma unroll
           for (int kk = 0; kk < nk16; ++kk) {
-            const uint64_t a_hi = bw_desc(qs + kk * 32, 16, 1024), s_hi = bw_desc(ksel + kk * 32, 16, 1024);
+            const uint64_t a_hi = bw_desc(qs + ko(kk, TC_A_BYTES), 16, 1024), s_hi = bw_desc(ksel + ko(kk, BW_KSEL_BYTES), 16, 1024);
             if (NPROD == 3) {
-              const uint64_t a_lo = bw_desc(qs + TC_A_BYTES + kk * 32, 16, 1024);
-              const uint64_t s_lo = bw_desc(ksel + BW_KSEL_BYTES + kk * 32, 16, 1024);
+              const uint64_t a_lo = bw_desc(qs + SM::kAHalf + ko(kk, TC_A_BYTES), 16, 1024);
+              const uint64_t s_lo = bw_desc(ksel + SM::kKselHalf + ko(kk, BW_KSEL_BYTES), 16, 1024);
               ptx::umma_bf16(tsel, a_hi, s_lo, id_sel, kk != 0);
               ptx::umma_bf16(tsel, a_lo, s_hi, id_sel, 1u);
               ptx::umma_bf16(tsel, a_hi, s_hi, id_sel, 1u);
@@ -349,10 +379,10 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         if (mode == 2) {
 #pragma unroll
           for (int kk = 0; kk < nk16; ++kk) {
-            const uint64_t a_hi = bw_desc(qs + kk * 32, 16, 1024), b_hi = bw_desc(ks + kk * 32, 16, 1024);
+            const uint64_t a_hi = bw_desc(qs + ko(kk, TC_A_BYTES), 16, 1024), b_hi = bw_desc(ks + ko(kk, SM::kKBlock), 16, 1024);
             if (NPROD == 3) {
-              const uint64_t a_lo = bw_desc(qs + TC_A_BYTES + kk * 32, 16, 1024);
-              const uint64_t b_lo = bw_desc(ks + TC_B_BYTES + kk * 32, 16, 1024);
+              const uint64_t a_lo = bw_desc(qs + SM::kAHalf + ko(kk, TC_A_BYTES), 16, 1024);
+              const uint64_t b_lo = bw_desc(ks + SM::kKHalf + ko(kk, SM::kKBlock), 16, 1024);
               ptx::umma_bf16(tm_S, a_hi, b_lo, id_S, kk != 0);
               ptx::umma_bf16(tm_S, a_lo, b_hi, id_S, 1u);
               ptx::umma_bf16(tm_S, a_hi, b_hi, id_S, 1u);
@@ -376,11 +406,11 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
           const uint64_t p_hi = bw_desc(qs + k0 * 32, 16, 1024), r_hi = bw_desc(qs + k1 * 32, 16, 1024);
           const uint64_t s0_hi = bw_desc(ksel + k0 * 32, 16, 1024), s1_hi = bw_desc(ksel + k1 * 32, 16, 1024);
           if (NPROD == 3) {
-            const uint64_t a_lo = bw_desc(qs + TC_A_BYTES + kk * 32, 16, 1024);
-            const uint64_t b_lo = bw_desc(ks + TC_B_BYTES + kk * 32, 16, 1024);
-            const uint64_t p_lo = bw_desc(qs + TC_A_BYTES + k0 * 32, 16, 1024), r_lo = bw_desc(qs + TC_A_BYTES + k1 * 32, 16, 1024);
-            const uint64_t s0_lo = bw_desc(ksel + BW_KSEL_BYTES + k0 * 32, 16, 1024);
-            const uint64_t s1_lo = bw_desc(ksel + BW_KSEL_BYTES + k1 * 32, 16, 1024);
+            const uint64_t a_lo = bw_desc(qs + SM::kAHalf + kk * 32, 16, 1024);
+            const uint64_t b_lo = bw_desc(ks + SM::kKHalf + kk * 32, 16, 1024);
+            const uint64_t p_lo = bw_desc(qs + SM::kAHalf + k0 * 32, 16, 1024), r_lo = bw_desc(qs + SM::kAHalf + k1 * 32, 16, 1024);
+            const uint64_t s0_lo = bw_desc(ksel + SM::kKselHalf + k0 * 32, 16, 1024);
+            const uint64_t s1_lo = bw_desc(ksel + SM::kKselHalf + k1 * 32, 16, 1024);
             ptx::umma_bf16(tm_S, a_hi, b_lo, id_S, kk != 0);
             if (sel0) {
               ptx::umma_bf16(tsel, p_hi, s0_lo, id_sel, kk != 0);
@@ -408,13 +438,22 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       for (int u = u_begin; u < u_end; ++u, ++it) {
         const BwUnit nxu = bw_next(P, x);
         const int d = P.ops.d[x.l];
-        const int st = it & 1;
+        const int st = it % NST;
         const uint32_t qs = base + SM::kQOff + st * SM::kQStage;
-        if (!s_issued) issue_S(x.l, it, 0);
+        if (!s_issued) {
+          if (WIDE) {                 // two k-blocks: S_sel first (its barrier frees the softmax warps' delta), then S
+            issue_S(x.l, it, 1);
+            issue_S(x.l, it, 2);
+          } else {
+            issue_S(x.l, it, 0);
+          }
+        }
         s_issued = false;
         // LR, next tile in the same window (no k / k_sel reload, whose TMA would wait for this unit's MMAs): its S_sel only
         // needs the next W tile, so it runs on the idle tensor pipe while the softmax warps are in this unit's dS pass
-        const bool early = LR && u + 1 < u_end && nxu.hg == x.hg && nxu.b == x.b && nxu.r0 == x.r0 && !(BW_DBG(P) & 32);
+        // (WIDE: one operand stage -- the next unit's interpolation table can only be loaded once this unit's dz product
+        // has read the current one, so nothing of the next unit is issued ahead)
+        const bool early = LR && !WIDE && u + 1 < u_end && nxu.hg == x.hg && nxu.b == x.b && nxu.r0 == x.r0 && !(BW_DBG(P) & 32);
         const bool sel_early = early && !(BW_DBG(P) & 128);
         if (sel_early) issue_S(nxu.l, it + 1, 1);
         // ... and its S as soon as every softmax thread holds the last chunk of S(u) in registers (s_free), one chunk of
@@ -457,7 +496,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         } else {
           // dz (128 tok x 64 taps per half) += dS^T (MN-major A: rows = pixels) * W_hi (MN-major B: rows = pixels; the
           // A stage of this unit's S product)
-          const uint32_t id_dz = bw_idesc(128, TC_BK, 1, 1);
+          const uint32_t id_dz = bw_idesc(128, WIDE ? 128 : TC_BK, 1, 1);    // WIDE: both 64-tap blocks of W_hi, 16 KB apart (LBO)
           for (int mh = 0; mh < n_mh; ++mh)
             for (int k = 0; k < TC_BM / 16; ++k)
               ptx::umma_bf16(tm_dK + mh * 64, bw_desc(dsb + mh * 2 * 16384 + k * 2048, 16384, 1024),
@@ -481,8 +520,8 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
     const int ch = (warp - BW_SOFTMAX_WARP0) >> 2;   // column half of the CTA's 256 tokens
     const int row = quad * 32 + lane;
     const int stid = threadIdx.x - BW_SOFTMAX_WARP0 * 32;   // 0..255
-    const int col0 = ch * 128;
-    const int ncol = max(0, min(128, ntok - col0));
+    const int col0 = ch * CPT;
+    const int ncol = max(0, min(CPT, ntok - col0));
     const uint32_t lane_off = static_cast<uint32_t>(quad * 32) << 16;
     const uint32_t dsb = base + SM::kDsOff;
     uint8_t* ds_ptr = base_ptr + SM::kDsOff;
@@ -583,8 +622,8 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         uint32_t v[2][32];
         // LR: the first HOLD chunks of dS stay packed in registers until the previous unit's dz product has retired
         // (it still reads the single dS tile): the exponentials of those chunks run under that product
-        constexpr int HOLD = LR ? BW_LR_HOLD : 1;
-        uint32_t pk[4][16];
+        constexpr int HOLD = LR ? (BW_LR_HOLD < NCHUNK ? BW_LR_HOLD : NCHUNK) : 1;
+        uint32_t pk[NCHUNK][16];
         auto store_chunk = [&](int c) {
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
@@ -595,10 +634,10 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         };
         ptx::tmem_ld32(tm_S + lane_off + col0, v[0]);
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < NCHUNK; ++c) {
           ptx::tmem_ld_wait();
-          if (c < 3) ptx::tmem_ld32(tm_S + lane_off + col0 + 32 * (c + 1), v[(c + 1) & 1]);
-          if (LR && c == 3) {
+          if (c < NCHUNK - 1) ptx::tmem_ld32(tm_S + lane_off + col0 + 32 * (c + 1), v[(c + 1) & 1]);
+          if (LR && c == NCHUNK - 1) {
             // S(u) is in registers: the tensor pipe may overwrite the accumulator with S(u+1)
             ptx::tc_fence_before();
             ptx::mbar_arrive(bar_sfree);
@@ -759,12 +798,14 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       c_end = BW_CLK();
       if (LR) {
         // ---- dz: flush the window accumulator (token rows x 64 taps) when the next tile leaves this window
-        if (lr_flush && ch < n_mh) {
-          const int t = tok0 + ch * 128 + row;
+        // thread (row, ch): token row of the accumulator's lane; 64 of its tap columns (WIDE: tap half ch of the one
+        // 128-token accumulator; else all 64 taps of token half ch)
+        if (lr_flush && (WIDE || ch < n_mh)) {
+          const int t = tok0 + (WIDE ? 0 : ch * 128) + row;
           const int h = P.ops.heads[x.l];
           const int r0 = x.r0;
-          const int nvalid = min(TC_BK, s * s - r0 * s);      // taps of the window inside the source image
-          float* dz = P.dz[x.l] + ((static_cast<int64_t>(x.b) * h + x.head) * P.T + t) * (s * s) + r0 * s;
+          const int nvalid = min(WIDE ? 128 : TC_BK, s * s - r0 * s) - (WIDE ? ch * 64 : 0);      // taps of the window inside the source image
+          float* dz = P.dz[x.l] + ((static_cast<int64_t>(x.b) * h + x.head) * P.T + t) * (s * s) + r0 * s + (WIDE ? ch * 64 : 0);
 #pragma unroll
           for (int c = 0; c < 2; ++c) {
             uint32_t v[32];
@@ -829,24 +870,36 @@ size_t lr_bwd_post_workspace(const skp_attn_layer& a, int B, int T);
 int lr_bwd_post(const skp_attn_layer& a, int B, int T, const float* dz, char* ws, cudaStream_t st);
 int lr_launch_weights(int s, int R, const LrGeom& g, __nv_bfloat16* hi, __nv_bfloat16* lo, cudaStream_t st);
 
+// Which main kernel a layer's gradient takes.  The "upsample after the logits" kernels do not see dim_head (their K
+// dimension is the interpolation window; only the native-resolution GEMMs before and after see it):
+//   BWD_LR64   windows of <= 64 taps (16^2 sources at R = 128): 256 tokens per CTA, the fast path
+//   BWD_LR128  windows of <= 128 taps (32^2 sources at R = 128): 128 tokens per CTA (BwSmem WIDE), slower per exponential
+//              than the staged kernel -- taken when the staged kernel cannot run (dim_head > 64: SD-1.5's 80 at 32^2) or
+//              when SKP_BWD_LR=2 asks for it (tests, A/B)
+//   BWD_STAGED staged q' with dQ'/dK products + bicubic adjoint: dim_head <= 64 (64-column TMEM accumulators)
+//   BWD_NONE   none of them (e.g. 64^2 sources with dim_head > 64): the call falls back to the CUDA-core kernel
+// SKP_BWD_LR=0 sends every layer down the staged path (A/B measurements); read per call: the tests switch it.
+enum { BWD_NONE = 0, BWD_STAGED = 1, BWD_LR64 = 2, BWD_LR128 = 3 };
+static int bwd_layer_kind(const skp_attn_layer& a, int R) {
+  const char* e = getenv("SKP_BWD_LR");
+  const int mode = e ? atoi(e) : 1;
+  const int d = a.C / a.heads;
+  const bool staged_ok = d <= 64 && d % 16 == 0;
+  const bool lr_shape = (a.s * a.s) % 8 == 0 && a.s != R && R % TC_BM == 0;
+  const int kw = lr_shape ? lr_geometry(a.s, R).kw : 0;
+  if (mode != 0 && kw == TC_BK) return BWD_LR64;
+  if (mode != 0 && kw == 2 * TC_BK && (!staged_ok || mode == 2)) return BWD_LR128;
+  return staged_ok ? BWD_STAGED : BWD_NONE;
+}
+static bool bwd_layer_lr(const skp_attn_layer& a, int R) { return bwd_layer_kind(a, R) >= BWD_LR64; }
+
 bool attn_map_bwd_tc_supported(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int n_idx) {
   if (!attn_map_tc_supported(h_layers, n_layers, B, T, R, n_idx)) return false;
   if (n_idx < 1 || n_idx > BW_SEL || R > 256) return false;
   if (!((R <= TC_BM && TC_BM % R == 0) || (R % TC_BM == 0))) return false;
-  for (int l = 0; l < n_layers; ++l) {
-    const int d = h_layers[l].C / h_layers[l].heads;
-    if (d > 64 || d % 16 != 0) return false;     // dQ' / dK accumulators are 64 TMEM columns each
-  }
+  for (int l = 0; l < n_layers; ++l)
+    if (bwd_layer_kind(h_layers[l], R) == BWD_NONE) return false;
   return true;
-}
-
-// Layers whose tiles interpolate from at most 64 source pixels (16^2 sources at R = 128) take the "upsample after the
-// logits" gradient; wider windows (32^2: 128 taps need 256 TMEM columns next to the 256 of S) keep the staged path.
-// SKP_BWD_LR=0 sends every layer down the staged path (A/B measurements).
-static bool bwd_layer_lr(const skp_attn_layer& a, int R) {
-  const char* e = getenv("SKP_BWD_LR");          // read per call: the tests switch it to cover both paths
-  const bool enabled = !(e && atoi(e) == 0);
-  return enabled && (a.s * a.s) % 8 == 0 && a.s != R && lr_geometry(a.s, R).kw == TC_BK;
 }
 
 size_t attn_map_bwd_tc_workspace(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int precision) {
@@ -863,10 +916,10 @@ size_t attn_map_bwd_tc_workspace(const skp_attn_layer* h_layers, int n_layers, i
   return total + 1024;
 }
 
-template <int NPROD, int NH, bool LR>
+template <int NPROD, int NH, bool LR, bool WIDE = false>
 static int launch_bwd(const BwdParams& P, cudaStream_t st) {
-  using SM = BwSmem<NPROD>;
-  auto kern = attn_map_bwd_tc_kernel<NPROD, NH, LR>;
+  using SM = BwSmem<NPROD, WIDE>;
+  auto kern = attn_map_bwd_tc_kernel<NPROD, NH, LR, WIDE>;
   SKP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::kDynamic));
   kern<<<(::skp::note_launch(), P.n_chunks * NH), BW_THREADS, SM::kDynamic, st>>>(P);
   SKP_LAUNCH_CHECK();
@@ -874,14 +927,16 @@ static int launch_bwd(const BwdParams& P, cudaStream_t st) {
 }
 
 // one launch of the main kernel over a subset of the captured layers (`sub`, with their global head offsets)
-static int bwd_launch_group(const skp_attn_layer* sub, const int* ghead, int n_sub, int heads_all, bool lr, int B, int T, int R,
+static int bwd_launch_group(const skp_attn_layer* sub, const int* ghead, int n_sub, int heads_all, int kind, int B, int T, int R,
                             const int64_t* token_idx, int n_idx, int64_t idx_stride, const float* dmaps_sel, const float* dpT,
                             const float* row_stats, bool x3, char** ws_io, cudaStream_t st) {
   BwdParams P;
   memset(&P, 0, sizeof(P));
   char* ws = nullptr;
+  const bool lr = kind >= BWD_LR64, wide = kind == BWD_LR128;
   SKP_REQUIRE(!lr || x3, "skp_attn_map_bwd: the upsample-after-logits path is bf16x3 only");
-  int rc = lr ? tc_prepare_lr(sub, n_sub, B, T, R, *ws_io, st, &P.ops, &ws) : tc_prepare(sub, n_sub, B, T, R, x3, *ws_io, st, &P.ops, &ws);
+  int rc = lr ? tc_prepare_lr(sub, n_sub, B, T, R, *ws_io, st, &P.ops, &ws, wide ? 128 : TC_BN)
+              : tc_prepare(sub, n_sub, B, T, R, x3, *ws_io, st, &P.ops, &ws);
   if (rc != SKP_OK) return rc;
   const int tiles = R * R / TC_BM;
   char* post_ws[TC_MAX_LAYERS];
@@ -930,10 +985,13 @@ static int bwd_launch_group(const skp_attn_layer* sub, const int* ghead, int n_s
     P.prof = d_prof;
   }
 #endif
-  const int nh = T > TC_BN ? 2 : 1;
+  const int nh = wide ? (T > 384 ? 4 : T > 256 ? 3 : T > 128 ? 2 : 1) : (T > TC_BN ? 2 : 1);    // token parts per tile
   const int sms = num_sms();      // persistent grid: one CTA per SM of the CURRENT device
   P.n_chunks = sms / nh < P.n_units ? sms / nh : P.n_units;
-  if (lr) {
+  if (wide) {
+    rc = nh == 4 ? launch_bwd<3, 4, true, true>(P, st) : nh == 3 ? launch_bwd<3, 3, true, true>(P, st)
+       : nh == 2 ? launch_bwd<3, 2, true, true>(P, st) : launch_bwd<3, 1, true, true>(P, st);
+  } else if (lr) {
     if (x3) rc = nh == 2 ? launch_bwd<3, 2, true>(P, st) : launch_bwd<3, 1, true>(P, st);
     else rc = nh == 2 ? launch_bwd<1, 2, true>(P, st) : launch_bwd<1, 1, true>(P, st);
   } else {
@@ -971,11 +1029,12 @@ int attn_map_bwd_tc(const skp_attn_layer* h_layers, int n_layers, int B, int T, 
     return SKP_ERR_WORKSPACE;
   }
   const bool x3 = precision != SKP_PREC_TC_BF16;
-  // two launches: layers with narrow interpolation windows (LR) and the rest (staged dQ' / dK + bicubic adjoint)
-  skp_attn_layer group[2][TC_MAX_LAYERS];
-  int ghead[2][TC_MAX_LAYERS], n_group[2] = {0, 0}, heads_all = 0;
+  // up to three launches: staged dQ' / dK + bicubic adjoint, upsample-after-logits with 64-tap and with 128-tap windows
+  skp_attn_layer group[4][TC_MAX_LAYERS];
+  int ghead[4][TC_MAX_LAYERS], n_group[4] = {0, 0, 0, 0}, heads_all = 0;
   for (int l = 0; l < n_layers; ++l) {
-    const int gi = bwd_layer_lr(h_layers[l], R) ? 1 : 0;
+    const int gi = bwd_layer_kind(h_layers[l], R);
+    SKP_REQUIRE(gi != BWD_NONE, "skp_attn_map_bwd: layer %d has no tensor-core backward", l);
     group[gi][n_group[gi]] = h_layers[l];
     ghead[gi][n_group[gi]++] = heads_all;
     heads_all += h_layers[l].heads;
@@ -985,9 +1044,9 @@ int attn_map_bwd_tc(const skp_attn_layer* h_layers, int n_layers, int B, int T, 
   ws += tc_align_up(static_cast<size_t>(B) * R * R * BW_SEL * 4, 1024);
   bw_transpose_dp_kernel<<<(::skp::note_launch(), dim3((R * R + 255) / 256, B)), 256, 0, st>>>(dmaps_sel, n_idx, R * R, dpT);
   SKP_LAUNCH_CHECK();
-  for (int gi = 0; gi < 2; ++gi) {
+  for (int gi = BWD_STAGED; gi <= BWD_LR128; ++gi) {
     if (n_group[gi] == 0) continue;
-    int rc = bwd_launch_group(group[gi], ghead[gi], n_group[gi], heads_all, gi == 1, B, T, R, token_idx, n_idx, idx_stride, dmaps_sel,
+    int rc = bwd_launch_group(group[gi], ghead[gi], n_group[gi], heads_all, gi, B, T, R, token_idx, n_idx, idx_stride, dmaps_sel,
                               dpT, row_stats, x3, &ws, st);
     if (rc != SKP_OK) return rc;
   }

@@ -86,6 +86,7 @@ __global__ void __launch_bounds__(LGG_THREADS) lr_grad_gemm_kernel(const __grid_
   uint8_t* base_ptr = smem_raw + (base - raw);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int mt = blockIdx.x, zg = blockIdx.y;           // zg = output batch * heads + head
+  const int n0 = blockIdx.z * LGG_BN;                   // first dim_head column of this CTA (dim_head > 64: several N chunks)
   const int zo = zg / P.heads, head = zg - zo * P.heads;
   auto bar_full = [&](int s) { return base + LGG_STAGES * LGG_STAGE + 8u * s; };
   auto bar_empty = [&](int s) { return base + LGG_STAGES * LGG_STAGE + 8u * (LGG_STAGES + s); };
@@ -124,7 +125,7 @@ __global__ void __launch_bounds__(LGG_THREADS) lr_grad_gemm_kernel(const __grid_
         ptx::mbar_arrive_expect_tx(bar_full(s), LGG_STAGE);
         const uint32_t st = base + s * LGG_STAGE;
         ptx::tma_load_3d(st, &P.a_map, bar_full(s), kb * TC_BK, mt * TC_BM, za);
-        ptx::tma_load_3d(st + LGG_A_BYTES, &P.b_map, bar_full(s), kb * TC_BK, 0, zb);
+        ptx::tma_load_3d(st + LGG_A_BYTES, &P.b_map, bar_full(s), kb * TC_BK, n0, zb);
       };
       const int ahead = total < LGG_STAGES ? total : LGG_STAGES;
       for (int it = 0; it < ahead; ++it) load(it);
@@ -149,17 +150,18 @@ __global__ void __launch_bounds__(LGG_THREADS) lr_grad_gemm_kernel(const __grid_
     const int quad = warp & 3;
     const int m = mt * TC_BM + quad * 32 + lane;
     const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
-    float* o = P.out + static_cast<int64_t>(zo) * P.out_z + static_cast<int64_t>(m) * P.ld + head * P.d;
+    float* o = P.out + static_cast<int64_t>(zo) * P.out_z + static_cast<int64_t>(m) * P.ld + head * P.d + n0;
+    const int dn = P.d - n0;                              // columns of this chunk that exist
 #pragma unroll 1
     for (int c = 0; c < LGG_BN / 32; ++c) {
-      if (c * 32 >= P.d) break;
+      if (c * 32 >= dn) break;
       uint32_t v[32];
       ptx::tmem_ld32(t_lane + c * 32, v);
       ptx::tmem_ld_wait();
       if (m < P.m_valid) {
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
-          if (c * 32 + q * 4 < P.d) {
+          if (c * 32 + q * 4 < dn) {
             float4* p4 = reinterpret_cast<float4*>(o + c * 32 + q * 4);
             float4 cur = *p4;
             cur.x = fmaf(P.alpha, __uint_as_float(v[4 * q]), cur.x);
@@ -220,7 +222,7 @@ int lr_bwd_post(const skp_attn_layer& a, int B, int T, const float* dz, char* ws
     if (rc != SKP_OK) return rc;
     G.out = a.dq; G.out_z = static_cast<int64_t>(s2) * a.C; G.ld = a.C; G.d = d; G.heads = a.heads; G.m_valid = s2; G.K = Tp;
     G.nsum = 1; G.a_zstride = 0; G.b_zstride = 0; G.b_shared = a.k_shared; G.alpha = a.scale;
-    lr_grad_gemm_kernel<<<(::skp::note_launch(), dim3((s2 + TC_BM - 1) / TC_BM, Z)), LGG_THREADS, LGG_DYNAMIC, st>>>(G);
+    lr_grad_gemm_kernel<<<(::skp::note_launch(), dim3((s2 + TC_BM - 1) / TC_BM, Z, (d + LGG_BN - 1) / LGG_BN)), LGG_THREADS, LGG_DYNAMIC, st>>>(G);
     SKP_LAUNCH_CHECK();
   }
   // dk[bk, t, head*d + c] += scale * sum_b sum_sp dzb[z][t][sp] * qT[z][c][sp]
@@ -232,7 +234,7 @@ int lr_bwd_post(const skp_attn_layer& a, int B, int T, const float* dz, char* ws
     if (rc != SKP_OK) return rc;
     G.out = a.dk; G.out_z = static_cast<int64_t>(T) * a.C; G.ld = a.C; G.d = d; G.heads = a.heads; G.m_valid = T; G.K = s2;
     G.nsum = a.k_shared ? B : 1; G.a_zstride = a.heads; G.b_zstride = a.heads; G.b_shared = 0; G.alpha = a.scale;
-    lr_grad_gemm_kernel<<<(::skp::note_launch(), dim3((T + TC_BM - 1) / TC_BM, Bk * a.heads)), LGG_THREADS, LGG_DYNAMIC, st>>>(G);
+    lr_grad_gemm_kernel<<<(::skp::note_launch(), dim3((T + TC_BM - 1) / TC_BM, Bk * a.heads, (d + LGG_BN - 1) / LGG_BN)), LGG_THREADS, LGG_DYNAMIC, st>>>(G);
     SKP_LAUNCH_CHECK();
   }
   return SKP_OK;

@@ -292,7 +292,7 @@ def test_resampling_matches_oracle(ops):
     assert torch.equal(ops.bilinear_upsample(_cu(y), 16).cpu(), y)
 
 
-@pytest.mark.parametrize("lr", ["0", "1"])
+@pytest.mark.parametrize("lr", ["0", "1", "2"])
 @pytest.mark.parametrize("spec,T,R,B,shared", [
     ([(4, 64, 4), (8, 32, 2)], 40, 16, 2, True),             # dim_head 16, several pixel rows per tile
     ([(8, 128, 2), (16, 64, 1)], 300, 32, 2, False),         # dim_head 64, two token halves, per-image k
@@ -303,7 +303,7 @@ def test_attention_maps_backward_tcgen05_matches_oracle_autograd(ops, monkeypatc
     dQ'/dK products and the bicubic adjoint (bf16 dS, k, q' operands): 1e-2 of the gradient's max; lr=1 "upsample after
     the logits" on the layers with 64-tap windows (the interpolation table is a bf16 operand too): 1.5e-2 of the max
     (measured 1.04e-2 worst case on these problems, 0.2-0.4e-2 on unit-variance inputs, scripts/bwd_err.py)."""
-    monkeypatch.setenv("SKP_BWD_LR", "0" if lr == "0" else "1")
+    monkeypatch.setenv("SKP_BWD_LR", lr)      # 2: 128-tap windows (the 32^2 layer at R = 128) through the 128-token wide-window kernel too
     tol = 1e-2 if lr == "0" else 1.5e-2
     qs, ks, heads, sc = _random_layers(spec, T, B, 5, shared)
     g = torch.Generator().manual_seed(9)
@@ -333,6 +333,44 @@ def test_attention_maps_backward_tcgen05_matches_oracle_autograd(ops, monkeypatc
     (sel2 * _cu(w)).sum().backward()
     for a, b_ in zip([t.grad for t in qc + kc], [t.grad for t in qd + kd]):
         assert (a - b_).abs().max().item() <= tol * float(b_.abs().max())
+
+
+def test_backward_sd15_head_shapes_on_tensor_cores(ops):
+    """SD-1.5 — the model the reference actually loads (`main.py:29`): 8 heads, dim_head 160 at 16^2 and 80 at 32^2.
+    dim_head > 64 used to send the whole call to the fp32 CUDA-core kernel (260 ms per 8-image call); the
+    upsample-after-logits kernels do not see dim_head, so the 16^2 layers take the 64-tap kernel and the 32^2 layer the
+    128-tap one.  Against fp64 autograd through the oracle on a pixel subset (the gradient is linear in the upstream
+    gradient), T = 300 (three token quarters, ragged), 1.5e-2 of each gradient's max; forward rtol 1e-3."""
+    from stablekeypoints_b200 import _lib
+    spec, T, R, B = [(16, 1280, 8), (32, 640, 8)], 300, 128, 2
+    qs, ks, heads, sc = _random_layers(spec, T, B, 41, True)
+    g = torch.Generator().manual_seed(8)
+    idx = torch.stack([torch.randperm(T, generator=g)[:10] for _ in range(B)])
+    pix = [torch.randperm(R * R, generator=g)[:48] for _ in range(B)]
+    w = torch.zeros(B, 10, R * R)
+    for b in range(B):
+        w[b][:, pix[b]] = torch.randn(10, 48, generator=g)
+    q64 = [q.double().requires_grad_(True) for q in qs]
+    k64 = [k.double().requires_grad_(True) for k in ks]
+    loss = 0.0
+    for b in range(B):
+        m = O.attention_maps_at_pixels([q[b] for q in q64], [k[0] for k in k64], heads, sc, R, pix[b])
+        loss = loss + (m[idx[b]] * w[b][:, pix[b]].double()).sum()
+    want = torch.autograd.grad(loss, q64 + k64)
+    qc = [_cu(q).requires_grad_(True) for q in qs]
+    kc = [_cu(k).requires_grad_(True) for k in ks]
+    with torch.no_grad():
+        full, stats = ops.attention_maps([q.detach() for q in qc], [k.detach() for k in kc], heads, sc, R, return_stats=True)
+    for b in range(B):
+        ref = O.attention_maps_at_pixels([q[b] for q in qs], [k[0] for k in ks], heads, sc, R, pix[b])
+        assert torch.allclose(full[b].reshape(T, -1)[:, pix[b]].cpu().double(), ref, rtol=1e-3, atol=1e-9)
+    before = _lib.load().skp_kernel_launches()
+    sel = ops.selected_planes(full, _cu(idx), qc, kc, heads, sc, R, row_stats=stats)
+    (sel * _cu(w.reshape(B, 10, R, R))).sum().backward()
+    for name, got, ref in zip(["dq16", "dq32", "dk16", "dk32"], [t.grad for t in qc + kc], want):
+        scale = float(ref.abs().max())
+        err = (got.cpu().double() - ref).abs().max().item()
+        assert torch.isfinite(got).all() and err <= 1.5e-2 * scale, f"{name}: {err / scale:.2e} of max"
 
 
 def test_backward_full_size_tcgen05_vs_cuda_core(ops):
