@@ -76,6 +76,8 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="all", choices=["all", "optimize", "extract", "cub9", "sdxl"])
+    ap.add_argument("--model", default="", help="stand-in architecture instead of the workload's (e.g. sd15: what the reference loads, "
+                                                 "8 heads of dim 160 / 80; BASELINE names sd21-base)")
     ap.add_argument("--images-per-pass", type=int, default=0, help="images per UNet pass on each GPU (0: the workload's default)")
     ap.add_argument("--precision", default="auto", choices=["auto", "tc_bf16x3", "tc_bf16", "simt_f32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -99,6 +101,8 @@ def workload_cfg(name: str, args) -> dict:
             cfg["max_query_tokens"] = 16 ** 2
     if args.images_per_pass:
         cfg["images_per_pass"] = args.images_per_pass
+    if args.model and not args.tiny:
+        cfg["model"] = args.model
     return cfg
 
 
