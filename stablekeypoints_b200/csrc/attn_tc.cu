@@ -263,11 +263,12 @@ constexpr int FW_SOFTMAX_WARP0 = 4;
 constexpr int FW_QCOLS = 64;                                  // tokens per softmax thread
 constexpr int FW_MAX_PARTS = 8;                               // 64-token column parts of a cluster (2 x 4 or 4 x 2)
 constexpr int FW_NH = 1;                                      // column groups a TMEM buffer is handed over in (1 or 2)
-// LR: when max |s_low| of a unit's (image, head) is below this, every logit of the unit lies in +-1.9 x 50 = +-95 (log2
-// units) and exp2 of the RAW logits can neither overflow (512 x 2^95 < 2^127) nor lose a row (2^-95 is a normal float):
-// the softmax is shift invariant, so the row-max pass (a TMEM round trip per chunk + 64 compares per thread + the exchange
-// of maxima) is skipped and the unit's statistics are (m = 0, l = sum exp2 S).  Larger logits take the max-subtracted path.
-constexpr float FW_FAST_ABSMAX = 50.0f;
+// LR: with [lo, hi] the range of the native-resolution logits of a unit's (image, head), every upsampled logit lies within
+// c +- 0.945 (hi - lo), c = (hi + lo) / 2.  When that half-width is <= FW_FAST_HALFWIDTH (log2 units), exp2(S - c) can
+// neither overflow (512 x 2^118 < 2^128) nor flush a single term (2^-118 is a normal float): the softmax is shift
+// invariant, so the row-max pass (a TMEM round trip per chunk + 64 compares per thread + the exchange of maxima) is skipped
+// and the unit's statistics are (m = round(c), l = sum exp2(S - m)).  Wider ranges take the max-subtracted path.
+constexpr float FW_FAST_HALFWIDTH = 117.0f;
 constexpr int FW_MAX_UNITS = 128;                             // units (heads of all captured layers) the flag table holds
 template <int BN>
 struct FwCfg {
@@ -328,13 +329,18 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
     ptx::fence_barrier_init();
   }
   if (LR && threadIdx.x < FW_MAX_UNITS) {
-    // unit u = global head index -> (layer, head); +inf (slow path) for units past the table or without a bound
+    // unit u = global head index -> (layer, head): the constant shift m of the bounded path, or +inf (max-subtracted
+    // path) for units past the table, without a recorded range, or whose range is too wide
     float v = INFINITY;
     const int u = threadIdx.x;
     if (u < P.ops.total_heads && P.ops.total_heads <= FW_MAX_UNITS) {
       int l = 0;
       while (l + 1 < P.ops.n_layers && u >= P.ops.head_base[l + 1]) ++l;
-      if (P.ops.absmax[l]) v = __int_as_float(P.ops.absmax[l][blockIdx.y * P.ops.heads[l] + (u - P.ops.head_base[l])]);
+      if (P.ops.absmax[l]) {
+        const int* key = P.ops.absmax[l] + 2 * (blockIdx.y * P.ops.heads[l] + (u - P.ops.head_base[l]));
+        const float hi = lr_range_value(key[0]), lo = -lr_range_value(key[1]);
+        if (hi >= lo && 0.945f * (hi - lo) + 1.0f <= FW_FAST_HALFWIDTH) v = rintf(0.5f * (hi + lo));   // integer-valued like the row maxima
+      }
     }
     amax_s[u] = v;
   }
@@ -520,9 +526,9 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
       const uint32_t taddr = t_lane + buf * TC_BNk + col0;
       ptx::mbar_wait_hint(bar_xfull(buf), par, 500u);
       FW_PROF(3)
-      float mg = 0.0f, total = 0.0f;
+      float mg = m_own, total = 0.0f;
       if (fast_uu) {
-        // every part posted (0, sum exp2 S): the row's statistics are the plain sum, four independent adds deep
+        // every part posted (the unit's constant m, sum exp2(S - m)): the row's statistics are the plain sum
         float tq[NPART];
 #pragma unroll
         for (int q = 0; q < NPART; ++q) tq[q] = stats[(buf * FW_MAX_PARTS + q) * TC_BM + row].y;
@@ -590,8 +596,10 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
         ptx::tc_fence_after();
         FW_PROF(0)
         const uint32_t taddr = t_lane + buf * TC_BNk + col0;
-        // bounded logits (see FW_FAST_ABSMAX): no row-max pass, m = 0.  Uniform over the cluster: one flag per (image, head)
-        const bool fast = LR && amax_s[u < FW_MAX_UNITS ? u : 0] <= FW_FAST_ABSMAX && u < FW_MAX_UNITS;
+        // bounded logits (see FW_FAST_HALFWIDTH): no row-max pass, m = the unit's constant.  Uniform over the cluster: one
+        // value per (image, head)
+        const float m_unit = LR && u < FW_MAX_UNITS ? amax_s[u] : INFINITY;
+        const bool fast = LR && m_unit < INFINITY;
         // ---- pass A: row max over my columns (four independent chains)
         float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
 #pragma unroll
@@ -618,7 +626,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
         }
         // Rounded up to an integer: any m >= the true max stabilises the exponentials equally well, and
         // integer-valued maxima make every rescale 2^(m_part - m_row) an exponent-field add, not a MUFU.
-        const float m = fast ? 0.0f : ceilf(fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)));
+        const float m = fast ? m_unit : ceilf(fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)));
         FW_PROF(2)
         // ---- pass C of the previous unit
         if (u > 0) pass_c(u - 1, m_prev, wgt_prev, fast_prev);

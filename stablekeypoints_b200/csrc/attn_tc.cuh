@@ -3,6 +3,7 @@
 
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cstring>
 
 #include "common.cuh"
 #include "ptx_sm100.cuh"
@@ -35,11 +36,24 @@ struct TcOperands {
   // lr_window_row0(tile) * s + 64 kb
   int lr, R;
   int win_s[TC_MAX_LAYERS], win_nr[TC_MAX_LAYERS];
-  // lr: bit pattern of max |s_low| over all tokens and source pixels of every (image, head): [layer][b * heads + head].
-  // Bounds the logits of that (image, head) at every feature pixel (|S| <= 1.9 max |s_low|: bicubic weights, A = -0.75,
-  // sum |w| <= 1.375 per axis), which lets the forward skip the row-max pass when exp2 cannot over/underflow.
+  // lr: order-preserving integer keys of (max s_low, max -s_low) over all tokens and source pixels of every (image, head):
+  // [layer][(b * heads + head) * 2 + {0, 1}] (lr_range_key / lr_range_value).  The range bounds the logits of that (image,
+  // head) at every feature pixel -- bicubic weights (A = -0.75) sum to 1 with at most 0.445 of negative mass over both axes,
+  // so S lies within [min - 0.445 range, max + 0.445 range] -- which lets the forward skip the row-max pass when exp2 of
+  // the logits shifted by the range's centre cannot over/underflow.
   const int* absmax[TC_MAX_LAYERS];
 };
+
+// float <-> int key whose signed-integer order is the float order (atomicMax on floats of either sign)
+__device__ __host__ __forceinline__ int lr_range_key(float v) {
+#ifdef __CUDA_ARCH__
+  const int b = __float_as_int(v);
+#else
+  int b; memcpy(&b, &v, 4);
+#endif
+  return b >= 0 ? b : b ^ 0x7fffffff;
+}
+__device__ __forceinline__ float lr_range_value(int key) { return __int_as_float(key >= 0 ? key : key ^ 0x7fffffff); }
 
 // window of source rows [r0, r0 + nr) a 128-pixel tile of the R x R output interpolates from (s x s source)
 struct LrGeom {

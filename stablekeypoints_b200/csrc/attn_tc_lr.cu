@@ -37,7 +37,7 @@ struct LrGemmParams {
   CUtensorMap q_map[2];   // (d, s*s, B*h), box (64, 256, 1)
   __nv_bfloat16* out_hi;  // [B*h][T][s*s]
   __nv_bfloat16* out_lo;
-  int* absmax;            // [B*h]: bit pattern of max |s_low| of the (image, head) (atomicMax on non-negative floats)
+  int* absmax;            // [B*h][2]: lr_range_key of (max s_low, max -s_low) of the (image, head), via atomicMax
   int T, s2, d, heads, k_shared;
 };
 
@@ -78,7 +78,7 @@ size_t attn_map_lr_workspace(const skp_attn_layer* h_layers, int n_layers, int B
     total += 2 * tc_align_up(static_cast<size_t>(a.k_shared ? 1 : B) * T * a.C * 2, 1024);     // k hi, lo
     total += 2 * tc_align_up(static_cast<size_t>(B) * a.heads * T * s2 * 2, 1024);             // s_low hi, lo
     total += 2 * tc_align_up(tiles * TC_BM * lr_geometry(a.s, R).kw * 2, 1024);                // W hi, lo
-    total += tc_align_up(static_cast<size_t>(B) * a.heads * sizeof(int), 1024);                // max |s_low| per (image, head)
+    total += tc_align_up(static_cast<size_t>(B) * a.heads * 2 * sizeof(int), 1024);            // range of s_low per (image, head)
   }
   return total + 1024;
 }
@@ -222,7 +222,8 @@ __global__ void __launch_bounds__(LRG_THREADS) lr_logits_kernel(const __grid_con
     uint8_t* stg_hi = base_ptr + (warp - 2) * (2 * LRG_STG_BYTES);
     uint8_t* stg_lo = stg_hi + LRG_STG_BYTES;
     const int t0 = tt * LRG_BM + quad * 32;
-    float amax = 0.0f;          // rows / columns past T / s*s hold zeros (TMA zero fill): they cannot raise the maximum
+    // rows / columns past T / s*s hold zeros (TMA zero fill): they can only widen the range towards 0, which stays valid
+    float vmax = -INFINITY, vmin = INFINITY;
 #pragma unroll 1
     for (int half = 0; half < 2; ++half) {
       const int col0 = st * LRG_BN + half * 128;
@@ -238,7 +239,8 @@ __global__ void __launch_bounds__(LRG_THREADS) lr_logits_kernel(const __grid_con
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const float f0 = __uint_as_float(v[8 * q + 2 * j]), f1 = __uint_as_float(v[8 * q + 2 * j + 1]);
-            amax = fmaxf(amax, fmaxf(fabsf(f0), fabsf(f1)));
+            vmax = fmaxf(vmax, fmaxf(f0, f1));
+            vmin = fminf(vmin, fminf(f0, f1));
             const __nv_bfloat16 h0 = __float2bfloat16_rn(f0), h1 = __float2bfloat16_rn(f1);
             const __nv_bfloat162 hh = __halves2bfloat162(h0, h1);
             const __nv_bfloat162 ll = __halves2bfloat162(__float2bfloat16_rn(f0 - __bfloat162float(h0)),
@@ -264,8 +266,12 @@ __global__ void __launch_bounds__(LRG_THREADS) lr_logits_kernel(const __grid_con
       }
       __syncwarp();
     }
-    amax = warp_max(amax);
-    if (lane == 0 && P.absmax) atomicMax(P.absmax + z, __float_as_int(amax));   // non-negative floats order like their bit patterns
+    vmax = warp_max(vmax);
+    vmin = -warp_max(-vmin);
+    if (lane == 0 && P.absmax && vmax >= vmin) {
+      atomicMax(P.absmax + 2 * z, lr_range_key(vmax));
+      atomicMax(P.absmax + 2 * z + 1, lr_range_key(-vmin));
+    }
   }
   __syncwarp();
   ptx::tc_fence_before();
@@ -299,8 +305,8 @@ int tc_prepare_lr(const skp_attn_layer* h_layers, int n_layers, int B, int T, in
     const size_t sb = static_cast<size_t>(B) * a.heads * T * s2 * 2, wb = static_cast<size_t>(tiles) * TC_BM * g.kw * 2;
     __nv_bfloat16 *q_hi = take(qb), *q_lo = take(qb), *k_hi = take(kb), *k_lo = take(kb), *s_hi = take(sb), *s_lo = take(sb);
     __nv_bfloat16 *w_hi = take(wb), *w_lo = take(wb);   // reserved even when an earlier layer's table is reused
-    int* absmax = reinterpret_cast<int*>(take(static_cast<size_t>(B) * a.heads * sizeof(int)));
-    SKP_CUDA(cudaMemsetAsync(absmax, 0, static_cast<size_t>(B) * a.heads * sizeof(int), st));
+    int* absmax = reinterpret_cast<int*>(take(static_cast<size_t>(B) * a.heads * 2 * sizeof(int)));
+    SKP_CUDA(cudaMemsetAsync(absmax, 0x80, static_cast<size_t>(B) * a.heads * 2 * sizeof(int), st));   // keys of ~ -3e38: below every logit
     const float mult = a.scale * 1.4426950408889634f;
     lr_split_heads_kernel<<<(::skp::note_launch(), dim3(s2, B)), 256, 0, st>>>(a.q, s2, a.C, a.heads, mult, q_hi, q_lo);
     lr_split_heads_kernel<<<(::skp::note_launch(), dim3(T, Bk)), 256, 0, st>>>(a.k, T, a.C, a.heads, 1.0f, k_hi, k_lo);
