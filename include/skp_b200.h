@@ -124,6 +124,16 @@ int skp_attn_map_bwd(const skp_attn_layer* h_layers, int n_layers, int B, int T,
                      const int64_t* token_idx, int n_idx, int64_t idx_stride, const float* dmaps_sel,
                      const float* row_stats, int precision, void* workspace, size_t workspace_bytes, void* stream);
 
+/* skp_attn_map_bwd that does not recompute what the forward already staged (ABI 107).  fwd_workspace / fwd_workspace_bytes:
+ * the workspace skp_attn_map_fwd was given for the SAME layers, q, k, B, T, R and precision (all tokens or selected ones),
+ * still intact.  Layers on the upsample-after-logits path then read their native-resolution logits and interpolation tables
+ * from it instead of running the two head splits, the logit GEMM and the table kernel again; other layers, or a forward
+ * that staged upsampled q' instead, are unaffected (the pointer is ignored).  NULL == skp_attn_map_bwd. */
+int skp_attn_map_bwd_reuse(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R,
+                           const int64_t* token_idx, int n_idx, int64_t idx_stride, const float* dmaps_sel,
+                           const float* row_stats, int precision, void* workspace, size_t workspace_bytes,
+                           const void* fwd_workspace, size_t fwd_workspace_bytes, void* stream);
+
 /* ---------------------------------------------------------------------------------------
  * Resampling (SURVEY.md Appendix A semantics == torch.nn.functional, align_corners=False)
  * ------------------------------------------------------------------------------------- */

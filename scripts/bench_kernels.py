@@ -25,8 +25,10 @@ w = torch.randn(B, 10, 128, 128, generator=g).to(dev)
 
 def run():
     with torch.no_grad():
-        full, stats = ops.attention_maps([q.detach() for q in qs], [k.detach() for k in ks], heads, sc, 128, precision=prec, return_stats=True)
-    sel = ops.selected_planes(full, idx, qs, ks, heads, sc, 128, precision=prec, row_stats=stats)
+        full, stats, ws = ops.attention_maps([q.detach() for q in qs], [k.detach() for k in ks], heads, sc, 128, precision=prec,
+                                             return_stats=True, return_workspace=True)
+    sel = ops.selected_planes(full, idx, qs, ks, heads, sc, 128, precision=prec, row_stats=stats,
+                              fwd_workspace=None if os.environ.get("BK_NO_REUSE") else ws)
     (sel * w).sum().backward()
 
 

@@ -36,6 +36,7 @@ SIGNATURES = {
     "skp_attn_map_workspace_bytes_for": (_Z, [C.POINTER(AttnLayer), _I, _I, _I, _I, _I, _I]),
     "skp_attn_map_fwd": (_I, [C.POINTER(AttnLayer), _I, _I, _I, _I, _P, _I, _L, _P, _P, _I, _P, _Z, _P]),
     "skp_attn_map_fwd_static": (_I, [C.POINTER(AttnLayer), _I, _I, _I, _I, _P, _I, _L, _P, _P, _I, _P]),
+    "skp_attn_map_bwd_reuse": (_I, [C.POINTER(AttnLayer), _I, _I, _I, _I, _P, _I, _L, _P, _P, _I, _P, _Z, _P, _Z, _P]),
     "skp_attn_map_bwd": (_I, [C.POINTER(AttnLayer), _I, _I, _I, _I, _P, _I, _L, _P, _P, _I, _P, _Z, _P]),
     "skp_bilinear_upsample": (_I, [_P, _I, _I, _I, _P, _I, _I, _P]),
     "skp_bicubic_upsample_nhwc": (_I, [_P, _I, _I, _I, _P, _I, _P]),

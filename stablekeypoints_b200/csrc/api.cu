@@ -29,7 +29,7 @@ int note_launch() {
 }
 }  // namespace skp
 
-extern "C" int skp_version(void) { return 106; }
+extern "C" int skp_version(void) { return 107; }
 extern "C" long long skp_kernel_launches(void) { return skp::g_launches.load(std::memory_order_relaxed); }
 extern "C" const char* skp_last_error(void) { return skp::g_err; }
 extern "C" int skp_device_arch(int device) {

@@ -14,7 +14,7 @@ int attn_map_fwd_tc(const skp_attn_layer*, int, int, int, int, const int64_t*, i
 bool attn_map_bwd_tc_supported(const skp_attn_layer*, int, int, int, int, int n_idx);
 size_t attn_map_bwd_tc_workspace(const skp_attn_layer*, int, int, int, int, int precision);
 int attn_map_bwd_tc(const skp_attn_layer*, int, int, int, int, const int64_t*, int, int64_t, const float*, const float*, int precision,
-                    void*, size_t, cudaStream_t);
+                    void*, size_t, cudaStream_t, const void* fwd_workspace, size_t fwd_workspace_bytes);
 }  // namespace skp
 
 using namespace skp;
@@ -69,12 +69,20 @@ extern "C" int skp_attn_map_fwd(const skp_attn_layer* h_layers, int n_layers, in
   return SKP_ERR_INVALID;
 }
 
-extern "C" int skp_attn_map_bwd(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, const int64_t* token_idx,
-                                int n_idx, int64_t idx_stride, const float* dmaps_sel, const float* row_stats, int precision,
-                                void* workspace, size_t workspace_bytes, void* stream) {
+extern "C" int skp_attn_map_bwd_reuse(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, const int64_t* token_idx,
+                                      int n_idx, int64_t idx_stride, const float* dmaps_sel, const float* row_stats, int precision,
+                                      void* workspace, size_t workspace_bytes, const void* fwd_workspace,
+                                      size_t fwd_workspace_bytes, void* stream) {
   int p = resolve_precision(h_layers, n_layers, B, T, R, n_idx, precision);
   if (p != SKP_PREC_SIMT_F32 && row_stats && attn_map_bwd_tc_supported(h_layers, n_layers, B, T, R, n_idx))
     return attn_map_bwd_tc(h_layers, n_layers, B, T, R, token_idx, n_idx, idx_stride, dmaps_sel, row_stats, p, workspace,
-                           workspace_bytes, as_stream(stream));
+                           workspace_bytes, as_stream(stream), fwd_workspace, fwd_workspace_bytes);
   return attn_map_bwd_simt(h_layers, n_layers, B, T, R, token_idx, n_idx, idx_stride, dmaps_sel, workspace, workspace_bytes, as_stream(stream));
+}
+
+extern "C" int skp_attn_map_bwd(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, const int64_t* token_idx,
+                                int n_idx, int64_t idx_stride, const float* dmaps_sel, const float* row_stats, int precision,
+                                void* workspace, size_t workspace_bytes, void* stream) {
+  return skp_attn_map_bwd_reuse(h_layers, n_layers, B, T, R, token_idx, n_idx, idx_stride, dmaps_sel, row_stats, precision, workspace,
+                                workspace_bytes, nullptr, 0, stream);
 }

@@ -795,6 +795,11 @@ static bool fwd_uses_lr(const skp_attn_layer* h_layers, int n_layers, int B, int
   return precision != SKP_PREC_TC_BF16 && !(e && atoi(e) == 0) && attn_map_lr_supported(h_layers, n_layers, B, T, R, n_idx);
 }
 
+// does skp_attn_map_fwd (all tokens, this precision) stage upsample-after-logits operands?  The backward may then reuse them
+bool attn_map_fwd_stages_lr(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int precision) {
+  return fwd_uses_lr(h_layers, n_layers, B, T, R, 0, precision);
+}
+
 // what the forward call will need: 0.45 GB for 8 SD-2.1 images on the upsample-after-logits path, 2.35 GB staged
 size_t attn_map_tc_workspace(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int precision) {
   if (fwd_uses_lr(h_layers, n_layers, B, T, R, 0, precision)) return attn_map_lr_workspace(h_layers, n_layers, B, T, R) + 1024;

@@ -69,8 +69,18 @@ __device__ __host__ __forceinline__ int lr_window_row0(int tile, int s, int R, i
 LrGeom lr_geometry(int s, int R);
 bool attn_map_lr_supported(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int n_idx);
 size_t attn_map_lr_workspace(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R);
+// operands of one layer as tc_prepare_lr stages them in a workspace
+struct LrLayerBufs {
+  __nv_bfloat16 *q_hi, *q_lo, *k_hi, *k_lo, *s_hi, *s_lo, *w_hi, *w_lo;
+  int* range;
+};
+// carve-up of an "upsample after the logits" operand workspace over `n_layers` layers (no launches): the layout
+// tc_prepare_lr writes, so that a later call can find the operands an earlier call staged.  -> first free byte
+char* lr_carve(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, void* workspace, LrLayerBufs* out);
+// bn: token rows per TMA box of the logit window (k_map).  ready (optional, n_layers entries): operands ALREADY staged for
+// these layers (by the forward of the same q / k): nothing is launched, no workspace is consumed, only the maps are encoded.
 int tc_prepare_lr(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, void* workspace, cudaStream_t st,
-                  TcOperands* out, char** ws_end, int bn = TC_BN);   // bn: token rows per TMA box of the logit window (k_map)
+                  TcOperands* out, char** ws_end, int bn = TC_BN, const LrLayerBufs* ready = nullptr);
 
 bool attn_map_tc_supported(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int n_idx);
 size_t attn_map_tc_workspace(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int precision);

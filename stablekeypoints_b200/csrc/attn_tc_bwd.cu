@@ -529,6 +529,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
     uint32_t it = 0;
     int prev_l = -1, prev_b = -1;
     int tk[BW_SEL];                            // token ids of the selected planes of the current image
+    uint32_t valid_mask = 0, mine_mask = 0;    // bit j: plane j names a token (< T) / a token of this thread's columns
     float2 nx_ml = make_float2(0.f, 1.f);
     float nx_dp[BW_SEL];
     auto load_row = [&](const BwUnit& y, float2& ml, float (&dpr)[BW_SEL]) {
@@ -573,6 +574,15 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         named_bar_sync(1, TC_SOFTMAX_THREADS);
 #pragma unroll
         for (int j = 0; j < BW_SEL; ++j) tk[j] = tok_s[j];      // registers: the per-unit loops below read them 32 times
+        // the range tests of the two per-unit loops over the selected planes, once per image instead of once per unit
+        // (three compares and a reconvergence scope per plane and unit: ~110 of the ~1.3 k instructions a warp issues per unit)
+        valid_mask = mine_mask = 0;
+#pragma unroll
+        for (int j = 0; j < BW_SEL; ++j) {
+          const int t = tk[j], tl = tk[j] - tok0;
+          if (t >= 0 && t < P.T) valid_mask |= 1u << j;
+          if (j < P.n_idx && tl >= col0 && tl < col0 + ncol) mine_mask |= 1u << j;
+        }
         prev_l = x.l;
         prev_b = x.b;
       }
@@ -602,8 +612,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         ptx::tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < BW_SEL; ++j) {
-          const int t = tk[j];
-          const float ps = (t >= 0 && t < P.T) ? ptx::ex2(__uint_as_float(sv[j]) - m) * inv_l : 0.0f;
+          const float ps = ((valid_mask >> j) & 1u) ? ptx::ex2(__uint_as_float(sv[j]) - m) * inv_l : 0.0f;
           delta = fmaf(ps, dp[j], delta);
           dp[j] *= ps;                          // dp[j] now holds P_sel[j] * dP[j]
         }
@@ -678,7 +687,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
 #pragma unroll
       for (int j = 0; j < BW_SEL; ++j) {
         const int t = tk[j] - tok0;
-        if (j < P.n_idx && t >= col0 && t < col0 + ncol) {
+        if ((mine_mask >> j) & 1u) {
           const uint32_t off = (t >> 6) * 16384 + row * 128 + ((((t & 63) >> 3) ^ (row & 7)) << 4) + (t & 7) * 2;
           __nv_bfloat16* e = reinterpret_cast<__nv_bfloat16*>(ds_ptr + off);
           *e = __float2bfloat16_rn(__bfloat162float(*e) + dp[j]);
@@ -929,13 +938,13 @@ static int launch_bwd(const BwdParams& P, cudaStream_t st) {
 // one launch of the main kernel over a subset of the captured layers (`sub`, with their global head offsets)
 static int bwd_launch_group(const skp_attn_layer* sub, const int* ghead, int n_sub, int heads_all, int kind, int B, int T, int R,
                             const int64_t* token_idx, int n_idx, int64_t idx_stride, const float* dmaps_sel, const float* dpT,
-                            const float* row_stats, bool x3, char** ws_io, cudaStream_t st) {
+                            const float* row_stats, bool x3, char** ws_io, cudaStream_t st, const LrLayerBufs* ready) {
   BwdParams P;
   memset(&P, 0, sizeof(P));
   char* ws = nullptr;
   const bool lr = kind >= BWD_LR64, wide = kind == BWD_LR128;
   SKP_REQUIRE(!lr || x3, "skp_attn_map_bwd: the upsample-after-logits path is bf16x3 only");
-  int rc = lr ? tc_prepare_lr(sub, n_sub, B, T, R, *ws_io, st, &P.ops, &ws, wide ? 128 : TC_BN)
+  int rc = lr ? tc_prepare_lr(sub, n_sub, B, T, R, *ws_io, st, &P.ops, &ws, wide ? 128 : TC_BN, ready)
               : tc_prepare(sub, n_sub, B, T, R, x3, *ws_io, st, &P.ops, &ws);
   if (rc != SKP_OK) return rc;
   const int tiles = R * R / TC_BM;
@@ -1019,9 +1028,14 @@ static int bwd_launch_group(const skp_attn_layer* sub, const int* ghead, int n_s
   return SKP_OK;
 }
 
+bool attn_map_fwd_stages_lr(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int precision);
+
+// fwd_workspace (optional): the workspace skp_attn_map_fwd staged its operands in for the SAME layers / q / k / B / T / R /
+// precision.  Layers on the upsample-after-logits path then take their native-resolution logits and interpolation tables
+// from it instead of recomputing them (two head splits, the logit GEMM and the table per layer).
 int attn_map_bwd_tc(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, const int64_t* token_idx, int n_idx,
                     int64_t idx_stride, const float* dmaps_sel, const float* row_stats, int precision, void* workspace,
-                    size_t workspace_bytes, cudaStream_t st) {
+                    size_t workspace_bytes, cudaStream_t st, const void* fwd_workspace, size_t fwd_workspace_bytes) {
   SKP_REQUIRE(token_idx && dmaps_sel && row_stats, "skp_attn_map_bwd (tcgen05): token_idx, dmaps_sel and row_stats are required");
   const size_t need = attn_map_bwd_tc_workspace(h_layers, n_layers, B, T, R, precision);
   if (!workspace || workspace_bytes < need) {
@@ -1032,9 +1046,18 @@ int attn_map_bwd_tc(const skp_attn_layer* h_layers, int n_layers, int B, int T, 
   // up to three launches: staged dQ' / dK + bicubic adjoint, upsample-after-logits with 64-tap and with 128-tap windows
   skp_attn_layer group[4][TC_MAX_LAYERS];
   int ghead[4][TC_MAX_LAYERS], n_group[4] = {0, 0, 0, 0}, heads_all = 0;
+  LrLayerBufs fwd_bufs[TC_MAX_LAYERS], ready[4][TC_MAX_LAYERS];
+  bool reuse = false;
+  if (fwd_workspace && attn_map_fwd_stages_lr(h_layers, n_layers, B, T, R, precision)) {
+    const char* end = lr_carve(h_layers, n_layers, B, T, R, const_cast<void*>(fwd_workspace), fwd_bufs);
+    SKP_REQUIRE(static_cast<size_t>(end - static_cast<const char*>(fwd_workspace)) <= fwd_workspace_bytes,
+                "skp_attn_map_bwd: the forward workspace handed back is smaller than the forward's operand layout");
+    reuse = true;
+  }
   for (int l = 0; l < n_layers; ++l) {
     const int gi = bwd_layer_kind(h_layers[l], R);
     SKP_REQUIRE(gi != BWD_NONE, "skp_attn_map_bwd: layer %d has no tensor-core backward", l);
+    ready[gi][n_group[gi]] = fwd_bufs[l];
     group[gi][n_group[gi]] = h_layers[l];
     ghead[gi][n_group[gi]++] = heads_all;
     heads_all += h_layers[l].heads;
@@ -1047,7 +1070,7 @@ int attn_map_bwd_tc(const skp_attn_layer* h_layers, int n_layers, int B, int T, 
   for (int gi = BWD_STAGED; gi <= BWD_LR128; ++gi) {
     if (n_group[gi] == 0) continue;
     int rc = bwd_launch_group(group[gi], ghead[gi], n_group[gi], heads_all, gi, B, T, R, token_idx, n_idx, idx_stride, dmaps_sel,
-                              dpT, row_stats, x3, &ws, st);
+                              dpT, row_stats, x3, &ws, st, reuse && gi >= BWD_LR64 ? ready[gi] : nullptr);
     if (rc != SKP_OK) return rc;
   }
   return SKP_OK;

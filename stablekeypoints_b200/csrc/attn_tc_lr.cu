@@ -282,19 +282,12 @@ __global__ void __launch_bounds__(LRG_THREADS) lr_logits_kernel(const __grid_con
   }
 }
 
-// Stages the operands of the "upsample after the logits" formulation in `workspace` (launches on `st`) and fills
-// `O` so that the main kernels see A = W tables (q_map) and B = s_low (k_map) with d[l] = taps per tile.
-int tc_prepare_lr(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, void* workspace, cudaStream_t st,
-                  TcOperands* O, char** ws_end, int bn) {
+char* lr_carve(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, void* workspace, LrLayerBufs* out) {
   char* ws = reinterpret_cast<char*>(tc_align_up(reinterpret_cast<size_t>(workspace), 1024));
   const int tiles = R * R / TC_BM;
-  __nv_bfloat16* w_tab[TC_MAX_LAYERS][2];
-  int base = 0;
-  SKP_CUDA(cudaFuncSetAttribute(lr_logits_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LRG_DYNAMIC));
   for (int l = 0; l < n_layers; ++l) {
     const skp_attn_layer& a = h_layers[l];
-    SKP_REQUIRE(a.q && a.k, "skp_attn_map: layer %d has null q/k", l);
-    const int d = a.C / a.heads, s2 = a.s * a.s, Bk = a.k_shared ? 1 : B;
+    const int s2 = a.s * a.s, Bk = a.k_shared ? 1 : B;
     const LrGeom g = lr_geometry(a.s, R);
     auto take = [&](size_t bytes) {
       __nv_bfloat16* p = reinterpret_cast<__nv_bfloat16*>(ws);
@@ -303,24 +296,49 @@ int tc_prepare_lr(const skp_attn_layer* h_layers, int n_layers, int B, int T, in
     };
     const size_t qb = static_cast<size_t>(B) * s2 * a.C * 2, kb = static_cast<size_t>(Bk) * T * a.C * 2;
     const size_t sb = static_cast<size_t>(B) * a.heads * T * s2 * 2, wb = static_cast<size_t>(tiles) * TC_BM * g.kw * 2;
-    __nv_bfloat16 *q_hi = take(qb), *q_lo = take(qb), *k_hi = take(kb), *k_lo = take(kb), *s_hi = take(sb), *s_lo = take(sb);
-    __nv_bfloat16 *w_hi = take(wb), *w_lo = take(wb);   // reserved even when an earlier layer's table is reused
-    int* absmax = reinterpret_cast<int*>(take(static_cast<size_t>(B) * a.heads * 2 * sizeof(int)));
+    LrLayerBufs& o = out[l];
+    o.q_hi = take(qb); o.q_lo = take(qb); o.k_hi = take(kb); o.k_lo = take(kb); o.s_hi = take(sb); o.s_lo = take(sb);
+    o.w_hi = take(wb); o.w_lo = take(wb);            // reserved even when an earlier layer's table is reused
+    o.range = reinterpret_cast<int*>(take(static_cast<size_t>(B) * a.heads * 2 * sizeof(int)));
+    for (int m = 0; m < l; ++m)                        // one interpolation table per source size: the first layer's
+      if (h_layers[m].s == a.s) {
+        o.w_hi = out[m].w_hi;
+        o.w_lo = out[m].w_lo;
+        break;
+      }
+  }
+  return ws;
+}
+
+// Stages the operands of the "upsample after the logits" formulation in `workspace` (launches on `st`) and fills
+// `O` so that the main kernels see A = W tables (q_map) and B = s_low (k_map) with d[l] = taps per tile.
+int tc_prepare_lr(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, void* workspace, cudaStream_t st,
+                  TcOperands* O, char** ws_end, int bn, const LrLayerBufs* ready) {
+  LrLayerBufs own[TC_MAX_LAYERS];
+  char* ws = reinterpret_cast<char*>(tc_align_up(reinterpret_cast<size_t>(workspace), 1024));
+  if (!ready) ws = lr_carve(h_layers, n_layers, B, T, R, workspace, own);
+  const LrLayerBufs* bufs = ready ? ready : own;
+  const int tiles = R * R / TC_BM;
+  int base = 0;
+  if (!ready) SKP_CUDA(cudaFuncSetAttribute(lr_logits_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LRG_DYNAMIC));
+  for (int l = 0; l < n_layers; ++l) {
+    const skp_attn_layer& a = h_layers[l];
+    SKP_REQUIRE(a.q && a.k, "skp_attn_map: layer %d has null q/k", l);
+    const int d = a.C / a.heads, s2 = a.s * a.s, Bk = a.k_shared ? 1 : B;
+    const LrGeom g = lr_geometry(a.s, R);
+    __nv_bfloat16 *q_hi = bufs[l].q_hi, *q_lo = bufs[l].q_lo, *k_hi = bufs[l].k_hi, *k_lo = bufs[l].k_lo;
+    __nv_bfloat16 *s_hi = bufs[l].s_hi, *s_lo = bufs[l].s_lo, *w_hi = bufs[l].w_hi, *w_lo = bufs[l].w_lo;
+    int* absmax = bufs[l].range;
+    if (!ready) {
     SKP_CUDA(cudaMemsetAsync(absmax, 0x80, static_cast<size_t>(B) * a.heads * 2 * sizeof(int), st));   // keys of ~ -3e38: below every logit
     const float mult = a.scale * 1.4426950408889634f;
     lr_split_heads_kernel<<<(::skp::note_launch(), dim3(s2, B)), 256, 0, st>>>(a.q, s2, a.C, a.heads, mult, q_hi, q_lo);
     lr_split_heads_kernel<<<(::skp::note_launch(), dim3(T, Bk)), 256, 0, st>>>(a.k, T, a.C, a.heads, 1.0f, k_hi, k_lo);
-    int same = -1;
+    bool own_table = true;
     for (int m = 0; m < l; ++m)
-      if (h_layers[m].s == a.s) same = m;
-    if (same >= 0) {
-      w_hi = w_tab[same][0];
-      w_lo = w_tab[same][1];
-    } else {
+      if (h_layers[m].s == a.s) own_table = false;
+    if (own_table)
       lr_weights_kernel<<<(::skp::note_launch(), tiles), 256, static_cast<size_t>(TC_BM) * (g.nr + a.s) * sizeof(float), st>>>(a.s, R, g.nr, g.kw, w_hi, w_lo);
-    }
-    w_tab[l][0] = w_hi;
-    w_tab[l][1] = w_lo;
     SKP_LAUNCH_CHECK();
     LrGemmParams G;
     memset(&G, 0, sizeof(G));
@@ -333,7 +351,8 @@ int tc_prepare_lr(const skp_attn_layer* h_layers, int n_layers, int B, int T, in
     dim3 grid((T + LRG_BM - 1) / LRG_BM, (s2 + LRG_BN - 1) / LRG_BN, B * a.heads);
     lr_logits_kernel<<<(::skp::note_launch(), grid), LRG_THREADS, LRG_DYNAMIC, st>>>(G);
     SKP_LAUNCH_CHECK();
-    rc = tc_encode_map(&O->q_map[l][0], w_hi, g.kw, TC_BM, tiles, TC_BM);
+    }
+    int rc = tc_encode_map(&O->q_map[l][0], w_hi, g.kw, TC_BM, tiles, TC_BM);
     if (rc == SKP_OK) rc = tc_encode_map(&O->q_map[l][1], w_lo, g.kw, TC_BM, tiles, TC_BM);
     if (rc == SKP_OK) rc = tc_encode_map(&O->k_map[l][0], s_hi, s2, T, B * a.heads, bn);
     if (rc == SKP_OK) rc = tc_encode_map(&O->k_map[l][1], s_lo, s2, T, B * a.heads, bn);

@@ -385,11 +385,11 @@ class _AttentionMaps(torch.autograd.Function):
                  ptr(maps), ptr(stats), prec, ptr(ws), nbytes, stream_of(maps))
         ctx.save_for_backward(token_idx, stats, *qs, *ks)
         ctx.meta = meta
-        ctx.mark_non_differentiable(stats)
-        return maps, stats
+        ctx.mark_non_differentiable(stats, ws)
+        return maps, stats, ws
 
     @staticmethod
-    def backward(ctx, g, _gstats=None):
+    def backward(ctx, g, _gstats=None, _gws=None):
         heads, scales, weights, R, prec = ctx.meta
         n = len(heads)
         token_idx, stats = ctx.saved_tensors[0], ctx.saved_tensors[1]
@@ -426,8 +426,10 @@ class _AttentionMaps(torch.autograd.Function):
         return (None, None, *dqs, *dks)
 
 
-def _attn_backward_compact(meta, token_idx, g, qs, ks, stats=None):
-    """dq, dk for a compact gradient g (B, n_idx, R, R) on planes token_idx (n_idx,) or (B, n_idx)."""
+def _attn_backward_compact(meta, token_idx, g, qs, ks, stats=None, fwd_ws=None):
+    """dq, dk for a compact gradient g (B, n_idx, R, R) on planes token_idx (n_idx,) or (B, n_idx).
+    fwd_ws: the workspace tensor of the forward of the same q / k (`attention_maps(..., return_workspace=True)`): the backward
+    reads the native-resolution logits and interpolation tables the forward staged in it instead of recomputing them."""
     heads, scales, weights, R, prec = meta
     n = len(heads)
     B, T = qs[0].shape[0], ks[0].shape[1]
@@ -442,8 +444,8 @@ def _attn_backward_compact(meta, token_idx, g, qs, ks, stats=None):
         for i in range(0, token_idx.shape[-1], chunk):
             tok = token_idx[..., i:i + chunk].contiguous()
             dsel = g[:, i:i + chunk].contiguous()
-            call("skp_attn_map_bwd", arr, n, B, T, R, ptr(tok), tok.shape[-1], tok.shape[-1] if per_image else 0,
-                 ptr(dsel), ptr(stats), prec, ptr(ws), nbytes, stream_of(g))
+            call("skp_attn_map_bwd_reuse", arr, n, B, T, R, ptr(tok), tok.shape[-1], tok.shape[-1] if per_image else 0,
+                 ptr(dsel), ptr(stats), prec, ptr(ws), nbytes, ptr(fwd_ws), fwd_ws.numel() if fwd_ws is not None else 0, stream_of(g))
     return dqs, dks
 
 
@@ -457,7 +459,7 @@ class _SelectedPlanes(torch.autograd.Function):
     for `attn_map[top_embedding_indices]` (`optimize.py:420-424`)."""
 
     @staticmethod
-    def forward(ctx, meta, token_idx, maps_full, stats, *tensors):
+    def forward(ctx, meta, token_idx, maps_full, stats, fwd_ws, *tensors):
         n = len(meta[0])
         qs = [_f32(t) for t in tensors[:n]]
         ks = [_f32(t) for t in tensors[n:]]
@@ -465,6 +467,7 @@ class _SelectedPlanes(torch.autograd.Function):
         R = meta[3]
         out = torch.gather(maps_full, 1, token_idx.view(B, K, 1, 1).expand(B, K, R, R))
         ctx.has_stats = stats is not None
+        ctx.fwd_ws = fwd_ws if stats is not None else None        # a plain attribute: never part of the graph
         ctx.save_for_backward(token_idx, *([stats] if stats is not None else []), *qs, *ks)
         ctx.meta = meta
         return out
@@ -476,8 +479,9 @@ class _SelectedPlanes(torch.autograd.Function):
         token_idx = saved.pop(0)
         stats = saved.pop(0) if ctx.has_stats else None
         qs, ks = saved[:n], saved[n:]
-        dqs, dks = _attn_backward_compact(ctx.meta, token_idx, g, qs, ks, stats)
-        return (None, None, None, None, *dqs, *dks)
+        dqs, dks = _attn_backward_compact(ctx.meta, token_idx, g, qs, ks, stats, ctx.fwd_ws)
+        ctx.fwd_ws = None
+        return (None, None, None, None, None, *dqs, *dks)
 
 
 def _meta(heads, scales, weights, feature_res, precision, n):
@@ -488,17 +492,19 @@ def _meta(heads, scales, weights, feature_res, precision, n):
 
 
 def selected_planes(maps_full: torch.Tensor, token_idx: torch.Tensor, qs, ks, heads, scales, feature_res: int,
-                    weights=None, precision: str = "auto", row_stats: Optional[torch.Tensor] = None) -> torch.Tensor:
+                    weights=None, precision: str = "auto", row_stats: Optional[torch.Tensor] = None,
+                    fwd_workspace: Optional[torch.Tensor] = None) -> torch.Tensor:
     """(B, K, R, R) = maps_full[b, token_idx[b]] with gradients flowing to qs / ks (see _SelectedPlanes).
-    `row_stats` = the statistics `attention_maps(..., return_stats=True)` returned with `maps_full`."""
+    `row_stats` = the statistics `attention_maps(..., return_stats=True)` returned with `maps_full`; `fwd_workspace` = the
+    workspace tensor of that same call (`return_workspace=True`), which lets the backward reuse the operands it holds."""
     token_idx = token_idx.to(device=maps_full.device, dtype=torch.int64).contiguous()
     return _SelectedPlanes.apply(_meta(heads, scales, weights, feature_res, precision, len(qs)), token_idx,
-                                 maps_full, row_stats, *qs, *ks)
+                                 maps_full, row_stats, fwd_workspace, *qs, *ks)
 
 
 def attention_maps(qs: Sequence[torch.Tensor], ks: Sequence[torch.Tensor], heads: Sequence[int], scales: Sequence[float],
                    feature_res: int, token_idx: Optional[torch.Tensor] = None, weights: Optional[Sequence[float]] = None,
-                   precision: str = "auto", return_stats: bool = False):
+                   precision: str = "auto", return_stats: bool = False, return_workspace: bool = False):
     """qs[l] (B, s_l^2, C_l) low-resolution to_q(x); ks[l] (B or 1, T, C_l) to_k(context).
     -> (B, T', R, R) with T' = len(token_idx) or T.  Differentiable w.r.t. every q and k.
     return_stats: also return the (B, sum heads, R^2, 2) softmax statistics (for `selected_planes`)."""
@@ -507,5 +513,7 @@ def attention_maps(qs: Sequence[torch.Tensor], ks: Sequence[torch.Tensor], heads
         weights = [1.0 / n] * n
     meta = (tuple(int(h) for h in heads), tuple(float(s) for s in scales), tuple(float(w) for w in weights),
             int(feature_res), _lib.PRECISIONS[precision])
-    maps, stats = _AttentionMaps.apply(meta, token_idx, *qs, *ks)
+    maps, stats, ws = _AttentionMaps.apply(meta, token_idx, *qs, *ks)
+    if return_workspace:
+        return maps, stats, ws
     return (maps, stats) if return_stats else maps

@@ -205,10 +205,12 @@ def token_opt_losses(ldm, image, transformed_img, context, transform, controller
     qs, ks, heads, scales, R = _layer_args(handles)
     ctrl.reset()
     with torch.no_grad():
-        maps, stats = ops.attention_maps([q.detach() for q in qs], [k.detach() for k in ks], heads, scales, R,
-                                         return_stats=True)                                              # (2B,T,R,R)
+        maps, stats, fwd_ws = ops.attention_maps([q.detach() for q in qs], [k.detach() for k in ks], heads, scales, R,
+                                                 return_stats=True, return_workspace=True)               # (2B,T,R,R)
         idx = select_tokens_batched(maps[:B], maps[B:], top_k_strategy, furthest_point_num_samples, top_k, sigma, num_subjects)
-    sel = ops.selected_planes(maps, torch.cat([idx, idx], dim=0), qs, ks, heads, scales, R, row_stats=stats)   # (2B,K,R,R)
+    # the backward reuses the native-resolution logits / interpolation tables the forward staged in its workspace
+    sel = ops.selected_planes(maps, torch.cat([idx, idx], dim=0), qs, ks, heads, scales, R, row_stats=stats,
+                              fwd_workspace=fwd_ws)                                                       # (2B,K,R,R)
     per_image = ops.keypoint_losses_batched(sel, transform.inverse_theta(), float(sigma), int(num_subjects))
     return per_image[:, 0].mean(), per_image[:, 1].mean(), idx
 

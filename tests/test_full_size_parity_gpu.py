@@ -105,11 +105,22 @@ def test_bench_backward_vs_fp64_oracle_autograd(ops):
     qc = [q.to(DEV).requires_grad_(True) for q in qs]
     kc = [k.to(DEV).requires_grad_(True) for k in ks]
     with torch.no_grad():
-        full, stats = ops.attention_maps([q.detach() for q in qc], [k.detach() for k in kc], heads, sc, R, return_stats=True)
-    sel = ops.selected_planes(full, idx.to(DEV), qc, kc, heads, sc, R, row_stats=stats)
-    (sel * w.reshape(B, K, R, R).to(DEV)).sum().backward()
+        full, stats, fwd_ws = ops.attention_maps([q.detach() for q in qc], [k.detach() for k in kc], heads, sc, R,
+                                                 return_stats=True, return_workspace=True)
+    # (i) as the optimisation drives it: the backward reuses the operands the forward staged in its workspace
+    # (skp_attn_map_bwd_reuse); (ii) without the hand-over (skp_attn_map_bwd semantics): bit-identical gradients
+    grads = []
+    for ws in (fwd_ws, None):
+        for t in qc + kc:
+            t.grad = None
+        sel = ops.selected_planes(full, idx.to(DEV), qc, kc, heads, sc, R, row_stats=stats, fwd_workspace=ws)
+        (sel * w.reshape(B, K, R, R).to(DEV)).sum().backward()
+        grads.append([t.grad.clone() for t in qc + kc])
     names = [f"dq[{i}]" for i in range(4)] + [f"dk[{i}]" for i in range(4)]
-    for name, got, ref in zip(names, [t.grad for t in qc + kc], want):
+    for name, got, ref in zip(names, grads[0], want):
         scale = float(ref.abs().max())
         err = (got.cpu().double() - ref).abs().max().item()
         assert torch.isfinite(got).all() and err <= 1.5e-2 * scale, f"{name}: {err / scale:.2e} of max"
+    for name, a, b_ in zip(names, grads[0], grads[1]):
+        # same operands, same kernels: only the order of the fp32 reductions into dz / dq may differ
+        assert (a - b_).abs().max().item() <= 1e-5 * float(b_.abs().max()), name
