@@ -34,6 +34,16 @@ namespace skp {
 #define BW_DBG(P) 0
 #endif
 
+// Timestamp trace (diagnostic builds only: nvcc -DSKP_BWD_TRACE): lane 0 of every warp of one CTA stamps clock64 at the
+// marked events of units BW_TR_U0 .. +BW_TR_N and prints them at the end of the kernel (scripts/bwd_trace.py reads the lines).
+#ifdef SKP_BWD_TRACE
+constexpr int BW_TR_U0 = 40, BW_TR_N = 12, BW_TR_EV = 12, BW_TR_CTA = 2;
+__device__ long long g_bw_tr[12][BW_TR_N][BW_TR_EV];
+#define BW_TR(ev) { if (LR && !WIDE && blockIdx.x == BW_TR_CTA && lane == 0 && it >= BW_TR_U0 && it < BW_TR_U0 + BW_TR_N) g_bw_tr[warp][it - BW_TR_U0][ev] = clock64(); }
+#else
+#define BW_TR(ev)
+#endif
+
 constexpr int BW_SEL = 16;            // selected tokens per launch (UMMA N of the S_sel product)
 constexpr int BW_KSEL_BYTES = BW_SEL * 128;   // 16 rows x 128 B
 constexpr int BW_DS_BYTES = TC_BM * TC_BN * 2;   // 64 KB: dS tile, 4 slabs of [128 px][64 tok] bf16
@@ -214,8 +224,12 @@ __device__ __forceinline__ bool bw_flush_between(const BwdParams& P, const BwUni
   return last || nx.hg != x.hg || (!P.ops.k_shared[x.l] && nx.b != x.b);
 }
 
-// 12 warps = 3 warpgroups: {TMA, MMA, 2 idle} shrink to 56 registers, the 8 softmax warps grow to 224
+// 12 warps = 3 warpgroups: {TMA, S issuer, dz issuer, idle} shrink to 64 registers, the 8 softmax warps grow to 216
 constexpr int BW_THREADS = 384;
+// setmaxnreg moves registers inside the CTA's launch allocation (384 threads x 168): what the four small warps give back
+// must cover what the eight softmax warps take, or setmaxnreg.inc waits forever
+constexpr int BW_REGS_LAUNCH = 168, BW_REGS_SMALL = 64, BW_REGS_SOFTMAX = 216;
+static_assert(4 * (BW_REGS_LAUNCH - BW_REGS_SMALL) >= 8 * (BW_REGS_SOFTMAX - BW_REGS_LAUNCH), "setmaxnreg budget");
 #ifndef BW_LR_HOLD
 #define BW_LR_HOLD 2      // chunks (32 tokens each) of a row's dS kept in registers across the wait for the previous dz product
 #endif
@@ -281,8 +295,44 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
   const uint32_t tm_S = tmem_base, tm_dQ = tmem_base + 256, tm_dK = tmem_base + 320;
   auto tm_sel = [&](uint32_t i) { return tmem_base + 448u + 16u * (i & 1u); };     // S_sel, double-buffered by unit parity
 
+  // ---- the products that consume the dS tile of unit (x, it), issued by one thread (LR: lane 0 of warp 2; staged: the S issuer)
+  auto issue_post = [&](const BwUnit& x, uint32_t it, bool dk_fresh) {
+    const int d = P.ops.d[x.l];
+    const int st = it % NST;
+    const uint32_t ks = base + SM::kKOff, dsb = base + SM::kDsOff;
+    const uint32_t qs = base + SM::kQOff + st * SM::kQStage;
+    if (!LR) {
+      // dQ' (128 px x d) = dS (K-major A, K = 256 tokens) * K_hi (MN-major B: rows = tokens)
+      const uint32_t id_dq = bw_idesc(TC_BM, d, 0, 1);
+      const int nkt = (ntok + 15) / 16;
+      for (int k = 0; k < nkt; ++k)
+        ptx::umma_bf16(tm_dQ, bw_desc(dsb + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024), bw_desc(ks + k * 2048, 16384, 1024),
+                       id_dq, k != 0);
+      // dK (128 tok x d per half) += dS^T (MN-major A: rows = pixels) * Q'_hi (MN-major B: rows = pixels)
+      const uint32_t id_dk = bw_idesc(128, d, 1, 1);
+      for (int mh = 0; mh < n_mh; ++mh)
+        for (int k = 0; k < TC_BM / 16; ++k)
+          ptx::umma_bf16(tm_dK + mh * 64, bw_desc(dsb + mh * 2 * 16384 + k * 2048, 16384, 1024),
+                         bw_desc(qs + k * 2048, 16384, 1024), id_dk, (dk_fresh && k == 0) ? 0u : 1u);
+    } else {
+      // dz (128 tok x 64 taps per half) += dS^T (MN-major A: rows = pixels) * W_hi (MN-major B: rows = pixels; the
+      // A stage of this unit's S product).  Descriptors = the unit's base descriptor + a constant per k-step.
+      const uint32_t id_dz = bw_idesc(128, WIDE ? 128 : TC_BK, 1, 1);    // WIDE: both 64-tap blocks of W_hi, 16 KB apart (LBO)
+      const uint64_t b0 = bw_desc(qs, 16384, 1024);
+      for (int mh = 0; mh < n_mh; ++mh) {
+        const uint64_t a0 = bw_desc(dsb + mh * 2 * 16384, 16384, 1024);
+#pragma unroll
+        for (int k = 0; k < TC_BM / 16; ++k)
+          ptx::umma_bf16(tm_dK + mh * 64, a0 + static_cast<uint64_t>(k * (2048 >> 4)), b0 + static_cast<uint64_t>(k * (2048 >> 4)), id_dz,
+                         (dk_fresh && k == 0) ? 0u : 1u);
+      }
+    }
+    ptx::umma_commit(bar_mmadone);
+    ptx::umma_commit(bar_qempty(st));
+  };
+
   if (warp < BW_SOFTMAX_WARP0) {
-  ptx::setmaxnreg_dec<56>();
+  ptx::setmaxnreg_dec<BW_REGS_SMALL>();
   if (warp == 0) {
     // =========================== TMA producer (one lane) ===================================
     if (lane == 0) {
@@ -338,10 +388,9 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
     // =========================== MMA issuer (one lane) =====================================
     if (lane == 0) {
       uint32_t it = 0;
-      bool dk_fresh = true;
-      long long pf_q = 0, pf_ds = 0, pf_is = 0, pf_id = 0;      // profiler (SKP_BWD_DBG & 8), kept in registers
+      long long pf_q = 0, pf_ds = 0, pf_is = 0;      // profiler (SKP_BWD_DBG & 8), kept in registers
       BwUnit x = bw_decode(P, u_begin);
-      const uint32_t ks = base + SM::kKOff, ksel = base + SM::kKselOff, dsb = base + SM::kDsOff;
+      const uint32_t ks = base + SM::kKOff, ksel = base + SM::kKselOff;
       // ---- S = Q' K^T (256 tokens) and S_sel = Q' K_sel^T (16 tokens) of the unit in stage (jt & 1)
       // mode 0: both, S_sel interleaved into the first half of S; 1: S_sel only; 2: S only
       auto issue_S = [&](int l, uint32_t jt, int mode) {
@@ -434,13 +483,22 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         ptx::umma_commit(bar_sfull);
         pf_is += BW_CLK() - c0;
       };
+      // LR: two issuing threads.  This one: the logit products S / S_sel; lane 0 of warp 2: the dz product that consumes dS.
+      // One thread issuing everything spent ~100 cycles per small MMA (N = 16 / 64: 48 on the tensor pipe,
+      // scripts/mma_small_probe.cu) computing descriptors and moving them to uniform registers between the instructions,
+      // with S(u+1) queued behind that.  Staged path: this thread issues dQ' / dK too, AHEAD of S(u+1) (the softmax warps
+      // drain dQ' right after their dS store; S(u+1) first was measured 7 % slower on SDXL's four 32^2 layers).
       bool s_issued = false;       // S of this unit went out early, in the previous iteration
+      bool dk_fresh = true;
       for (int u = u_begin; u < u_end; ++u, ++it) {
         const BwUnit nxu = bw_next(P, x);
-        const int d = P.ops.d[x.l];
-        const int st = it % NST;
-        const uint32_t qs = base + SM::kQOff + st * SM::kQStage;
+        BW_TR(0)
         if (!s_issued) {
+          if (LR && it > 0) {
+            // the accumulator is free once every softmax thread holds S(u-1) in registers
+            ptx::mbar_wait_hint(bar_sfree, (it - 1) & 1u, 1000u);
+            ptx::tc_fence_after();
+          }
           if (WIDE) {                 // two k-blocks: S_sel first (its barrier frees the softmax warps' delta), then S
             issue_S(x.l, it, 1);
             issue_S(x.l, it, 2);
@@ -453,68 +511,54 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         // needs the next W tile, so it runs on the idle tensor pipe while the softmax warps are in this unit's dS pass
         // (WIDE: one operand stage -- the next unit's interpolation table can only be loaded once this unit's dz product
         // has read the current one, so nothing of the next unit is issued ahead)
-        const bool early = LR && !WIDE && u + 1 < u_end && nxu.hg == x.hg && nxu.b == x.b && nxu.r0 == x.r0 && !(BW_DBG(P) & 32);
-        const bool sel_early = early && !(BW_DBG(P) & 128);
-        if (sel_early) issue_S(nxu.l, it + 1, 1);
-        // ... and its S as soon as every softmax thread holds the last chunk of S(u) in registers (s_free), one chunk of
-        // exponentials + the corrections ahead of ds_full
-        const bool s_ahead = early && !(BW_DBG(P) & 256);
-        if (s_ahead) {
+        const bool early = LR && !WIDE && u + 1 < u_end && nxu.hg == x.hg && nxu.b == x.b && nxu.r0 == x.r0;
+        if (early) {
+          issue_S(nxu.l, it + 1, 1);
+          BW_TR(1)
+          // ... and its S as soon as every softmax thread holds S(u) in registers (s_free): under the whole dS pass of unit u
           long long c9 = BW_CLK();
           ptx::mbar_wait_hint(bar_sfree, it & 1u, 1000u);
           ptx::tc_fence_after();
+          BW_TR(2)
           pf_ds += BW_CLK() - c9;
-          issue_S(nxu.l, it + 1, sel_early ? 2 : 0);
+          issue_S(nxu.l, it + 1, 2);
+          BW_TR(3)
           s_issued = true;
         }
-        // ---- wait for dS (bf16, [px][tok]) in shared memory
-        long long c0 = BW_CLK();
-        ptx::mbar_wait_hint(bar_dsfull, it & 1u, 2000u);
-        ptx::tc_fence_after();
-        pf_ds += BW_CLK() - c0;
-        // LR: the softmax warps are done with S(u), so S(u+1) can run AHEAD of the dz product of this unit (they start
-        // on the next unit ~1200 cycles earlier and only need dz(u) retired before their first dS store).  Not when
-        // the next unit reloads k / k_sel: those single buffers are only refilled after this unit's MMAs retire.
-        if (early && !s_ahead) {
-          issue_S(nxu.l, it + 1, sel_early ? 2 : 0);
-          s_issued = true;
-        }
-        c0 = BW_CLK();
         if (!LR) {
-          // dQ' (128 px x d) = dS (K-major A, K = 256 tokens) * K_hi (MN-major B: rows = tokens)
-          const uint32_t id_dq = bw_idesc(TC_BM, d, 0, 1);
-          const int nkt = (ntok + 15) / 16;
-          for (int k = 0; k < nkt; ++k)
-            ptx::umma_bf16(tm_dQ, bw_desc(dsb + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024), bw_desc(ks + k * 2048, 16384, 1024),
-                           id_dq, k != 0);
-          // dK (128 tok x d per half) += dS^T (MN-major A: rows = pixels) * Q'_hi (MN-major B: rows = pixels)
-          const uint32_t id_dk = bw_idesc(128, d, 1, 1);
-          for (int mh = 0; mh < n_mh; ++mh)
-            for (int k = 0; k < TC_BM / 16; ++k)
-              ptx::umma_bf16(tm_dK + mh * 64, bw_desc(dsb + mh * 2 * 16384 + k * 2048, 16384, 1024),
-                             bw_desc(qs + k * 2048, 16384, 1024), id_dk, (dk_fresh && k == 0) ? 0u : 1u);
-        } else {
-          // dz (128 tok x 64 taps per half) += dS^T (MN-major A: rows = pixels) * W_hi (MN-major B: rows = pixels; the
-          // A stage of this unit's S product)
-          const uint32_t id_dz = bw_idesc(128, WIDE ? 128 : TC_BK, 1, 1);    // WIDE: both 64-tap blocks of W_hi, 16 KB apart (LBO)
-          for (int mh = 0; mh < n_mh; ++mh)
-            for (int k = 0; k < TC_BM / 16; ++k)
-              ptx::umma_bf16(tm_dK + mh * 64, bw_desc(dsb + mh * 2 * 16384 + k * 2048, 16384, 1024),
-                             bw_desc(qs + k * 2048, 16384, 1024), id_dz, (dk_fresh && k == 0) ? 0u : 1u);
+          ptx::mbar_wait_hint(bar_dsfull, it & 1u, 2000u);
+          ptx::tc_fence_after();
+          issue_post(x, it, dk_fresh);
+          dk_fresh = bw_flush_between<false>(P, x, nxu, u + 1 >= u_end);
         }
-        ptx::umma_commit(bar_mmadone);
-        ptx::umma_commit(bar_qempty(st));
-        pf_id += BW_CLK() - c0;
-        dk_fresh = bw_flush_between<LR>(P, x, nxu, u + 1 >= u_end);
         x = nxu;
       }
       if (P.prof && blockIdx.x == ((BW_DBG(P) >> 6) & 1)) {
-        P.prof[0] = pf_q; P.prof[1] = pf_ds; P.prof[8] = pf_is; P.prof[9] = pf_id;
+        P.prof[0] = pf_q; P.prof[1] = pf_ds; P.prof[8] = pf_is;
+      }
+    }
+  } else if (warp == 2) {
+    // =========================== LR: MMA issuer of the dz product (one lane) =================
+    if (LR && lane == 0) {
+      uint32_t it = 0;
+      bool dk_fresh = true;
+      BwUnit x = bw_decode(P, u_begin);
+      for (int u = u_begin; u < u_end; ++u, ++it) {
+        const BwUnit nxu = bw_next(P, x);
+        // dS (bf16, [px][tok]) in shared memory.  The operand stage it is multiplied with was waited for by the S issuer
+        // (q_full): S(u) read it before the softmax warps could produce dS(u).
+        ptx::mbar_wait_hint(bar_dsfull, it & 1u, 2000u);
+        ptx::tc_fence_after();
+        BW_TR(4)
+        issue_post(x, it, dk_fresh);
+        BW_TR(5)
+        dk_fresh = bw_flush_between<true>(P, x, nxu, u + 1 >= u_end);
+        x = nxu;
       }
     }
   }
   } else {
-    ptx::setmaxnreg_inc<224>();
+    ptx::setmaxnreg_inc<BW_REGS_SOFTMAX>();
     // =========================== softmax-recompute / dS / drain warps ========================
     const int quad = warp & 3;                 // TMEM lane quadrant this warp may access
     const int ch = (warp - BW_SOFTMAX_WARP0) >> 2;   // column half of the CTA's 256 tokens
@@ -528,7 +572,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
     const int R = P.R;
     uint32_t it = 0;
     int prev_l = -1, prev_b = -1;
-    int tk[BW_SEL];                            // token ids of the selected planes of the current image
+    uint32_t poff[BW_SEL];                     // byte offset of (my row, selected plane j's token) in the dS tile (planes of my columns)
     uint32_t valid_mask = 0, mine_mask = 0;    // bit j: plane j names a token (< T) / a token of this thread's columns
     float2 nx_ml = make_float2(0.f, 1.f);
     float nx_dp[BW_SEL];
@@ -547,13 +591,20 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
     long long pf[6] = {0, 0, 0, 0, 0, 0}, c_end = BW_CLK();   // profiler (SKP_BWD_DBG & 8), kept in registers
     bool mma_pending = false;      // LR: the wait for the previous unit's dz product is deferred to the first dS store
     BwUnit x = bw_decode(P, u_begin), nxu = x;
+    float wgt = 0.0f;                            // P.ops.weight[x.l], re-read when the layer changes
+    if (u_begin < u_end) load_row(x, nx_ml, nx_dp);
+    // The scalar work of a unit's top (next tuple, its window row, the addresses of the next row's statistics and upstream
+    // gradients) is a ~1.2 k-cycle chain of dependent parameter-bank reads, 64-bit multiplies and reconvergence scopes
+    // that every softmax warp repeats in lockstep with the MUFU pipe idle: it now sits behind the first chunk of the dense
+    // pass, where the exponentials leave half the issue slots free (PREP below).
     for (int u = u_begin; u < u_end; ++u, ++it, x = nxu) {
-      nxu = bw_next(P, x);
+      BW_TR(0)
       const int d = P.ops.d[x.l], s = P.s[x.l], C = P.C[x.l];
       const int up = ((R & (R - 1)) | (s & (s - 1))) == 0 ? R >> (__ffs(s) - 1) : R / s, nj = 5 * up;
       const int njp = (nj + 3) & ~3;            // table row pitch: the gather loops run in groups of four taps
-      const float wgt = P.ops.weight[x.l], scale = P.ops.scale[x.l];
+      const float scale = P.ops.scale[x.l];
       if (x.l != prev_l || x.b != prev_b) {
+        wgt = P.ops.weight[x.l];
         named_bar_sync(1, TC_SOFTMAX_THREADS);
         if (!LR && x.l != prev_l) {
           const float ratio = static_cast<float>(s) / R;
@@ -572,63 +623,73 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         }
         if (stid < BW_SEL) tok_s[stid] = stid < P.n_idx ? static_cast<int>(P.token_idx[x.b * P.idx_stride + stid]) : -1;
         named_bar_sync(1, TC_SOFTMAX_THREADS);
-#pragma unroll
-        for (int j = 0; j < BW_SEL; ++j) tk[j] = tok_s[j];      // registers: the per-unit loops below read them 32 times
-        // the range tests of the two per-unit loops over the selected planes, once per image instead of once per unit
-        // (three compares and a reconvergence scope per plane and unit: ~110 of the ~1.3 k instructions a warp issues per unit)
+        // the range tests and the dS-tile addresses of the two per-unit loops over the selected planes, once per image
+        // instead of once per unit (registers: the per-unit loops read them 32 times)
         valid_mask = mine_mask = 0;
 #pragma unroll
         for (int j = 0; j < BW_SEL; ++j) {
-          const int t = tk[j], tl = tk[j] - tok0;
+          const int t = tok_s[j], tl = t - tok0;
           if (t >= 0 && t < P.T) valid_mask |= 1u << j;
           if (j < P.n_idx && tl >= col0 && tl < col0 + ncol) mine_mask |= 1u << j;
+          poff[j] = dsb + static_cast<uint32_t>((tl >> 6) * 16384 + row * 128 + ((((tl & 63) >> 3) ^ (row & 7)) << 4) + (tl & 7) * 2);
         }
         prev_l = x.l;
         prev_b = x.b;
       }
       // (m, l) and the n_idx upstream gradients of this row were fetched one unit ahead (nx_*): a unit
       // is too short to hide a DRAM round trip behind itself
-      if (u == u_begin) load_row(x, nx_ml, nx_dp);
-      const float m = nx_ml.x, inv_l = 1.0f / nx_ml.y;
+      const float m = nx_ml.x, inv_l = ptx::rcp_approx(nx_ml.y);      // l is a normal number on both forward paths (max-subtracted: l >= 1; constant shift: l > 2^-118): no special cases
       float dp[BW_SEL];
 #pragma unroll
       for (int j = 0; j < BW_SEL; ++j) dp[j] = wgt * nx_dp[j];
-      // LR: next unit's row statistics / upstream gradients go out now and land under this unit's dS pass (there is
-      // no long MMA wait at the end of the unit to hide them any more)
-      // Unconditional (the last unit re-reads its own row): a load under a branch made the compiler copy the loaded
-      // registers right behind it, i.e. wait for the whole memory round trip at the loop top (780 cycles per unit).
-      if (LR) load_row(u + 1 < u_end ? nxu : x, nx_ml, nx_dp);
 
       long long c1 = BW_CLK();
       pf[5] += c1 - c_end;                      // loop top: decode, prefetch issue, table rebuilds
+      BW_TR(1)
       ptx::mbar_wait(bar_selfull(it), (it >> 1) & 1u);
       ptx::tc_fence_after();
+      BW_TR(2)
       pf[0] += BW_CLK() - c1;
       c1 = BW_CLK();
       float delta = 0.0f;
+      float psel[BW_SEL];                       // P of the selected planes' tokens (this row)
       {
         uint32_t sv[BW_SEL];
         ptx::tmem_ld16(tm_sel(it) + lane_off, sv);
         ptx::tmem_ld_wait();
+        float dl[4] = {0.0f, 0.0f, 0.0f, 0.0f};     // four chains instead of one 16-deep dependent FFMA chain
 #pragma unroll
         for (int j = 0; j < BW_SEL; ++j) {
-          const float ps = ((valid_mask >> j) & 1u) ? ptx::ex2(__uint_as_float(sv[j]) - m) * inv_l : 0.0f;
-          delta = fmaf(ps, dp[j], delta);
-          dp[j] *= ps;                          // dp[j] now holds P_sel[j] * dP[j]
+          psel[j] = ((valid_mask >> j) & 1u) ? ptx::ex2(__uint_as_float(sv[j]) - m) * inv_l : 0.0f;
+          dl[j & 3] = fmaf(psel[j], dp[j], dl[j & 3]);
         }
+        delta = (dl[0] + dl[1]) + (dl[2] + dl[3]);
+      }
+      // dS of the selected planes' tokens = P (dP - delta), packed now: 8 registers live across the dense pass instead of 32
+      uint32_t pv[BW_SEL / 2];
+#pragma unroll
+      for (int j = 0; j < BW_SEL / 2; ++j) {
+        const __nv_bfloat162 h2 = __floats2bfloat162_rn(psel[2 * j] * (dp[2 * j] - delta), psel[2 * j + 1] * (dp[2 * j + 1] - delta));
+        pv[j] = *reinterpret_cast<const uint32_t*>(&h2);
       }
       // ---- dS = P * (dP - delta): dense part -P*delta for my 128 columns, then the n_idx corrections
       const float nd = -delta * inv_l;
+      BW_TR(3)
       {
         long long c2 = BW_CLK();
         ptx::mbar_wait(bar_sfull, it & 1u);
         ptx::tc_fence_after();
+        BW_TR(4)
         const long long c3 = BW_CLK();
         pf[0] += c3 - c2;
         c1 += c3 - c2;                          // the dS slot of the profile excludes this wait
       }
       {
-        uint32_t v[2][32];
+        // LR: the thread's whole row segment of S goes to registers at once and the accumulator is handed back (s_free): the
+        // S product of the next unit then runs under this unit's entire dS pass instead of under its last chunk (with two
+        // 32-column buffers the softmax warps waited 0.6 - 2 k cycles per unit for S once their loop top was out of the way)
+        constexpr int NBUF = LR ? NCHUNK : 2;
+        uint32_t v[NBUF][32];
         // LR: the first HOLD chunks of dS stay packed in registers until the previous unit's dz product has retired
         // (it still reads the single dS tile): the exponentials of those chunks run under that product
         constexpr int HOLD = LR ? (BW_LR_HOLD < NCHUNK ? BW_LR_HOLD : NCHUNK) : 1;
@@ -641,35 +702,51 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
             *reinterpret_cast<uint4*>(ds_ptr + off) = make_uint4(pk[c][4 * q], pk[c][4 * q + 1], pk[c][4 * q + 2], pk[c][4 * q + 3]);
           }
         };
-        ptx::tmem_ld32(tm_S + lane_off + col0, v[0]);
+        if (LR) {
+#pragma unroll
+          for (int c = 0; c < NCHUNK; ++c) ptx::tmem_ld32(tm_S + lane_off + col0 + 32 * c, v[c]);
+          ptx::tmem_ld_wait();
+          // S(u) is in registers: the tensor pipe may overwrite the accumulator with S(u+1)
+          ptx::tc_fence_before();
+          ptx::mbar_arrive(bar_sfree);
+          BW_TR(7)
+        } else {
+          ptx::tmem_ld32(tm_S + lane_off + col0, v[0]);
+        }
 #pragma unroll
         for (int c = 0; c < NCHUNK; ++c) {
-          ptx::tmem_ld_wait();
-          if (c < NCHUNK - 1) ptx::tmem_ld32(tm_S + lane_off + col0 + 32 * (c + 1), v[(c + 1) & 1]);
-          if (LR && c == NCHUNK - 1) {
-            // S(u) is in registers: the tensor pipe may overwrite the accumulator with S(u+1)
-            ptx::tc_fence_before();
-            ptx::mbar_arrive(bar_sfree);
+          if (!LR) {
+            ptx::tmem_ld_wait();
+            if (c < NCHUNK - 1) ptx::tmem_ld32(tm_S + lane_off + col0 + 32 * (c + 1), v[(c + 1) & 1]);
           }
           if (32 * (c + 1) <= ncol) {
             // all 32 columns of the chunk are tokens (all but the chunk holding T's end): no per-column range test
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
-              const float e0 = ptx::ex2(__uint_as_float(v[c & 1][2 * j]) - m) * nd;
-              const float e1 = ptx::ex2(__uint_as_float(v[c & 1][2 * j + 1]) - m) * nd;
+              const float e0 = ptx::ex2(__uint_as_float(v[c % NBUF][2 * j]) - m) * nd;
+              const float e1 = ptx::ex2(__uint_as_float(v[c % NBUF][2 * j + 1]) - m) * nd;
               const __nv_bfloat162 h2 = __floats2bfloat162_rn(e0, e1);
               pk[c][j] = *reinterpret_cast<const uint32_t*>(&h2);
             }
           } else {
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
-              float e0 = ptx::ex2(__uint_as_float(v[c & 1][2 * j]) - m) * nd;
-              float e1 = ptx::ex2(__uint_as_float(v[c & 1][2 * j + 1]) - m) * nd;
+              float e0 = ptx::ex2(__uint_as_float(v[c % NBUF][2 * j]) - m) * nd;
+              float e1 = ptx::ex2(__uint_as_float(v[c % NBUF][2 * j + 1]) - m) * nd;
               e0 = (32 * c + 2 * j < ncol) ? e0 : 0.0f;
               e1 = (32 * c + 2 * j + 1 < ncol) ? e1 : 0.0f;
               const __nv_bfloat162 h2 = __floats2bfloat162_rn(e0, e1);
               pk[c][j] = *reinterpret_cast<const uint32_t*>(&h2);
             }
+          }
+          if (c == 0) {
+            // PREP: the next unit's tuple; LR: its row statistics / upstream gradients go out now and land under the rest
+            // of this unit (there is no long MMA wait at the end of an LR unit to hide them).  Unconditional (the last unit
+            // re-reads its own row): a load under a branch made the compiler copy the loaded registers right behind it,
+            // i.e. wait for the whole memory round trip (780 cycles per unit).
+            nxu = bw_next(P, x);
+            if (LR) load_row(u + 1 < u_end ? nxu : x, nx_ml, nx_dp);
+            BW_TR(5)
           }
           if (c + 1 == HOLD) {
             if (LR && mma_pending) {
@@ -679,25 +756,28 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
             }
 #pragma unroll
             for (int cc = 0; cc <= c; ++cc) store_chunk(cc);
+            BW_TR(6)
           } else if (c + 1 > HOLD) {
             store_chunk(c);
           }
         }
       }
+      BW_TR(8)
+      // selected planes' tokens of my columns: dS = P (dP - delta), from the fp32 P of the S_sel product.  A predicated 16-bit
+      // STORE over the dense pass's -P delta (same thread, program order), not a read-modify-write of the bf16 tile: sixteen
+      // reconvergence scopes with a dependent LDS -> add -> pack -> STS chain each were ~19 % of the softmax warps' samples
 #pragma unroll
       for (int j = 0; j < BW_SEL; ++j) {
-        const int t = tk[j] - tok0;
-        if ((mine_mask >> j) & 1u) {
-          const uint32_t off = (t >> 6) * 16384 + row * 128 + ((((t & 63) >> 3) ^ (row & 7)) << 4) + (t & 7) * 2;
-          __nv_bfloat16* e = reinterpret_cast<__nv_bfloat16*>(ds_ptr + off);
-          *e = __float2bfloat16_rn(__bfloat162float(*e) + dp[j]);
-        }
+        const unsigned short hv = static_cast<unsigned short>((j & 1) ? pv[j >> 1] >> 16 : pv[j >> 1] & 0xffffu);
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %0, 0;\n\t@p st.shared.b16 [%1], %2;\n\t}" ::"r"((mine_mask >> j) & 1u),
+                     "r"(poff[j]), "h"(hv) : "memory");
       }
       pf[1] += BW_CLK() - c1;
       c1 = BW_CLK();
       ptx::fence_proxy_async();
       ptx::tc_fence_before();
       ptx::mbar_arrive(bar_dsfull);
+      BW_TR(9)
       pf[2] += BW_CLK() - c1;
       c1 = BW_CLK();
 
@@ -712,6 +792,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       } else {
         mma_pending = true;
       }
+      BW_TR(11)
       pf[3] += BW_CLK() - c1;
       c1 = BW_CLK();
       if (!LR && ch * 32 < d && !(BW_DBG(P) & 4)) {
@@ -828,6 +909,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
                              __uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3]));
             }
           }
+      BW_TR(10)
           ptx::tc_fence_before();
         }
       } else
@@ -869,6 +951,15 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem_base, 512);
   }
+#ifdef SKP_BWD_TRACE
+  if (LR && !WIDE && blockIdx.x == BW_TR_CTA && lane == 0 && (warp == 1 || warp >= BW_SOFTMAX_WARP0))
+    for (int i = 0; i < BW_TR_N; ++i) {
+      const long long* e = g_bw_tr[warp][i];
+      const long long t0 = g_bw_tr[1][0][0];
+      printf("TR w%02d u%02d %lld %lld %lld %lld %lld %lld %lld %lld %lld %lld %lld %lld\n", warp, i, e[0] - t0, e[1] - t0, e[2] - t0, e[3] - t0,
+             e[4] - t0, e[5] - t0, e[6] - t0, e[7] - t0, e[8] - t0, e[9] - t0, e[10] - t0, e[11] - t0);
+    }
+#endif
 }
 
 // ==========================================================================================
