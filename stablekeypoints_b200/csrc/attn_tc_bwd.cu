@@ -116,13 +116,19 @@ template <int NPROD, bool WIDE = false>
 struct BwSmem {
   static constexpr int kNkb = WIDE ? 2 : 1;                         // 64-wide k-blocks of the S product
   static constexpr int kBn = WIDE ? 128 : TC_BN;                    // tokens per CTA
-  static constexpr int kQStages = WIDE ? 1 : 2;
-  static constexpr int kAHalf = kNkb * TC_A_BYTES;                  // [hi k-block 0 (, 1)] then the same for lo
-  static constexpr int kQStage = (NPROD == 3 ? 2 : 1) * kAHalf;
+  // A operand (Q' tile / interpolation table of the pixel tile): the hi half is also the B operand of the products that
+  // consume dS, so its slot is busy until those retire; the lo half only until the unit's logit product has.  With two
+  // combined stages the tile of unit u+1 could only be fetched once the dz product of unit u-1 had retired, and S(u+1)
+  // arrived ~1 k cycles late every other unit (SKP_BWD_TRACE): three hi slots + two lo slots instead (+16 KB).
+  static constexpr int kHiStages = WIDE ? 1 : 3;
+  static constexpr int kLoStages = WIDE ? 1 : 2;
+  static constexpr int kAHalf = kNkb * TC_A_BYTES;                  // one slot: k-block 0 (, 1)
+  static constexpr int kQStage = (NPROD == 3 ? 2 : 1) * kAHalf;     // bytes of a unit's A operand (hi + lo)
   static constexpr int kQOff = 0;
+  static constexpr int kLoOff = kQOff + kHiStages * kAHalf;
   static constexpr int kKBlock = kBn * TC_BK * 2;                   // one k-block of the k / logit-window tile
   static constexpr int kKHalf = kNkb * kKBlock;
-  static constexpr int kKOff = kQOff + kQStages * kQStage;          // k hi (+ lo)
+  static constexpr int kKOff = kLoOff + (NPROD == 3 ? kLoStages * kAHalf : 0);          // k hi (+ lo)
   static constexpr int kKBytes = (NPROD == 3 ? 2 : 1) * kKHalf;
   static constexpr int kKselOff = kKOff + kKBytes;
   static constexpr int kKselHalf = kNkb * BW_KSEL_BYTES;
@@ -130,11 +136,12 @@ struct BwSmem {
   static constexpr int kDsOff = kKselOff + kKselBytes;              // dS tile; aliased by the fp32 dQ' staging
   static constexpr int kDsBytes = TC_BM * kBn * 2;
   static constexpr int kWxtOff = kDsOff + (WIDE ? kDsBytes : BW_DS_BYTES);
-  static constexpr int kBarOff = kWxtOff + BW_WXT_FLOATS * 4;       // q_full[2], q_empty[2], s_full, ds_full, mma_done, sel_full[2], s_free
-  static constexpr int kTmemPtrOff = kBarOff + 8 * 10;
+  static constexpr int kBarOff = kWxtOff + BW_WXT_FLOATS * 4;       // q_full[3], hi_empty[3], lo_empty[2], s_full, ds_full, mma_done, sel_full[2], s_free
+  static constexpr int kTmemPtrOff = kBarOff + 8 * 14;
   static constexpr int kTokOff = kTmemPtrOff + 8;                   // int tok[16]
   static constexpr int kTotal = kTokOff + 4 * BW_SEL;
   static constexpr int kDynamic = kTotal + 1024;
+  static_assert(kDynamic <= 232448, "over the 227 KB of dynamic shared memory per CTA");
 };
 
 __device__ __forceinline__ uint64_t bw_desc(uint32_t addr, uint32_t lbo, uint32_t sbo) {
@@ -243,7 +250,7 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
 attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
   using SM = BwSmem<NPROD, WIDE>;
   static_assert(!WIDE || (LR && NPROD == 3), "wide windows exist on the upsample-after-logits path only");
-  constexpr int NKB = SM::kNkb, BNT = SM::kBn, NST = SM::kQStages;
+  constexpr int NKB = SM::kNkb, BNT = SM::kBn, HS = SM::kHiStages, LS = SM::kLoStages;
   constexpr int CPT = BNT / 2;            // logit columns per softmax thread (row, column half): 128, WIDE: 64
   constexpr int NCHUNK = CPT / 32;
   extern __shared__ uint8_t smem_raw[];
@@ -259,23 +266,27 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
   const int ntok = max(0, min(BNT, P.T - tok0));            // tokens this CTA owns
   const int n_mh = ntok > 128 ? 2 : 1;
 
-  auto bar_qfull = [&](int s) { return base + SM::kBarOff + 8u * s; };
-  auto bar_qempty = [&](int s) { return base + SM::kBarOff + 8u * (2 + s); };
-  const uint32_t bar_sfull = base + SM::kBarOff + 8u * 4;
-  const uint32_t bar_dsfull = base + SM::kBarOff + 8u * 5;
-  const uint32_t bar_mmadone = base + SM::kBarOff + 8u * 6;
-  const uint32_t bar_sfree = base + SM::kBarOff + 8u * 9;
-  auto bar_selfull = [&](uint32_t i) { return base + SM::kBarOff + 8u * (7 + (i & 1u)); };
+  auto bar_qfull = [&](int s) { return base + SM::kBarOff + 8u * s; };               // unit's A operand landed (slot it % HS)
+  auto bar_hiempty = [&](int s) { return base + SM::kBarOff + 8u * (3 + s); };        // hi slot: every MMA of the unit retired
+  auto bar_loempty = [&](int s) { return base + SM::kBarOff + 8u * (6 + s); };        // lo slot: the unit's logit products retired
+  const uint32_t bar_sfull = base + SM::kBarOff + 8u * 8;
+  const uint32_t bar_dsfull = base + SM::kBarOff + 8u * 9;
+  const uint32_t bar_mmadone = base + SM::kBarOff + 8u * 10;
+  const uint32_t bar_sfree = base + SM::kBarOff + 8u * 13;
+  auto bar_selfull = [&](uint32_t i) { return base + SM::kBarOff + 8u * (11 + (i & 1u)); };
+  auto a_hi_slot = [&](uint32_t i) { return base + SM::kQOff + (i % HS) * SM::kAHalf; };
+  auto a_lo_slot = [&](uint32_t i) { return base + SM::kLoOff + (i % LS) * SM::kAHalf; };
   volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(base_ptr + SM::kTmemPtrOff);
   volatile int* tok_s = reinterpret_cast<volatile int*>(base_ptr + SM::kTokOff);
   float* wxt = reinterpret_cast<float*>(base_ptr + SM::kWxtOff);
   float* stg = reinterpret_cast<float*>(base_ptr + SM::kDsOff);       // [128][64] fp32, chunk-swizzled
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < 3; ++s) {
       ptx::mbar_init(bar_qfull(s), 1);
-      ptx::mbar_init(bar_qempty(s), 1);
+      ptx::mbar_init(bar_hiempty(s), 1);
     }
+    for (int s = 0; s < 2; ++s) ptx::mbar_init(bar_loempty(s), 1);
     ptx::mbar_init(bar_sfull, 1);
     ptx::mbar_init(bar_dsfull, TC_SOFTMAX_THREADS);
     ptx::mbar_init(bar_mmadone, 1);
@@ -298,9 +309,8 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
   // ---- the products that consume the dS tile of unit (x, it), issued by one thread (LR: lane 0 of warp 2; staged: the S issuer)
   auto issue_post = [&](const BwUnit& x, uint32_t it, bool dk_fresh) {
     const int d = P.ops.d[x.l];
-    const int st = it % NST;
     const uint32_t ks = base + SM::kKOff, dsb = base + SM::kDsOff;
-    const uint32_t qs = base + SM::kQOff + st * SM::kQStage;
+    const uint32_t qs = a_hi_slot(it);
     if (!LR) {
       // dQ' (128 px x d) = dS (K-major A, K = 256 tokens) * K_hi (MN-major B: rows = tokens)
       const uint32_t id_dq = bw_idesc(TC_BM, d, 0, 1);
@@ -328,7 +338,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       }
     }
     ptx::umma_commit(bar_mmadone);
-    ptx::umma_commit(bar_qempty(st));
+    ptx::umma_commit(bar_hiempty(it % HS));
   };
 
   if (warp < BW_SOFTMAX_WARP0) {
@@ -344,23 +354,24 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       BwUnit x = bw_decode(P, u_begin);
       for (int u = u_begin; u < u_end; ++u, ++it, x = bw_next(P, x)) {
         const int h = P.ops.heads[x.l];
-        const int st = it % NST;
-        ptx::mbar_wait_hint(bar_qempty(st), ((it / NST) & 1u) ^ 1u, 2000u);
+        const int st = it % HS;
+        ptx::mbar_wait_hint(bar_hiempty(st), ((it / HS) & 1u) ^ 1u, 2000u);
+        if (NPROD == 3) ptx::mbar_wait_hint(bar_loempty(it % LS), ((it / LS) & 1u) ^ 1u, 2000u);
         const int r0 = LR ? x.r0 : 0;
         const bool need_k = LR ? (x.hg != prev_hg || x.b != prev_b || r0 != prev_r0)
                                : (x.hg != prev_hg || (!P.ops.k_shared[x.l] && x.b != prev_b));
         const bool need_ksel = need_k || x.b != prev_b;
-        if (need_ksel && it > 0) ptx::mbar_wait_hint(bar_qempty((it - 1) % NST), ((it - 1) / NST) & 1u, 2000u);   // previous unit done with k / k_sel
+        if (need_ksel && it > 0) ptx::mbar_wait_hint(bar_hiempty((it - 1) % HS), ((it - 1) / HS) & 1u, 2000u);   // previous unit done with k / k_sel
         const uint32_t bytes = SM::kQStage + (need_k ? SM::kKBytes : 0) + (need_ksel ? SM::kKselBytes : 0);
         ptx::mbar_arrive_expect_tx(bar_qfull(st), bytes);
         const int qz = x.b * h + x.head;
-        const uint32_t qs = base + SM::kQOff + st * SM::kQStage;
+        const uint32_t qs = a_hi_slot(it), qs_lo = a_lo_slot(it);
         const int a_row = LR ? 0 : x.tile * TC_BM, a_z = LR ? x.tile : qz;     // (k, row, batch) of the A tile
         const int b_k0 = LR ? r0 * P.s[x.l] : 0;                              // first tap of the window in the s*s row
 #pragma unroll
         for (int kb = 0; kb < NKB; ++kb) {
           ptx::tma_load_3d(qs + kb * TC_A_BYTES, &P.ops.q_map[x.l][0], bar_qfull(st), kb * TC_BK, a_row, a_z);
-          if (NPROD == 3) ptx::tma_load_3d(qs + SM::kAHalf + kb * TC_A_BYTES, &P.ops.q_map[x.l][1], bar_qfull(st), kb * TC_BK, a_row, a_z);
+          if (NPROD == 3) ptx::tma_load_3d(qs_lo + kb * TC_A_BYTES, &P.ops.q_map[x.l][1], bar_qfull(st), kb * TC_BK, a_row, a_z);
         }
         if (need_k) {
           const int kz = LR ? qz : (P.ops.k_shared[x.l] ? 0 : x.b * h) + x.head;
@@ -394,10 +405,10 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       // ---- S = Q' K^T (256 tokens) and S_sel = Q' K_sel^T (16 tokens) of the unit in stage (jt & 1)
       // mode 0: both, S_sel interleaved into the first half of S; 1: S_sel only; 2: S only
       auto issue_S = [&](int l, uint32_t jt, int mode) {
-        const uint32_t qs = base + SM::kQOff + (jt % NST) * SM::kQStage;
+        const uint32_t qs = a_hi_slot(jt), ql = a_lo_slot(jt);
         const uint32_t tsel = tm_sel(jt), selbar = bar_selfull(jt);
         long long c0 = BW_CLK();
-        ptx::mbar_wait_hint(bar_qfull(jt % NST), (jt / NST) & 1u, 2000u);
+        ptx::mbar_wait_hint(bar_qfull(jt % HS), (jt / HS) & 1u, 2000u);
         ptx::tc_fence_after();
         pf_q += BW_CLK() - c0;
         c0 = BW_CLK();
@@ -412,7 +423,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
           for (int kk = 0; kk < nk16; ++kk) {
             const uint64_t a_hi = bw_desc(qs + ko(kk, TC_A_BYTES), 16, 1024), s_hi = bw_desc(ksel + ko(kk, BW_KSEL_BYTES), 16, 1024);
             if (NPROD == 3) {
-              const uint64_t a_lo = bw_desc(qs + SM::kAHalf + ko(kk, TC_A_BYTES), 16, 1024);
+              const uint64_t a_lo = bw_desc(ql + ko(kk, TC_A_BYTES), 16, 1024);
               const uint64_t s_lo = bw_desc(ksel + SM::kKselHalf + ko(kk, BW_KSEL_BYTES), 16, 1024);
               ptx::umma_bf16(tsel, a_hi, s_lo, id_sel, kk != 0);
               ptx::umma_bf16(tsel, a_lo, s_hi, id_sel, 1u);
@@ -430,7 +441,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
           for (int kk = 0; kk < nk16; ++kk) {
             const uint64_t a_hi = bw_desc(qs + ko(kk, TC_A_BYTES), 16, 1024), b_hi = bw_desc(ks + ko(kk, SM::kKBlock), 16, 1024);
             if (NPROD == 3) {
-              const uint64_t a_lo = bw_desc(qs + SM::kAHalf + ko(kk, TC_A_BYTES), 16, 1024);
+              const uint64_t a_lo = bw_desc(ql + ko(kk, TC_A_BYTES), 16, 1024);
               const uint64_t b_lo = bw_desc(ks + SM::kKHalf + ko(kk, SM::kKBlock), 16, 1024);
               ptx::umma_bf16(tm_S, a_hi, b_lo, id_S, kk != 0);
               ptx::umma_bf16(tm_S, a_lo, b_hi, id_S, 1u);
@@ -440,6 +451,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
             }
           }
           ptx::umma_commit(bar_sfull);
+          if (NPROD == 3) ptx::umma_commit(bar_loempty(jt % LS));
           pf_is += BW_CLK() - c0;
           return;
         }
@@ -455,9 +467,9 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
           const uint64_t p_hi = bw_desc(qs + k0 * 32, 16, 1024), r_hi = bw_desc(qs + k1 * 32, 16, 1024);
           const uint64_t s0_hi = bw_desc(ksel + k0 * 32, 16, 1024), s1_hi = bw_desc(ksel + k1 * 32, 16, 1024);
           if (NPROD == 3) {
-            const uint64_t a_lo = bw_desc(qs + SM::kAHalf + kk * 32, 16, 1024);
+            const uint64_t a_lo = bw_desc(ql + kk * 32, 16, 1024);
             const uint64_t b_lo = bw_desc(ks + SM::kKHalf + kk * 32, 16, 1024);
-            const uint64_t p_lo = bw_desc(qs + SM::kAHalf + k0 * 32, 16, 1024), r_lo = bw_desc(qs + SM::kAHalf + k1 * 32, 16, 1024);
+            const uint64_t p_lo = bw_desc(ql + k0 * 32, 16, 1024), r_lo = bw_desc(ql + k1 * 32, 16, 1024);
             const uint64_t s0_lo = bw_desc(ksel + SM::kKselHalf + k0 * 32, 16, 1024);
             const uint64_t s1_lo = bw_desc(ksel + SM::kKselHalf + k1 * 32, 16, 1024);
             ptx::umma_bf16(tm_S, a_hi, b_lo, id_S, kk != 0);
@@ -481,6 +493,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
           if (kk + 1 == n_selblk) ptx::umma_commit(selbar);
         }
         ptx::umma_commit(bar_sfull);
+        if (NPROD == 3) ptx::umma_commit(bar_loempty(jt % LS));
         pf_is += BW_CLK() - c0;
       };
       // LR: two issuing threads.  This one: the logit products S / S_sel; lane 0 of warp 2: the dz product that consumes dS.
