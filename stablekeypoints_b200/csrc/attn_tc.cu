@@ -762,6 +762,26 @@ int tc_encode_map(CUtensorMap* m, void* ptr, int d, int rows, int batch, int box
   return SKP_OK;
 }
 
+// fp32 (inner, rows, batch) array, box (32 floats = one 128 B swizzle row, box_rows, 1): the backward's logit-gradient flush
+int tc_encode_map_f32(CUtensorMap* m, void* ptr, int inner, int rows, int batch, int box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) {
+    set_error("cuTensorMapEncodeTiled entry point not available");
+    return SKP_ERR_CUDA;
+  }
+  cuuint64_t dims[3] = {static_cast<cuuint64_t>(inner), static_cast<cuuint64_t>(rows), static_cast<cuuint64_t>(batch)};
+  cuuint64_t strides[2] = {static_cast<cuuint64_t>(inner) * 4, static_cast<cuuint64_t>(inner) * 4 * rows};
+  cuuint32_t box[3] = {32, static_cast<cuuint32_t>(box_rows), 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled (fp32) failed with CUresult %d (inner=%d rows=%d batch=%d)", static_cast<int>(r), inner, rows, batch);
+    return SKP_ERR_CUDA;
+  }
+  return SKP_OK;
+}
+
 bool attn_map_tc_supported(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, int n_idx) {
   if (!h_layers || n_layers < 1 || n_layers > TC_MAX_LAYERS || B < 1 || B > 65535) return false;
   if (T < 1 || T > 2 * TC_BN || (static_cast<int64_t>(R) * R) % TC_BM != 0) return false;

@@ -89,6 +89,7 @@ size_t attn_map_staged_workspace(const skp_attn_layer* h_layers, int n_layers, i
 int tc_prepare(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R, bool x3, void* workspace, cudaStream_t st,
                TcOperands* out, char** ws_end);
 int tc_encode_map(CUtensorMap* m, void* ptr, int d, int rows, int batch, int box_rows);
+int tc_encode_map_f32(CUtensorMap* m, void* ptr, int inner, int rows, int batch, int box_rows);
 
 inline size_t tc_align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 

@@ -60,6 +60,7 @@ struct BwdParams {
   // "upsample after the logits" launches (template LR; ops then holds W tables / native-resolution logits, ksel_map the
   // selected tokens' logit rows): fp32 accumulator of the logit gradient dz[b*h + head][token][s*s] of every layer
   float* dz[TC_MAX_LAYERS];
+  CUtensorMap dz_map[TC_MAX_LAYERS];        // dz as (s*s, T, B*h) fp32, box (32, 128, 1): target of the window flush (TMA reduce-add)
   const unsigned char* wr0[TC_MAX_LAYERS];  // first source row of every tile's window (lr_window_row0 costs two divisions
                                             // and a float->int chain, ~700 cycles of dependent latency per call)
   int ghead[TC_MAX_LAYERS];                 // first head of the layer among ALL captured layers (row_stats index)
@@ -603,6 +604,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
     };
     long long pf[6] = {0, 0, 0, 0, 0, 0}, c_end = BW_CLK();   // profiler (SKP_BWD_DBG & 8), kept in registers
     bool mma_pending = false;      // LR: the wait for the previous unit's dz product is deferred to the first dS store
+    bool flush_pending = false;    // LR: a window flush (TMA reduce out of the dS tile's bytes) may still be reading shared memory
     BwUnit x = bw_decode(P, u_begin), nxu = x;
     float wgt = 0.0f;                            // P.ops.weight[x.l], re-read when the layer changes
     if (u_begin < u_end) load_row(x, nx_ml, nx_dp);
@@ -767,6 +769,12 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
               ptx::tc_fence_after();
               mma_pending = false;
             }
+            if (LR && !WIDE && flush_pending) {
+              // the previous unit's window flush was staged in the dS tile: the TMA engine must have read it
+              if (stid == 0) ptx::bulk_wait_group_read0();
+              named_bar_sync(1, TC_SOFTMAX_THREADS);
+              flush_pending = false;
+            }
 #pragma unroll
             for (int cc = 0; cc <= c; ++cc) store_chunk(cc);
             BW_TR(6)
@@ -903,7 +911,36 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         // ---- dz: flush the window accumulator (token rows x 64 taps) when the next tile leaves this window
         // thread (row, ch): token row of the accumulator's lane; 64 of its tap columns (WIDE: tap half ch of the one
         // 128-token accumulator; else all 64 taps of token half ch)
-        if (lr_flush && (WIDE || ch < n_mh)) {
+        if (!WIDE && lr_flush) {
+          // The accumulator goes through shared memory to the TMA engine, which adds it into dz at L2 (cp.reduce.async.bulk):
+          // token half ch = two [128 tokens][32 taps] fp32 tiles (128 B rows, 128B swizzle) in the bytes of the dS tile, free
+          // once the dz product has retired (waited for above).  As red.global.add.v4.f32 from the registers (each warp
+          // instruction touching 32 half-used sectors) a flush kept the softmax warps for ~5.4 k cycles (SKP_BWD_TRACE).
+          if (ch < n_mh) {
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+              uint32_t v[32];
+              ptx::tmem_ld32(tm_dK + lane_off + ch * 64 + c * 32, v);
+              ptx::tmem_ld_wait();
+              uint8_t* tile = ds_ptr + (ch * 2 + c) * 16384 + row * 128;
+#pragma unroll
+              for (int q = 0; q < 8; ++q)
+                *reinterpret_cast<uint4*>(tile + ((q ^ (row & 7)) << 4)) = make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+            }
+            ptx::tc_fence_before();
+          }
+          ptx::fence_proxy_async();
+          named_bar_sync(1, TC_SOFTMAX_THREADS);
+          if (stid == 0) {
+            const int z = x.b * P.ops.heads[x.l] + x.head;
+            for (int t4 = 0; t4 < 2 * n_mh; ++t4)
+              ptx::tma_reduce_add_3d(&P.dz_map[x.l], dsb + t4 * 16384, x.r0 * s + (t4 & 1) * 32, tok0 + (t4 >> 1) * 128, z);
+            ptx::bulk_commit_group();
+          }
+          flush_pending = true;
+      BW_TR(10)
+        }
+        if (WIDE && lr_flush) {
           const int t = tok0 + (WIDE ? 0 : ch * 128) + row;
           const int h = P.ops.heads[x.l];
           const int r0 = x.r0;
@@ -957,6 +994,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
   }
 
   // ---- teardown -------------------------------------------------------------------------------
+  if (LR && !WIDE && threadIdx.x == BW_SOFTMAX_WARP0 * 32) ptx::bulk_wait_group0();      // the last window flush (issued by this thread)
   __syncwarp();
   ptx::tc_fence_before();
   __syncthreads();
@@ -1080,6 +1118,8 @@ static int bwd_launch_group(const skp_attn_layer* sub, const int* ghead, int n_s
       const size_t dzb = tc_align_up(static_cast<size_t>(B) * a.heads * T * a.s * a.s * 4, 1024);
       P.dz[l] = reinterpret_cast<float*>(ws);
       SKP_CUDA(cudaMemsetAsync(ws, 0, dzb, st));
+      rc = tc_encode_map_f32(&P.dz_map[l], ws, a.s * a.s, T, B * a.heads, 128);
+      if (rc != SKP_OK) return rc;
       ws += dzb;
       post_ws[l] = ws;
       ws += lr_bwd_post_workspace(a, B, T) - dzb;
