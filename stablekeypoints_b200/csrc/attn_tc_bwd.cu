@@ -362,7 +362,13 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         const bool need_k = LR ? (x.hg != prev_hg || x.b != prev_b || r0 != prev_r0)
                                : (x.hg != prev_hg || (!P.ops.k_shared[x.l] && x.b != prev_b));
         const bool need_ksel = need_k || x.b != prev_b;
-        if (need_ksel && it > 0) ptx::mbar_wait_hint(bar_hiempty((it - 1) % HS), ((it - 1) / HS) & 1u, 2000u);   // previous unit done with k / k_sel
+        // previous unit done with k / k_sel.  LR: only the logit products read them (lo_empty: S and S_sel of the previous unit
+        // have retired, early in its dS pass), so a new window is fetched a unit ahead like the tables; staged path: the dQ'
+        // product reads k too (hi_empty: all MMAs of the previous unit)
+        if (need_ksel && it > 0) {
+          if (LR && !WIDE) ptx::mbar_wait_hint(bar_loempty((it - 1) % LS), ((it - 1) / LS) & 1u, 2000u);
+          else ptx::mbar_wait_hint(bar_hiempty((it - 1) % HS), ((it - 1) / HS) & 1u, 2000u);
+        }
         const uint32_t bytes = SM::kQStage + (need_k ? SM::kKBytes : 0) + (need_ksel ? SM::kKselBytes : 0);
         ptx::mbar_arrive_expect_tx(bar_qfull(st), bytes);
         const int qz = x.b * h + x.head;
@@ -452,7 +458,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
             }
           }
           ptx::umma_commit(bar_sfull);
-          if (NPROD == 3) ptx::umma_commit(bar_loempty(jt % LS));
+          ptx::umma_commit(bar_loempty(jt % LS));
           pf_is += BW_CLK() - c0;
           return;
         }
@@ -494,7 +500,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
           if (kk + 1 == n_selblk) ptx::umma_commit(selbar);
         }
         ptx::umma_commit(bar_sfull);
-        if (NPROD == 3) ptx::umma_commit(bar_loempty(jt % LS));
+        ptx::umma_commit(bar_loempty(jt % LS));
         pf_is += BW_CLK() - c0;
       };
       // LR: two issuing threads.  This one: the logit products S / S_sel; lane 0 of warp 2: the dz product that consumes dS.
@@ -521,11 +527,11 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
           }
         }
         s_issued = false;
-        // LR, next tile in the same window (no k / k_sel reload, whose TMA would wait for this unit's MMAs): its S_sel only
-        // needs the next W tile, so it runs on the idle tensor pipe while the softmax warps are in this unit's dS pass
-        // (WIDE: one operand stage -- the next unit's interpolation table can only be loaded once this unit's dz product
-        // has read the current one, so nothing of the next unit is issued ahead)
-        const bool early = LR && !WIDE && u + 1 < u_end && nxu.hg == x.hg && nxu.b == x.b && nxu.r0 == x.r0;
+        // LR: the next unit's S_sel runs on the idle tensor pipe while the softmax warps are in this unit's dS pass -- also when
+        // it interpolates from another window (the producer refills k / k_sel as soon as this unit's logit products have
+        // retired; waiting for the dz product first cost ~5 k cycles per window change).  WIDE: one operand stage -- the next
+        // unit's interpolation table can only be loaded once this unit's dz product has read the current one.
+        const bool early = LR && !WIDE && u + 1 < u_end;
         if (early) {
           issue_S(nxu.l, it + 1, 1);
           BW_TR(1)
