@@ -613,6 +613,9 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
     bool flush_pending = false;    // LR: a window flush (TMA reduce out of the dS tile's bytes) may still be reading shared memory
     BwUnit x = bw_decode(P, u_begin), nxu = x;
     float wgt = 0.0f;                            // P.ops.weight[x.l], re-read when the layer changes
+    float m = 0.0f, nd = 0.0f;                   // row prologue of the current unit (row_prologue below)
+    uint32_t pv[BW_SEL / 2];
+    bool have_row = false;                       // ... already computed during the previous unit
     if (u_begin < u_end) load_row(x, nx_ml, nx_dp);
     // The scalar work of a unit's top (next tuple, its window row, the addresses of the next row's statistics and upstream
     // gradients) is a ~1.2 k-cycle chain of dependent parameter-bank reads, 64-bit multiplies and reconvergence scopes
@@ -658,43 +661,51 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         prev_b = x.b;
       }
       // (m, l) and the n_idx upstream gradients of this row were fetched one unit ahead (nx_*): a unit
-      // is too short to hide a DRAM round trip behind itself
-      const float m = nx_ml.x, inv_l = ptx::rcp_approx(nx_ml.y);      // l is a normal number on both forward paths (max-subtracted: l >= 1; constant shift: l > 2^-118): no special cases
-      float dp[BW_SEL];
-#pragma unroll
-      for (int j = 0; j < BW_SEL; ++j) dp[j] = wgt * nx_dp[j];
-
-      long long c1 = BW_CLK();
-      pf[5] += c1 - c_end;                      // loop top: decode, prefetch issue, table rebuilds
-      BW_TR(1)
-      ptx::mbar_wait(bar_selfull(it), (it >> 1) & 1u);
-      ptx::tc_fence_after();
-      BW_TR(2)
-      pf[0] += BW_CLK() - c1;
-      c1 = BW_CLK();
-      float delta = 0.0f;
-      float psel[BW_SEL];                       // P of the selected planes' tokens (this row)
-      {
-        uint32_t sv[BW_SEL];
-        ptx::tmem_ld16(tm_sel(it) + lane_off, sv);
-        ptx::tmem_ld_wait();
+      // is too short to hide a DRAM round trip behind itself.
+      // Row prologue of unit `jt` from nx_*: m, the row's delta = sum_j P_sel[j] dP[j] (as nd = -delta / l) and dS of the selected
+      // planes' tokens = P (dP - delta), packed: 8 registers live across the dense pass instead of 32.  LR: for the next unit
+      // it runs inside the last chunk of this unit's dense pass (its S_sel went out a unit ahead: loaded before chunk 2), where
+      // the TMEM round trip, 16 exponentials and dependent sums (~0.6 k cycles at the top of a unit with the MUFU pipe idle)
+      // fill issue slots; at the top only for the first unit and after an image / layer change (masks and weight change:
+      // what was computed ahead is dropped).
+      auto prologue_load = [&](uint32_t jt, uint32_t (&sv)[BW_SEL]) {
+        ptx::mbar_wait(bar_selfull(jt), (jt >> 1) & 1u);
+        ptx::tc_fence_after();
+        ptx::tmem_ld16(tm_sel(jt) + lane_off, sv);
+      };
+      // plain arithmetic (no volatile asm): the compiler may interleave it with the exponentials of a dense chunk
+      auto prologue_math = [&](const uint32_t (&sv)[BW_SEL], float w, float& m_o, float& nd_o, uint32_t (&pv_o)[BW_SEL / 2]) {
+        const float mm = nx_ml.x, inv_l = ptx::rcp_approx(nx_ml.y);      // l is a normal number on both forward paths (max-subtracted: l >= 1; constant shift: l > 2^-118): no special cases
+        float psel[BW_SEL], dp[BW_SEL];           // P and weighted upstream gradient of the selected planes' tokens (this row)
         float dl[4] = {0.0f, 0.0f, 0.0f, 0.0f};     // four chains instead of one 16-deep dependent FFMA chain
 #pragma unroll
         for (int j = 0; j < BW_SEL; ++j) {
-          psel[j] = ((valid_mask >> j) & 1u) ? ptx::ex2(__uint_as_float(sv[j]) - m) * inv_l : 0.0f;
+          dp[j] = w * nx_dp[j];
+          psel[j] = ((valid_mask >> j) & 1u) ? ptx::ex2(__uint_as_float(sv[j]) - mm) * inv_l : 0.0f;
           dl[j & 3] = fmaf(psel[j], dp[j], dl[j & 3]);
         }
-        delta = (dl[0] + dl[1]) + (dl[2] + dl[3]);
-      }
-      // dS of the selected planes' tokens = P (dP - delta), packed now: 8 registers live across the dense pass instead of 32
-      uint32_t pv[BW_SEL / 2];
+        const float delta = (dl[0] + dl[1]) + (dl[2] + dl[3]);
 #pragma unroll
-      for (int j = 0; j < BW_SEL / 2; ++j) {
-        const __nv_bfloat162 h2 = __floats2bfloat162_rn(psel[2 * j] * (dp[2 * j] - delta), psel[2 * j + 1] * (dp[2 * j + 1] - delta));
-        pv[j] = *reinterpret_cast<const uint32_t*>(&h2);
+        for (int j = 0; j < BW_SEL / 2; ++j) {
+          const __nv_bfloat162 h2 = __floats2bfloat162_rn(psel[2 * j] * (dp[2 * j] - delta), psel[2 * j + 1] * (dp[2 * j + 1] - delta));
+          pv_o[j] = *reinterpret_cast<const uint32_t*>(&h2);
+        }
+        m_o = mm;
+        nd_o = -delta * inv_l;
+      };
+      long long c1 = BW_CLK();
+      pf[5] += c1 - c_end;                      // loop top: decode, prefetch issue, table rebuilds
+      BW_TR(1)
+      if (!have_row) {
+        uint32_t sv[BW_SEL];
+        prologue_load(it, sv);
+        ptx::tmem_ld_wait();
+        prologue_math(sv, wgt, m, nd, pv);
       }
+      BW_TR(2)
+      pf[0] += BW_CLK() - c1;
+      c1 = BW_CLK();
       // ---- dS = P * (dP - delta): dense part -P*delta for my 128 columns, then the n_idx corrections
-      const float nd = -delta * inv_l;
       BW_TR(3)
       {
         long long c2 = BW_CLK();
@@ -705,12 +716,18 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         pf[0] += c3 - c2;
         c1 += c3 - c2;                          // the dS slot of the profile excludes this wait
       }
+      constexpr bool AHEAD = LR && !WIDE;       // the next unit's row prologue runs inside this unit's last dense chunk
+      float m_n = 0.0f, nd_n = 0.0f;
+      uint32_t pv_n[BW_SEL / 2];
       {
         // LR: the thread's whole row segment of S goes to registers at once and the accumulator is handed back (s_free): the
         // S product of the next unit then runs under this unit's entire dS pass instead of under its last chunk (with two
         // 32-column buffers the softmax warps waited 0.6 - 2 k cycles per unit for S once their loop top was out of the way)
         constexpr int NBUF = LR ? NCHUNK : 2;
         uint32_t v[NBUF][32];
+        uint32_t sv_n[BW_SEL];
+#pragma unroll
+        for (int j = 0; j < BW_SEL; ++j) sv_n[j] = 0u;
         // LR: the first HOLD chunks of dS stay packed in registers until the previous unit's dz product has retired
         // (it still reads the single dS tile): the exponentials of those chunks run under that product
         constexpr int HOLD = LR ? (BW_LR_HOLD < NCHUNK ? BW_LR_HOLD : NCHUNK) : 1;
@@ -740,8 +757,16 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
             ptx::tmem_ld_wait();
             if (c < NCHUNK - 1) ptx::tmem_ld32(tm_S + lane_off + col0 + 32 * (c + 1), v[(c + 1) & 1]);
           }
-          if (32 * (c + 1) <= ncol) {
-            // all 32 columns of the chunk are tokens (all but the chunk holding T's end): no per-column range test
+          if (AHEAD && c == NCHUNK - 2 && u + 1 < u_end) prologue_load(it + 1, sv_n);
+          if (AHEAD && c == NCHUNK - 1) {
+            ptx::tmem_ld_wait();
+            prologue_math(sv_n, wgt, m_n, nd_n, pv_n);
+          }
+          if ((LR && !WIDE) || 32 * (c + 1) <= ncol) {
+            // all 32 columns of the chunk are tokens (all but the chunk holding T's end): no per-column range test.
+            // LR: none at all -- columns past T hold logits of zero-filled window rows, their dS only reaches the dz rows of
+            // those non-existent tokens (M dimension of the product), which the flush's tensor map clips
+            // (the staged path sums over tokens in dQ', the WIDE flush writes rows itself: both need the zeros)
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
               const float e0 = ptx::ex2(__uint_as_float(v[c % NBUF][2 * j]) - m) * nd;
@@ -990,6 +1015,14 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
           }
         }
         ptx::tc_fence_before();
+      }
+      // hand over the row prologue computed ahead (dropped when the next unit changes image or layer: its masks / weight differ)
+      have_row = AHEAD && u + 1 < u_end && nxu.b == x.b && nxu.l == x.l;
+      if (have_row) {
+        m = m_n;
+        nd = nd_n;
+#pragma unroll
+        for (int j = 0; j < BW_SEL / 2; ++j) pv[j] = pv_n[j];
       }
     }
     if (P.prof && blockIdx.x == ((BW_DBG(P) >> 6) & 1) && stid == 0) {
