@@ -259,7 +259,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
   const uint32_t base = (raw + 1023u) & ~1023u;
   uint8_t* base_ptr = smem_raw + (base - raw);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp-uniform for the compiler
   const int half = blockIdx.x % NH, chunk = blockIdx.x / NH;
   const int u_begin = static_cast<int>(static_cast<int64_t>(chunk) * P.n_units / P.n_chunks);
   const int u_end = static_cast<int>(static_cast<int64_t>(chunk + 1) * P.n_units / P.n_chunks);
@@ -317,13 +317,13 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       const uint32_t id_dq = bw_idesc(TC_BM, d, 0, 1);
       const int nkt = (ntok + 15) / 16;
       for (int k = 0; k < nkt; ++k)
-        ptx::umma_bf16(tm_dQ, bw_desc(dsb + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024), bw_desc(ks + k * 2048, 16384, 1024),
+        ptx::umma_bf16_elect(tm_dQ, bw_desc(dsb + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024), bw_desc(ks + k * 2048, 16384, 1024),
                        id_dq, k != 0);
       // dK (128 tok x d per half) += dS^T (MN-major A: rows = pixels) * Q'_hi (MN-major B: rows = pixels)
       const uint32_t id_dk = bw_idesc(128, d, 1, 1);
       for (int mh = 0; mh < n_mh; ++mh)
         for (int k = 0; k < TC_BM / 16; ++k)
-          ptx::umma_bf16(tm_dK + mh * 64, bw_desc(dsb + mh * 2 * 16384 + k * 2048, 16384, 1024),
+          ptx::umma_bf16_elect(tm_dK + mh * 64, bw_desc(dsb + mh * 2 * 16384 + k * 2048, 16384, 1024),
                          bw_desc(qs + k * 2048, 16384, 1024), id_dk, (dk_fresh && k == 0) ? 0u : 1u);
     } else {
       // dz (128 tok x 64 taps per half) += dS^T (MN-major A: rows = pixels) * W_hi (MN-major B: rows = pixels; the
@@ -334,12 +334,12 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         const uint64_t a0 = bw_desc(dsb + mh * 2 * 16384, 16384, 1024);
 #pragma unroll
         for (int k = 0; k < TC_BM / 16; ++k)
-          ptx::umma_bf16(tm_dK + mh * 64, a0 + static_cast<uint64_t>(k * (2048 >> 4)), b0 + static_cast<uint64_t>(k * (2048 >> 4)), id_dz,
+          ptx::umma_bf16_elect(tm_dK + mh * 64, a0 + static_cast<uint64_t>(k * (2048 >> 4)), b0 + static_cast<uint64_t>(k * (2048 >> 4)), id_dz,
                          (dk_fresh && k == 0) ? 0u : 1u);
       }
     }
-    ptx::umma_commit(bar_mmadone);
-    ptx::umma_commit(bar_hiempty(it % HS));
+    ptx::umma_commit_elect(bar_mmadone);
+    ptx::umma_commit_elect(bar_hiempty(it % HS));
   };
 
   if (warp < BW_SOFTMAX_WARP0) {
@@ -403,8 +403,8 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
       }
     }
   } else if (warp == 1) {
-    // =========================== MMA issuer (one lane) =====================================
-    if (lane == 0) {
+    // =========================== MMA issuer: logit products (whole warp, elected issue) ========
+    {
       uint32_t it = 0;
       long long pf_q = 0, pf_ds = 0, pf_is = 0;      // profiler (SKP_BWD_DBG & 8), kept in registers
       BwUnit x = bw_decode(P, u_begin);
@@ -432,14 +432,14 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
             if (NPROD == 3) {
               const uint64_t a_lo = bw_desc(ql + ko(kk, TC_A_BYTES), 16, 1024);
               const uint64_t s_lo = bw_desc(ksel + SM::kKselHalf + ko(kk, BW_KSEL_BYTES), 16, 1024);
-              ptx::umma_bf16(tsel, a_hi, s_lo, id_sel, kk != 0);
-              ptx::umma_bf16(tsel, a_lo, s_hi, id_sel, 1u);
-              ptx::umma_bf16(tsel, a_hi, s_hi, id_sel, 1u);
+              ptx::umma_bf16_elect(tsel, a_hi, s_lo, id_sel, kk != 0);
+              ptx::umma_bf16_elect(tsel, a_lo, s_hi, id_sel, 1u);
+              ptx::umma_bf16_elect(tsel, a_hi, s_hi, id_sel, 1u);
             } else {
-              ptx::umma_bf16(tsel, a_hi, s_hi, id_sel, kk != 0);
+              ptx::umma_bf16_elect(tsel, a_hi, s_hi, id_sel, kk != 0);
             }
           }
-          ptx::umma_commit(selbar);
+          ptx::umma_commit_elect(selbar);
           pf_is += BW_CLK() - c0;
           return;
         }
@@ -450,15 +450,15 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
             if (NPROD == 3) {
               const uint64_t a_lo = bw_desc(ql + ko(kk, TC_A_BYTES), 16, 1024);
               const uint64_t b_lo = bw_desc(ks + SM::kKHalf + ko(kk, SM::kKBlock), 16, 1024);
-              ptx::umma_bf16(tm_S, a_hi, b_lo, id_S, kk != 0);
-              ptx::umma_bf16(tm_S, a_lo, b_hi, id_S, 1u);
-              ptx::umma_bf16(tm_S, a_hi, b_hi, id_S, 1u);
+              ptx::umma_bf16_elect(tm_S, a_hi, b_lo, id_S, kk != 0);
+              ptx::umma_bf16_elect(tm_S, a_lo, b_hi, id_S, 1u);
+              ptx::umma_bf16_elect(tm_S, a_hi, b_hi, id_S, 1u);
             } else {
-              ptx::umma_bf16(tm_S, a_hi, b_hi, id_S, kk != 0);
+              ptx::umma_bf16_elect(tm_S, a_hi, b_hi, id_S, kk != 0);
             }
           }
-          ptx::umma_commit(bar_sfull);
-          ptx::umma_commit(bar_loempty(jt % LS));
+          ptx::umma_commit_elect(bar_sfull);
+          ptx::umma_commit_elect(bar_loempty(jt % LS));
           pf_is += BW_CLK() - c0;
           return;
         }
@@ -479,28 +479,28 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
             const uint64_t p_lo = bw_desc(ql + k0 * 32, 16, 1024), r_lo = bw_desc(ql + k1 * 32, 16, 1024);
             const uint64_t s0_lo = bw_desc(ksel + SM::kKselHalf + k0 * 32, 16, 1024);
             const uint64_t s1_lo = bw_desc(ksel + SM::kKselHalf + k1 * 32, 16, 1024);
-            ptx::umma_bf16(tm_S, a_hi, b_lo, id_S, kk != 0);
+            ptx::umma_bf16_elect(tm_S, a_hi, b_lo, id_S, kk != 0);
             if (sel0) {
-              ptx::umma_bf16(tsel, p_hi, s0_lo, id_sel, kk != 0);
-              ptx::umma_bf16(tsel, p_lo, s0_hi, id_sel, 1u);
+              ptx::umma_bf16_elect(tsel, p_hi, s0_lo, id_sel, kk != 0);
+              ptx::umma_bf16_elect(tsel, p_lo, s0_hi, id_sel, 1u);
             }
-            ptx::umma_bf16(tm_S, a_lo, b_hi, id_S, 1u);
-            if (sel0) ptx::umma_bf16(tsel, p_hi, s0_hi, id_sel, 1u);
-            if (sel1) ptx::umma_bf16(tsel, r_hi, s1_lo, id_sel, 1u);
-            ptx::umma_bf16(tm_S, a_hi, b_hi, id_S, 1u);
+            ptx::umma_bf16_elect(tm_S, a_lo, b_hi, id_S, 1u);
+            if (sel0) ptx::umma_bf16_elect(tsel, p_hi, s0_hi, id_sel, 1u);
+            if (sel1) ptx::umma_bf16_elect(tsel, r_hi, s1_lo, id_sel, 1u);
+            ptx::umma_bf16_elect(tm_S, a_hi, b_hi, id_S, 1u);
             if (sel1) {
-              ptx::umma_bf16(tsel, r_lo, s1_hi, id_sel, 1u);
-              ptx::umma_bf16(tsel, r_hi, s1_hi, id_sel, 1u);
+              ptx::umma_bf16_elect(tsel, r_lo, s1_hi, id_sel, 1u);
+              ptx::umma_bf16_elect(tsel, r_hi, s1_hi, id_sel, 1u);
             }
           } else {
-            ptx::umma_bf16(tm_S, a_hi, b_hi, id_S, kk != 0);
-            if (sel0) ptx::umma_bf16(tsel, p_hi, s0_hi, id_sel, kk != 0);
-            if (sel1) ptx::umma_bf16(tsel, r_hi, s1_hi, id_sel, 1u);
+            ptx::umma_bf16_elect(tm_S, a_hi, b_hi, id_S, kk != 0);
+            if (sel0) ptx::umma_bf16_elect(tsel, p_hi, s0_hi, id_sel, kk != 0);
+            if (sel1) ptx::umma_bf16_elect(tsel, r_hi, s1_hi, id_sel, 1u);
           }
-          if (kk + 1 == n_selblk) ptx::umma_commit(selbar);
+          if (kk + 1 == n_selblk) ptx::umma_commit_elect(selbar);
         }
-        ptx::umma_commit(bar_sfull);
-        ptx::umma_commit(bar_loempty(jt % LS));
+        ptx::umma_commit_elect(bar_sfull);
+        ptx::umma_commit_elect(bar_loempty(jt % LS));
         pf_is += BW_CLK() - c0;
       };
       // LR: two issuing threads.  This one: the logit products S / S_sel; lane 0 of warp 2: the dz product that consumes dS.
@@ -553,13 +553,13 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         }
         x = nxu;
       }
-      if (P.prof && blockIdx.x == ((BW_DBG(P) >> 6) & 1)) {
+      if (P.prof && lane == 0 && blockIdx.x == ((BW_DBG(P) >> 6) & 1)) {
         P.prof[0] = pf_q; P.prof[1] = pf_ds; P.prof[8] = pf_is;
       }
     }
   } else if (warp == 2) {
-    // =========================== LR: MMA issuer of the dz product (one lane) =================
-    if (LR && lane == 0) {
+    // =========================== LR: MMA issuer of the dz product (whole warp, elected issue) ==
+    if (LR) {
       uint32_t it = 0;
       bool dk_fresh = true;
       BwUnit x = bw_decode(P, u_begin);

@@ -137,6 +137,21 @@ __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
+// Warp-uniform issue: the whole (converged) warp runs the role's control flow and address arithmetic -- the compiler then keeps
+// descriptors in uniform registers and emits UTCHMMA back to back -- and one elected lane (always the same one) executes the
+// instruction.  A role written as `if (lane == 0) { ... }` gets an ELECT / 5 x R2UR / branch "waterfall" around every MMA (~100
+// cycles per instruction for the issuing thread: more than an N <= 128 MMA takes on the tensor pipe).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+__device__ __forceinline__ void umma_bf16_elect(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  if (elect_one()) umma_bf16(d_tmem, a_desc, b_desc, idesc, accumulate);
+}
+__device__ __forceinline__ void umma_commit_elect(uint32_t bar) {
+  if (elect_one()) umma_commit(bar);
+}
 
 // K-major, SWIZZLE_128B shared-memory matrix descriptor (rows of 64 bf16 = 128 B, 8-row atoms of
 // 1024 B).  Bit layout per cute::UMMA::SmemDescriptor: start>>4 [0,14), LBO>>4 [16,30),
