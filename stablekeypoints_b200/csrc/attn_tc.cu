@@ -262,7 +262,10 @@ __device__ __forceinline__ float exp2_poly(float x) {
 constexpr int FW_SOFTMAX_WARP0 = 4;
 constexpr int FW_QCOLS = 64;                                  // tokens per softmax thread
 constexpr int FW_MAX_PARTS = 8;                               // 64-token column parts of a cluster (2 x 4 or 4 x 2)
-constexpr int FW_NH = 1;                                      // column groups a TMEM buffer is handed over in (1 or 2)
+#ifndef SKP_FW_NH
+#define SKP_FW_NH 1
+#endif
+constexpr int FW_NH = SKP_FW_NH;                                      // column groups a TMEM buffer is handed over in (1 or 2)
 // LR: with [lo, hi] the range of the native-resolution logits of a unit's (image, head), every upsampled logit lies within
 // c +- 0.945 (hi - lo), c = (hi + lo) / 2.  When that half-width is <= FW_FAST_HALFWIDTH (log2 units), exp2(S - c) can
 // neither overflow (512 x 2^118 < 2^128) nor flush a single term (2^-118 is a normal float): the softmax is shift
@@ -294,6 +297,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
   if (base - raw > static_cast<uint32_t>(SM::kSlack)) __trap();
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp_u = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // the same value, warp-uniform for the compiler (MMA role)
   const uint32_t cta_rank = NSPLIT > 1 ? ptx::cluster_ctarank() : 0u;
   const int tile = blockIdx.x / NSPLIT;
   const int b = blockIdx.y;
@@ -412,13 +416,13 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
         }
       }
     }
-  } else if (warp == 1) {
-    // =========================== MMA issuer (one lane) =====================================
-    if (lane == 0) {
+  } else if (warp_u == 1) {
+    // =========================== MMA issuer (whole warp, elected issue: ptx::umma_bf16_elect) ==
+    {
       // FW_NH = 2 hands each buffer over as two N = 128 column halves with their own barriers (two softmax
-      // groups half a unit out of phase).  Measured on B200: an SS-mode M=128 K=16 MMA costs ~130 cycles
-      // whether N is 128 or 256 (the A tile is re-read from shared memory each time), so halving N doubles
-      // the tensor time per unit (3400 vs 1700 cycles) and the stagger buys nothing: one N = 256 hand-over.
+      // groups half a unit out of phase).  Round 1 measured ~130 cycles per MMA whether N was 128 or 256 and blamed
+      // the tensor pipe; scripts/mma_small_probe.cu says 64 vs 128 cycles -- the 130 were the single-lane issuer's
+      // ELECT / R2UR waterfall around every instruction, gone with the warp-uniform issue below.
       constexpr uint32_t idesc = ptx::umma_idesc_bf16(TC_BM, TC_BNk / FW_NH);
       constexpr uint32_t kHalfB = (TC_BNk / FW_NH) * 128;     // byte offset of the second group's first token row in a K tile
       uint32_t it = 0, u = 0, a_cnt = 0;
@@ -474,16 +478,16 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
                 if (NPROD == 3) {
                   const uint64_t a_lo = ptx::umma_desc_sw128(a_lo_s + kk * 32);
                   const uint64_t b_lo = ptx::umma_desc_sw128(b_lo_s + hf * kHalfB + kk * 32);
-                  ptx::umma_bf16(d_tmem, a_hi, b_lo, idesc, first);
-                  ptx::umma_bf16(d_tmem, a_lo, b_hi, idesc, 1u);
-                  ptx::umma_bf16(d_tmem, a_hi, b_hi, idesc, 1u);
+                  ptx::umma_bf16_elect(d_tmem, a_hi, b_lo, idesc, first);
+                  ptx::umma_bf16_elect(d_tmem, a_lo, b_hi, idesc, 1u);
+                  ptx::umma_bf16_elect(d_tmem, a_hi, b_hi, idesc, 1u);
                 } else {
-                  ptx::umma_bf16(d_tmem, a_hi, b_hi, idesc, first);
+                  ptx::umma_bf16_elect(d_tmem, a_hi, b_hi, idesc, first);
                 }
               }
-              if (kb == nkb - 1) ptx::umma_commit(bar_tfull(buf, hf));   // this half's logits are in TMEM
+              if (kb == nkb - 1) ptx::umma_commit_elect(bar_tfull(buf, hf));   // this half's logits are in TMEM
             }
-            ptx::umma_commit(bar_empty(s));      // smem slot free once these MMAs retire
+            ptx::umma_commit_elect(bar_empty(s));      // smem slot free once these MMAs retire
 #ifdef SKP_FWD_PROF
             mp_issue += clock64() - mp_t;
 #endif
@@ -491,7 +495,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
         }
       }
 #ifdef SKP_FWD_PROF
-      if (blockIdx.x < 2 && blockIdx.y == 0)
+      if (blockIdx.x < 2 && blockIdx.y == 0 && lane == 0)
         printf("cta %d mma thread: per unit: wait operands %lld, wait tempty %lld, issue %lld, total %lld\n", blockIdx.x,
                mp_full / u, mp_tempty / u, mp_issue / u, (clock64() - mp_t0) / u);
 #endif
