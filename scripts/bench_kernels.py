@@ -32,6 +32,13 @@ def run():
     (sel * w).sum().backward()
 
 
+if os.environ.get("BK_SELECT"):        # mode C only (extraction): forward restricted to 10 token ids shared by all images
+    ids = idx[0].contiguous()
+
+    def run():
+        with torch.no_grad():
+            ops.attention_maps([q.detach() for q in qs], [k.detach() for k in ks], heads, sc, 128, token_idx=ids, precision=prec)
+
 for _ in range(3):
     run()
 _lib.timing_start()

@@ -523,6 +523,32 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
 #pragma unroll
     for (int j = 0; j < (SELECT ? TC_MAX_SEL : FW_QCOLS); ++j) acc[j] = 0.0f;
 
+    // SELECT (extraction: only the K selected tokens are accumulated): the selected tokens of MY 64 columns as a compact,
+    // warp-uniform list (at most 16, ~1.25 on average: 10 tokens over 8 column parts) -- TMEM column and output plane of
+    // entry k packed 8 / 4 bits apiece, so every per-unit loop below runs over static k with a predicate `k < n_mine`
+    // instead of sixteen range tests on shared-memory token ids.  Their exponentials are computed from single-column loads
+    // of the LOGITS during pass B and stay in registers until the unit's statistics arrive: nothing is parked in TMEM (no
+    // tcgen05.st, no pass-C load) and the buffer is handed back right after pass B's loads.  (Mode C used to be SLOWER than
+    // mode A: 2.95 vs 2.45 ms per 8 images.)
+    uint32_t n_mine = 0;
+    unsigned long long my_cols[2] = {0ull, 0ull}, my_planes = 0ull;
+    if (SELECT) {
+#pragma unroll
+      for (int j = 0; j < TC_MAX_SEL; ++j) {
+        const int t = tok_s[j] - tok0 - col0;
+        if (j < P.n_idx && t >= 0 && t < ncol) {
+          if (n_mine < 8) my_cols[0] |= static_cast<unsigned long long>(t) << (8 * n_mine);
+          else my_cols[1] |= static_cast<unsigned long long>(t) << (8 * (n_mine - 8));
+          my_planes |= static_cast<unsigned long long>(j) << (4 * n_mine);
+          ++n_mine;
+        }
+      }
+    }
+    auto my_col = [&](int k) { return static_cast<uint32_t>(my_cols[k >> 3] >> (8 * (k & 7))) & 0xffu; };
+    float e_sel[SELECT ? TC_MAX_SEL : 1];      // of the unit whose pass B ran last = the unit the next pass C normalises
+#pragma unroll
+    for (int k = 0; k < (SELECT ? TC_MAX_SEL : 1); ++k) e_sel[k] = 0.0f;
+
     // normalise + accumulate unit uu, whose exponentials this thread parked in TMEM one iteration ago
     FW_PROF_DECL
     auto pass_c = [&](uint32_t uu, float m_own, float wgt_u, bool fast_uu) {
@@ -570,22 +596,19 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
           }
         }
       } else {
-        // all single-column loads go out before ONE wait (a wait per load serialised up to n_idx TMEM round trips:
-        // 4.23 -> 3.79 ms per 10-image extraction launch).  Keeping the selected exponentials in registers instead
-        // and releasing the buffer after pass B was measured slower (4.34 ms).
-        uint32_t ev[TC_MAX_SEL];
+        // the selected tokens' exponentials of unit uu are in registers (pass B): no TMEM access, no buffer to release
 #pragma unroll
-        for (int j = 0; j < TC_MAX_SEL; ++j) {
-          const int t = tok_s[j] - tok0 - col0;   // warp-uniform
-          ev[j] = 0u;
-          if (j < P.n_idx && t >= 0 && t < ncol) ev[j] = ptx::tmem_ld1(taddr + t);
+        for (int g = 0; g < TC_MAX_SEL; g += 4) {
+          if (static_cast<uint32_t>(g) < n_mine) {
+#pragma unroll
+            for (int k = g; k < g + 4; ++k) acc[k] = fmaf(cf, e_sel[k], acc[k]);
+          }
         }
-        ptx::tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < TC_MAX_SEL; ++j) acc[j] = fmaf(cf, __uint_as_float(ev[j]), acc[j]);
       }
-      ptx::tc_fence_before();
-      ptx::mbar_arrive(bar_tempty(buf, hf));
+      if (!SELECT) {
+        ptx::tc_fence_before();
+        ptx::mbar_arrive(bar_tempty(buf, hf));
+      }
     };
 
     uint32_t u = 0;
@@ -636,12 +659,31 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
         if (u > 0) pass_c(u - 1, m_prev, wgt_prev, fast_prev);
         // ---- pass B: exponentials (parked back in TMEM) and their sum
         float s0 = 0.0f, s1 = 0.0f, s2 = 0.0f, s3 = 0.0f;
+        uint32_t sv_sel[SELECT ? TC_MAX_SEL : 1];
+        if (SELECT) {
+          // logits of my selected tokens: predicated single-column loads, in flight together with the first chunk's load
+          // (groups of four under one warp-uniform branch: a thread rarely owns more than four of the tokens)
+#pragma unroll
+          for (int g = 0; g < TC_MAX_SEL; g += 4) {
+#pragma unroll
+            for (int k = g; k < g + 4; ++k) sv_sel[k] = 0xff800000u;             // -inf: exp2 = 0 for the entries past n_mine
+            if (static_cast<uint32_t>(g) < n_mine) {
+#pragma unroll
+              for (int k = g; k < g + 4; ++k) ptx::tmem_ld1_if(sv_sel[k], taddr + my_col(k), static_cast<uint32_t>(k) < n_mine);
+            }
+          }
+        }
 #pragma unroll
         for (int c = 0; c < NCH; ++c) {
           if (32 * c < ncol) {
             uint32_t v[32];
             ptx::tmem_ld32(taddr + 32 * c, v);
             ptx::tmem_ld_wait();
+            if (SELECT && (c == NCH - 1 || 32 * (c + 1) >= ncol)) {
+              // my columns of the logits are in registers: the tensor pipe may reuse the buffer (unit u + 2)
+              ptx::tc_fence_before();
+              ptx::mbar_arrive(bar_tempty(buf, hf));
+            }
             FW_PROF(7)
             if (ncol >= 32 * (c + 1)) {
 #pragma unroll
@@ -662,11 +704,25 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
               }
             }
             FW_PROF(8)
-            ptx::tmem_st32(taddr + 32 * c, v);
+            if (!SELECT) ptx::tmem_st32(taddr + 32 * c, v);
           }
         }
         const float sum = (s0 + s1) + (s2 + s3);
-        ptx::tmem_st_wait();
+        if (!SELECT) ptx::tmem_st_wait();
+        if (SELECT) {
+          if (ncol <= 0) {                       // no columns of mine: nothing was loaded, release here
+            ptx::tmem_ld_wait();
+            ptx::tc_fence_before();
+            ptx::mbar_arrive(bar_tempty(buf, hf));
+          }
+#pragma unroll
+          for (int g = 0; g < TC_MAX_SEL; g += 4) {
+            if (static_cast<uint32_t>(g) < n_mine) {
+#pragma unroll
+              for (int k = g; k < g + 4; ++k) e_sel[k] = ptx::ex2(__uint_as_float(sv_sel[k]) - m);
+            }
+          }
+        }
         FW_PROF(9)
         // ---- post (max, sum) to every column part of the cluster.  Local slot: plain store + arrive.
         // Remote slot: st.async, which completes bytes on the peer's mbarrier itself (no cluster-scope
@@ -706,9 +762,9 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
         if (j < ncol) out[static_cast<int64_t>(j) * P.R2] = acc[j];
     } else {
 #pragma unroll
-      for (int j = 0; j < TC_MAX_SEL; ++j) {
-        const int t = tok_s[j] - tok0 - col0;
-        if (j < P.n_idx && t >= 0 && t < ncol) P.maps[(static_cast<int64_t>(b) * P.n_idx + j) * P.R2 + p0 + row] = acc[j];
+      for (int k = 0; k < TC_MAX_SEL; ++k) {
+        const int j = static_cast<int>(my_planes >> (4 * k)) & 15;
+        if (static_cast<uint32_t>(k) < n_mine) P.maps[(static_cast<int64_t>(b) * P.n_idx + j) * P.R2 + p0 + row] = acc[k];
       }
     }
   }

@@ -246,6 +246,12 @@ __device__ __forceinline__ uint32_t tmem_ld1(uint32_t taddr) {
   return v;
 }
 
+// ... predicated (the predicate must be warp-uniform: the instruction is .sync.aligned); v keeps its value when it is off
+__device__ __forceinline__ void tmem_ld1_if(uint32_t& v, uint32_t taddr, bool on) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\t@p tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];\n\t}"
+               : "+r"(v) : "r"(taddr), "r"(static_cast<uint32_t>(on)) : "memory");
+}
+
 // warpgroup-wide register re-allocation (all 4 warps of the warpgroup must execute it)
 template <int N>
 __device__ __forceinline__ void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
