@@ -198,16 +198,18 @@ struct TcSmem {
   static constexpr int kRingOff = kAResident;
   static constexpr int kTiles = kAResident + kStages * kStageBytes;    // 192 KB (BN = 256); 64 / 96 KB (BN = 128)
   static constexpr int kBarOff = kTiles;                               // full[], empty[], tfull[2][2], tempty[2][2], xfull[2], afull
-  static constexpr int kNumBars = 2 * kStages + 11;
+  static constexpr int kStatBufs = BN == 128 ? 2 : 4;                  // ring of row-statistics slots / xfull barriers (see FW lag below)
+  static constexpr int kNumBars = 2 * kStages + 9 + kStatBufs;
   static constexpr int kTmemPtrOff = kBarOff + 8 * kNumBars;
   static constexpr int kTokOff = kTmemPtrOff + 8;                      // int tok[TC_MAX_SEL]
   static constexpr int kAmaxOff = kTokOff + 4 * TC_MAX_SEL;            // float amax[FW_MAX_UNITS]: max |s_low| of every unit's (image, head)
-  static constexpr int kStatsOff = kAmaxOff + 4 * 128;                 // float2 stats[2 buf][8 part][128 row]
-  static constexpr int kTotal = kStatsOff + 2 * 8 * TC_BM * 8;
+  static constexpr int kStatsOff = kAmaxOff + 4 * 128;                 // float2 stats[kStatBufs][8 part][128 row]
+  static constexpr int kTotal = kStatsOff + kStatBufs * 8 * TC_BM * 8;
   // slack for the manual 1024 B alignment of the tiles.  Two CTAs per SM leave 115712 B each: the BN = 128 / LR layout
   // (115440 B) keeps 256 B of slack -- the dynamic window starts 1 KB-aligned on sm_100 and the kernel traps if not
   static constexpr int kSlack = (BN == 128 && LR) ? 256 : 1024;
   static constexpr int kDynamic = kTotal + kSlack;
+  static_assert(kDynamic <= 232448, "over the 227 KB of dynamic shared memory per CTA");
 };
 
 // Phase profiler of the softmax warps (diagnostic builds only: nvcc -DSKP_FWD_PROF): cycles per phase averaged
@@ -309,8 +311,8 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
   // TMEM buffers are handed over in column halves: tfull/tempty[buffer][half]
   auto bar_tfull = [&](int i, int hf) { return base + SM::kBarOff + 8u * (2 * SM::kStages + 2 * i + hf); };
   auto bar_tempty = [&](int i, int hf) { return base + SM::kBarOff + 8u * (2 * SM::kStages + 4 + 2 * i + hf); };
-  auto bar_xfull = [&](int i) { return base + SM::kBarOff + 8u * (2 * SM::kStages + 8 + i); };
-  const uint32_t bar_afull = base + SM::kBarOff + 8u * (2 * SM::kStages + 10);
+  const uint32_t bar_afull = base + SM::kBarOff + 8u * (2 * SM::kStages + 8);
+  auto bar_xfull = [&](int i) { return base + SM::kBarOff + 8u * (2 * SM::kStages + 9 + i); };
   volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(base_ptr + SM::kTmemPtrOff);
   int* tok_s = reinterpret_cast<int*>(base_ptr + SM::kTokOff);
   float* amax_s = reinterpret_cast<float*>(base_ptr + SM::kAmaxOff);
@@ -327,8 +329,8 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
         ptx::mbar_init(bar_tfull(i, hf), 1);
         ptx::mbar_init(bar_tempty(i, hf), FW_SOFTMAX_THREADS / FW_NH);
       }
-      ptx::mbar_init(bar_xfull(i), FW_SOFTMAX_THREADS);
     }
+    for (int i = 0; i < SM::kStatBufs; ++i) ptx::mbar_init(bar_xfull(i), FW_SOFTMAX_THREADS);
     ptx::mbar_init(bar_afull, 1);
     ptx::fence_barrier_init();
   }
@@ -549,19 +551,28 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
 #pragma unroll
     for (int k = 0; k < (SELECT ? TC_MAX_SEL : 1); ++k) e_sel[k] = 0.0f;
 
-    // normalise + accumulate unit uu, whose exponentials this thread parked in TMEM one iteration ago
+    // Units between a unit's pass B and its normalisation (pass C).  1: the exponentials wait in TMEM, two buffers.  SELECT keeps
+    // them in registers, so it can afford 2: a unit's statistics are then one whole unit old when they are needed and the 32
+    // softmax warps of the cluster stop meeting at that barrier every unit (with lag 1 every warp's pass C waits for the
+    // slowest warp's pass B of the same unit: lockstep, the MUFU pipe idle outside pass B).  A statistics slot may be
+    // overwritten (remote st.async of unit u) once every reader is past unit u - XB: XB >= 2 * lag.
+    constexpr int XLAG = (SELECT && BN == TC_BN) ? 2 : 1;
+    constexpr int XB = 2 * XLAG;
+    static_assert(XB <= SM::kStatBufs, "statistics ring");
+    // normalise + accumulate unit uu, whose exponentials this thread parked in TMEM one iteration ago (SELECT: holds in e_u)
     FW_PROF_DECL
-    auto pass_c = [&](uint32_t uu, float m_own, float wgt_u, bool fast_uu) {
-      const uint32_t buf = uu & 1u, par = (uu >> 1) & 1u;
+    auto pass_c = [&](uint32_t uu, float m_own, float wgt_u, bool fast_uu, const float (&e_u)[SELECT ? TC_MAX_SEL : 1]) {
+      const uint32_t buf = uu & 1u;
+      const uint32_t xb = uu % XB, par = (uu / XB) & 1u;
       const uint32_t taddr = t_lane + buf * TC_BNk + col0;
-      ptx::mbar_wait_hint(bar_xfull(buf), par, 500u);
+      ptx::mbar_wait_hint(bar_xfull(xb), par, 500u);
       FW_PROF(3)
       float mg = m_own, total = 0.0f;
       if (fast_uu) {
         // every part posted (the unit's constant m, sum exp2(S - m)): the row's statistics are the plain sum
         float tq[NPART];
 #pragma unroll
-        for (int q = 0; q < NPART; ++q) tq[q] = stats[(buf * FW_MAX_PARTS + q) * TC_BM + row].y;
+        for (int q = 0; q < NPART; ++q) tq[q] = stats[(xb * FW_MAX_PARTS + q) * TC_BM + row].y;
 #pragma unroll
         for (int st = 1; st < NPART; st <<= 1)
 #pragma unroll
@@ -570,10 +581,10 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
       } else {
         mg = -INFINITY;
 #pragma unroll
-        for (int q = 0; q < NPART; ++q) mg = fmaxf(mg, stats[(buf * FW_MAX_PARTS + q) * TC_BM + row].x);
+        for (int q = 0; q < NPART; ++q) mg = fmaxf(mg, stats[(xb * FW_MAX_PARTS + q) * TC_BM + row].x);
 #pragma unroll
         for (int q = 0; q < NPART; ++q) {
-          const float2 sq = stats[(buf * FW_MAX_PARTS + q) * TC_BM + row];
+          const float2 sq = stats[(xb * FW_MAX_PARTS + q) * TC_BM + row];
           total += sq.y * pow2_int(sq.x - mg);
         }
       }
@@ -601,7 +612,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
         for (int g = 0; g < TC_MAX_SEL; g += 4) {
           if (static_cast<uint32_t>(g) < n_mine) {
 #pragma unroll
-            for (int k = g; k < g + 4; ++k) acc[k] = fmaf(cf, e_sel[k], acc[k]);
+            for (int k = g; k < g + 4; ++k) acc[k] = fmaf(cf, e_u[k], acc[k]);
           }
         }
       }
@@ -612,8 +623,15 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
     };
 
     uint32_t u = 0;
-    float m_prev = 0.0f, wgt_prev = 0.0f;
-    bool fast_prev = false;
+    float m_h[XLAG], wgt_h[XLAG], e_h[XLAG][SELECT ? TC_MAX_SEL : 1];      // [0] = the previous unit, [1] = the one before
+    bool fast_h[XLAG];
+#pragma unroll
+    for (int d = 0; d < XLAG; ++d) {
+      m_h[d] = wgt_h[d] = 0.0f;
+      fast_h[d] = false;
+#pragma unroll
+      for (int k = 0; k < (SELECT ? TC_MAX_SEL : 1); ++k) e_h[d][k] = 0.0f;
+    }
     for (int l = 0; l < P.ops.n_layers; ++l) {
       const int h = P.ops.heads[l];
       const float wgt = P.ops.weight[l];
@@ -656,7 +674,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
         const float m = fast ? m_unit : ceilf(fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)));
         FW_PROF(2)
         // ---- pass C of the previous unit
-        if (u > 0) pass_c(u - 1, m_prev, wgt_prev, fast_prev);
+        if (u >= static_cast<uint32_t>(XLAG)) pass_c(u - XLAG, m_h[XLAG - 1], wgt_h[XLAG - 1], fast_h[XLAG - 1], e_h[XLAG - 1]);
         // ---- pass B: exponentials (parked back in TMEM) and their sum
         float s0 = 0.0f, s1 = 0.0f, s2 = 0.0f, s3 = 0.0f;
         uint32_t sv_sel[SELECT ? TC_MAX_SEL : 1];
@@ -728,22 +746,29 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
         // Remote slot: st.async, which completes bytes on the peer's mbarrier itself (no cluster-scope
         // release fence, no L1 invalidate on the waiter).
         {
-          const int sidx = (buf * FW_MAX_PARTS + part) * TC_BM + row;
+          const uint32_t xb = u % XB;
+          const int sidx = (xb * FW_MAX_PARTS + part) * TC_BM + row;
           stats[sidx] = make_float2(m, sum);
           if (NSPLIT > 1) {
             const uint32_t slot = base + SM::kStatsOff + sidx * 8;
 #pragma unroll
             for (uint32_t dst = 0; dst < static_cast<uint32_t>(NSPLIT); ++dst)
-              if (dst != cta_rank) ptx::st_async_v2(ptx::mapa(slot, dst), m, sum, ptx::mapa(bar_xfull(buf), dst));
-            if (warp == FW_SOFTMAX_WARP0 && lane == 0) ptx::mbar_arrive_expect_tx(bar_xfull(buf), (NSPLIT - 1) * FW_SOFTMAX_THREADS * 8);
-            else ptx::mbar_arrive(bar_xfull(buf));
+              if (dst != cta_rank) ptx::st_async_v2(ptx::mapa(slot, dst), m, sum, ptx::mapa(bar_xfull(xb), dst));
+            if (warp == FW_SOFTMAX_WARP0 && lane == 0) ptx::mbar_arrive_expect_tx(bar_xfull(xb), (NSPLIT - 1) * FW_SOFTMAX_THREADS * 8);
+            else ptx::mbar_arrive(bar_xfull(xb));
           } else {
-            ptx::mbar_arrive(bar_xfull(buf));
+            ptx::mbar_arrive(bar_xfull(xb));
           }
         }
-        m_prev = m;
-        wgt_prev = wgt;
-        fast_prev = fast;
+#pragma unroll
+        for (int d = XLAG - 1; d > 0; --d) {
+          m_h[d] = m_h[d - 1]; wgt_h[d] = wgt_h[d - 1]; fast_h[d] = fast_h[d - 1];
+#pragma unroll
+          for (int k = 0; k < (SELECT ? TC_MAX_SEL : 1); ++k) e_h[d][k] = e_h[d - 1][k];
+        }
+        m_h[0] = m; wgt_h[0] = wgt; fast_h[0] = fast;
+#pragma unroll
+        for (int k = 0; k < (SELECT ? TC_MAX_SEL : 1); ++k) e_h[0][k] = e_sel[k];
         FW_PROF(10)
       }
     }
@@ -753,7 +778,9 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
              blockIdx.x, warp, pf_acc[0] / u, pf_acc[1] / u, pf_acc[2] / u, pf_acc[3] / u, pf_acc[4] / u, pf_acc[5] / u, pf_acc[6] / u,
              pf_acc[7] / u, pf_acc[8] / u, pf_acc[9] / u, pf_acc[10] / u);
 #endif
-    if (u > 0) pass_c(u - 1, m_prev, wgt_prev, fast_prev);
+#pragma unroll
+    for (int d = XLAG; d >= 1; --d)
+      if (u >= static_cast<uint32_t>(d)) pass_c(u - d, m_h[d - 1], wgt_h[d - 1], fast_h[d - 1], e_h[d - 1]);
     // ---- write-out: lanes hold consecutive pixels -> 128 B coalesced stores per token
     if (!SELECT) {
       float* out = P.maps + (static_cast<int64_t>(b) * P.T + tok0 + col0) * P.R2 + p0 + row;

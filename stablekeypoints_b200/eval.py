@@ -277,7 +277,7 @@ def evaluate(
     from .optimize import _make_dataset
 
     world, rank = dist_.world_size(), dist_.rank()
-    dataset = _make_dataset(dataset_name, dataset_loc, dataset)
+    dataset = _make_dataset(dataset_name, dataset_loc, dataset, split="test")      # `eval.py:401-424`: the test split
     n = len(dataset)
     per = (n + world - 1) // world
     regressor = torch.as_tensor(regressor).to(device=device, dtype=torch.float32)

@@ -215,14 +215,14 @@ def token_opt_losses(ldm, image, transformed_img, context, transform, controller
     return per_image[:, 0].mean(), per_image[:, 1].mean(), idx
 
 
-def _make_dataset(dataset_name, dataset_loc, dataset=None, **kw):
+def _make_dataset(dataset_name, dataset_loc, dataset=None, split="train", max_len=-1, **kw):
+    """`dataset=` wins; else the name is resolved like the reference's stages do (`optimize.py:301-326`, `eval.py:401-424`)."""
     if dataset is not None:
         return dataset
+    from . import datasets as D
     if dataset_name == "synthetic":
-        from .datasets import SyntheticKeypoints
-        return SyntheticKeypoints(**kw)
-    # the reference's dataset classes (`optimize.py:301-326`) are outside the hot path: pass `dataset=`
-    raise NotImplementedError(f"dataset {dataset_name!r}: pass a torch Dataset via dataset= (sample dict with 'img')")
+        return D.SyntheticKeypoints(**kw)
+    return D.make_dataset(dataset_name, dataset_loc, split=split, max_len=max_len)
 
 
 def optimize_embedding(
@@ -274,7 +274,7 @@ def optimize_embedding(
     from . import distributed as dist_
     from . import ptp_utils
     world, rank = dist_.world_size(), dist_.rank()
-    dataset = _make_dataset(dataset_name, dataset_loc, dataset)
+    dataset = _make_dataset(dataset_name, dataset_loc, dataset, split="train", max_len=max_len)
     transform = RandomAffineWithInverse(degrees=augment_degrees, scale=augment_scale, translate=augment_translate)
     if context is None:
         dim = context_dim or getattr(getattr(ldm, "cfg", None), "context_dim", 768)
