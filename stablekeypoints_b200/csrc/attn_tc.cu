@@ -23,6 +23,10 @@
 
 #include "attn_tc.cuh"
 
+#ifndef SKP_FW_XLAG
+#define SKP_FW_XLAG 1          // 2: SELECT-mode statistics lag of two units (see XLAG in the kernel)
+#endif
+
 namespace skp {
 
 struct TcParams {
@@ -198,7 +202,7 @@ struct TcSmem {
   static constexpr int kRingOff = kAResident;
   static constexpr int kTiles = kAResident + kStages * kStageBytes;    // 192 KB (BN = 256); 64 / 96 KB (BN = 128)
   static constexpr int kBarOff = kTiles;                               // full[], empty[], tfull[2][2], tempty[2][2], xfull[2], afull
-  static constexpr int kStatBufs = BN == 128 ? 2 : 4;                  // ring of row-statistics slots / xfull barriers (see FW lag below)
+  static constexpr int kStatBufs = (BN == 128 || SKP_FW_XLAG < 2) ? 2 : 4;                  // ring of row-statistics slots / xfull barriers (see FW lag below)
   static constexpr int kNumBars = 2 * kStages + 9 + kStatBufs;
   static constexpr int kTmemPtrOff = kBarOff + 8 * kNumBars;
   static constexpr int kTokOff = kTmemPtrOff + 8;                      // int tok[TC_MAX_SEL]
@@ -556,7 +560,7 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
     // softmax warps of the cluster stop meeting at that barrier every unit (with lag 1 every warp's pass C waits for the
     // slowest warp's pass B of the same unit: lockstep, the MUFU pipe idle outside pass B).  A statistics slot may be
     // overwritten (remote st.async of unit u) once every reader is past unit u - XB: XB >= 2 * lag.
-    constexpr int XLAG = (SELECT && BN == TC_BN) ? 2 : 1;
+    constexpr int XLAG = (SELECT && BN == TC_BN) ? SKP_FW_XLAG : 1;
     constexpr int XB = 2 * XLAG;
     static_assert(XB <= SM::kStatBufs, "statistics ring");
     // normalise + accumulate unit uu, whose exponentials this thread parked in TMEM one iteration ago (SELECT: holds in e_u)
