@@ -14,10 +14,6 @@
 //                              epilogue (every output element is owned by one CTA)
 #include "attn_tc.cuh"
 
-#ifndef SKP_DZ_VEC
-#define SKP_DZ_VEC 0
-#endif
-
 namespace skp {
 
 constexpr int LGG_THREADS = 192;       // warp 0: TMA + MMA issue, warps 2-5: epilogue
@@ -42,29 +38,7 @@ struct LrGradGemmParams {
 // dz fp32 [z][T][s2] -> bf16 [z][T][s2] and bf16 [z][s2][Tp] (Tp = T padded to 8, pad columns zero)
 // (a hi + lo split of dz was measured: no change of the gradient error, which is set by the bf16 dS / W operands of the
 // main kernel, so dz is rounded once)
-__global__ void lr_dz_convert_kernel(const float* __restrict__ dz, int T, int s2, int Tp, __nv_bfloat16* __restrict__ out,
-                                     __nv_bfloat16* __restrict__ outT) {
-  __shared__ float tile[32][33];
-  const int z = blockIdx.z, t0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
-  const float* src = dz + static_cast<int64_t>(z) * T * s2;
-  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
-    const int t = t0 + r, c = c0 + threadIdx.x;
-    float v = 0.0f;
-    if (t < T && c < s2) {
-      v = src[static_cast<int64_t>(t) * s2 + c];
-      out[(static_cast<int64_t>(z) * T + t) * s2 + c] = __float2bfloat16_rn(v);
-    }
-    tile[r][threadIdx.x] = v;
-  }
-  __syncthreads();
-  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
-    const int c = c0 + r, t = t0 + threadIdx.x;
-    if (c < s2 && t < Tp) outT[(static_cast<int64_t>(z) * s2 + c) * Tp + t] = __float2bfloat16_rn(tile[threadIdx.x][r]);
-  }
-}
-
-// the same conversion with 16-byte loads / 8-byte stores (SKP_DZ_VEC)
-__global__ void __launch_bounds__(256) lr_dz_convert_vec_kernel(const float* __restrict__ dz, int T, int s2, int Tp, __nv_bfloat16* __restrict__ out,
+__global__ void __launch_bounds__(256) lr_dz_convert_kernel(const float* __restrict__ dz, int T, int s2, int Tp, __nv_bfloat16* __restrict__ out,
                                                             __nv_bfloat16* __restrict__ outT) {
   // 64 x 64 tile, 16 x 16 threads: 16-byte loads, 8-byte stores in both orientations (s2 and Tp are multiples of 4)
   __shared__ float tile[64][65];
@@ -244,11 +218,7 @@ int lr_bwd_post(const skp_attn_layer& a, int B, int T, const float* dz, char* ws
   __nv_bfloat16* kT = take(static_cast<size_t>(Bk) * a.C * Tp * 2);
   __nv_bfloat16* qT = take(static_cast<size_t>(B) * a.C * s2 * 2);
   const dim3 tb(32, 8);
-#if SKP_DZ_VEC
-  lr_dz_convert_vec_kernel<<<(::skp::note_launch(), dim3((s2 + 63) / 64, (Tp + 63) / 64, Z)), 256, 0, st>>>(dz, T, s2, Tp, dzb, dzT);
-#else
-  lr_dz_convert_kernel<<<(::skp::note_launch(), dim3((s2 + 31) / 32, (Tp + 31) / 32, Z)), tb, 0, st>>>(dz, T, s2, Tp, dzb, dzT);
-#endif
+  lr_dz_convert_kernel<<<(::skp::note_launch(), dim3((s2 + 63) / 64, (Tp + 63) / 64, Z)), 256, 0, st>>>(dz, T, s2, Tp, dzb, dzT);
   lr_heads_transposed_kernel<<<(::skp::note_launch(), dim3((a.C + 31) / 32, (Tp + 31) / 32, Bk)), tb, 0, st>>>(a.k, T, Tp, a.C, a.heads, 1.0f, kT);
   lr_heads_transposed_kernel<<<(::skp::note_launch(), dim3((a.C + 31) / 32, (s2 + 31) / 32, B)), tb, 0, st>>>(a.q, s2, s2, a.C, a.heads, 1.0f, qT);
   SKP_LAUNCH_CHECK();
