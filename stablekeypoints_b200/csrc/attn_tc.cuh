@@ -8,6 +8,12 @@
 #include "common.cuh"
 #include "ptx_sm100.cuh"
 
+// 1: the backward's window flush accumulates dz in bf16 (TMA reduce-add on a bf16 tensor map); the native-resolution GEMMs then
+// read it as is (dq: MN-major A) and lr_dz_convert_kernel is not launched.  0: fp32 accumulation + conversion.
+#ifndef SKP_DZ_BF16
+#define SKP_DZ_BF16 1
+#endif
+
 namespace skp {
 
 constexpr int TC_MAX_LAYERS = 12;

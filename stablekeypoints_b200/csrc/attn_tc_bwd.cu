@@ -953,10 +953,25 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
               uint32_t v[32];
               ptx::tmem_ld32(tm_dK + lane_off + ch * 64 + c * 32, v);
               ptx::tmem_ld_wait();
+#if SKP_DZ_BF16
+              // bf16 accumulation: one [128 tokens][64 taps] bf16 tile (128 B rows) per token half
+              uint8_t* tile = ds_ptr + ch * 16384 + row * 128;
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                uint32_t w4[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  const __nv_bfloat162 h2 = __floats2bfloat162_rn(__uint_as_float(v[8 * q + 2 * e]), __uint_as_float(v[8 * q + 2 * e + 1]));
+                  w4[e] = *reinterpret_cast<const uint32_t*>(&h2);
+                }
+                *reinterpret_cast<uint4*>(tile + (((4 * c + q) ^ (row & 7)) << 4)) = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+              }
+#else
               uint8_t* tile = ds_ptr + (ch * 2 + c) * 16384 + row * 128;
 #pragma unroll
               for (int q = 0; q < 8; ++q)
                 *reinterpret_cast<uint4*>(tile + ((q ^ (row & 7)) << 4)) = make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+#endif
             }
             ptx::tc_fence_before();
           }
@@ -964,8 +979,12 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
           named_bar_sync(1, TC_SOFTMAX_THREADS);
           if (stid == 0) {
             const int z = x.b * P.ops.heads[x.l] + x.head;
+#if SKP_DZ_BF16
+            for (int mh = 0; mh < n_mh; ++mh) ptx::tma_reduce_add_3d(&P.dz_map[x.l], dsb + mh * 16384, x.r0 * s, tok0 + mh * 128, z);
+#else
             for (int t4 = 0; t4 < 2 * n_mh; ++t4)
               ptx::tma_reduce_add_3d(&P.dz_map[x.l], dsb + t4 * 16384, x.r0 * s + (t4 & 1) * 32, tok0 + (t4 >> 1) * 128, z);
+#endif
             ptx::bulk_commit_group();
           }
           flush_pending = true;
@@ -1057,7 +1076,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
 // ==========================================================================================
 // attn_tc_bwd_lr.cu / attn_tc_lr.cu
 size_t lr_bwd_post_workspace(const skp_attn_layer& a, int B, int T);
-int lr_bwd_post(const skp_attn_layer& a, int B, int T, const float* dz, char* ws, cudaStream_t st);
+int lr_bwd_post(const skp_attn_layer& a, int B, int T, const float* dz, char* ws, cudaStream_t st, bool dz_bf16);
 int lr_launch_weights(int s, int R, const LrGeom& g, __nv_bfloat16* hi, __nv_bfloat16* lo, cudaStream_t st);
 
 // Which main kernel a layer's gradient takes.  The "upsample after the logits" kernels do not see dim_head (their K
@@ -1157,7 +1176,9 @@ static int bwd_launch_group(const skp_attn_layer* sub, const int* ghead, int n_s
       const size_t dzb = tc_align_up(static_cast<size_t>(B) * a.heads * T * a.s * a.s * 4, 1024);
       P.dz[l] = reinterpret_cast<float*>(ws);
       SKP_CUDA(cudaMemsetAsync(ws, 0, dzb, st));
-      rc = tc_encode_map_f32(&P.dz_map[l], ws, a.s * a.s, T, B * a.heads, 128);
+      // (the wide-window kernel adds into fp32 dz with vector reductions and does not use the map)
+      rc = (SKP_DZ_BF16 && kind == BWD_LR64) ? tc_encode_map(&P.dz_map[l], ws, a.s * a.s, T, B * a.heads, 128)
+                                                 : tc_encode_map_f32(&P.dz_map[l], ws, a.s * a.s, T, B * a.heads, 128);
       if (rc != SKP_OK) return rc;
       ws += dzb;
       post_ws[l] = ws;
@@ -1204,7 +1225,7 @@ static int bwd_launch_group(const skp_attn_layer* sub, const int* ghead, int n_s
 #endif
   if (lr)
     for (int l = 0; l < n_sub; ++l) {
-      rc = lr_bwd_post(sub[l], B, T, P.dz[l], post_ws[l], st);
+      rc = lr_bwd_post(sub[l], B, T, P.dz[l], post_ws[l], st, SKP_DZ_BF16 && kind == BWD_LR64);
       if (rc != SKP_OK) return rc;
     }
   *ws_io = ws;

@@ -32,6 +32,7 @@ struct LrGradGemmParams {
   int ld, d, heads, m_valid, K;
   int nsum, a_zstride, b_zstride;   // the sum over z: A batch = za + i * a_zstride, B batch = zb + i * b_zstride
   int b_shared;           // B batch ignores the image (dq product with a shared k)
+  int a_mn;               // A is stored [k][m] (m contiguous): a_map = (M, K_rows, Z) with box (64, 64, 1), two 64-wide M slabs per stage
   float alpha;
 };
 
@@ -125,7 +126,17 @@ __global__ void __launch_bounds__(LGG_THREADS) lr_grad_gemm_kernel(const __grid_
   if (warp == 0) {
     if (lane == 0) {
       // one thread runs both the TMA ring (LGG_STAGES blocks ahead) and the MMA issue
-      constexpr uint32_t idesc = ptx::umma_idesc_bf16(TC_BM, LGG_BN);
+      // instruction descriptor of ptx::umma_idesc_bf16 (+ bit 15: A is MN-major); MN-major descriptor as in attn_tc_bwd.cu (bw_desc)
+      const uint32_t idesc = ptx::umma_idesc_bf16(TC_BM, LGG_BN) | (P.a_mn ? (1u << 15) : 0u);
+      auto mn_desc = [](uint32_t addr, uint32_t lbo, uint32_t sbo) {
+        uint64_t d = 0;
+        d |= static_cast<uint64_t>((addr & 0x3FFFFu) >> 4);
+        d |= static_cast<uint64_t>(lbo >> 4) << 16;
+        d |= static_cast<uint64_t>(sbo >> 4) << 32;
+        d |= static_cast<uint64_t>(1) << 46;
+        d |= static_cast<uint64_t>(2) << 61;
+        return d;
+      };
       auto load = [&](int it) {
         const int i = it / nkb, kb = it - i * nkb;
         const int s = it % LGG_STAGES;
@@ -134,7 +145,12 @@ __global__ void __launch_bounds__(LGG_THREADS) lr_grad_gemm_kernel(const __grid_
         ptx::mbar_wait(bar_empty(s), ((it / LGG_STAGES) & 1u) ^ 1u);
         ptx::mbar_arrive_expect_tx(bar_full(s), LGG_STAGE);
         const uint32_t st = base + s * LGG_STAGE;
-        ptx::tma_load_3d(st, &P.a_map, bar_full(s), kb * TC_BK, mt * TC_BM, za);
+        if (P.a_mn) {         // [k rows][64 m] slabs: m 0-63, then m 64-127
+          ptx::tma_load_3d(st, &P.a_map, bar_full(s), mt * TC_BM, kb * TC_BK, za);
+          ptx::tma_load_3d(st + LGG_A_BYTES / 2, &P.a_map, bar_full(s), mt * TC_BM + 64, kb * TC_BK, za);
+        } else {
+          ptx::tma_load_3d(st, &P.a_map, bar_full(s), kb * TC_BK, mt * TC_BM, za);
+        }
         ptx::tma_load_3d(st + LGG_A_BYTES, &P.b_map, bar_full(s), kb * TC_BK, n0, zb);
       };
       const int ahead = total < LGG_STAGES ? total : LGG_STAGES;
@@ -147,8 +163,8 @@ __global__ void __launch_bounds__(LGG_THREADS) lr_grad_gemm_kernel(const __grid_
         const int kb = it % nkb;
         const int nk16 = (min(TC_BK, P.K - kb * TC_BK) + 15) / 16;
         for (int kk = 0; kk < nk16; ++kk)
-          ptx::umma_bf16(tmem_base, ptx::umma_desc_sw128(st + kk * 32), ptx::umma_desc_sw128(st + LGG_A_BYTES + kk * 32), idesc,
-                         (it | kk) != 0);
+          ptx::umma_bf16(tmem_base, P.a_mn ? mn_desc(st + kk * 2048, LGG_A_BYTES / 2, 1024) : ptx::umma_desc_sw128(st + kk * 32),
+                         ptx::umma_desc_sw128(st + LGG_A_BYTES + kk * 32), idesc, (it | kk) != 0);
         ptx::umma_commit(bar_empty(s));
         if (it + LGG_STAGES < total) load(it + LGG_STAGES);
       }
@@ -206,7 +222,9 @@ size_t lr_bwd_post_workspace(const skp_attn_layer& a, int B, int T) {
 
 // dz (fp32, [B*h][T][s2], complete) -> accumulate dq and dk of this layer.  `ws` must hold lr_bwd_post_workspace minus the
 // dz buffer itself (the four bf16 arrays), 1024-aligned.
-int lr_bwd_post(const skp_attn_layer& a, int B, int T, const float* dz, char* ws, cudaStream_t st) {
+// dz_bf16: dz already is bf16 [B*h][T][s2] (accumulated that way by the main kernel): no conversion, the dq product reads it as
+// an MN-major A operand.
+int lr_bwd_post(const skp_attn_layer& a, int B, int T, const float* dz, char* ws, cudaStream_t st, bool dz_bf16) {
   const int s2 = a.s * a.s, d = a.C / a.heads, Tp = (T + 7) / 8 * 8, Bk = a.k_shared ? 1 : B, Z = B * a.heads;
   auto take = [&](size_t bytes) {
     __nv_bfloat16* p = reinterpret_cast<__nv_bfloat16*>(ws);
@@ -218,7 +236,8 @@ int lr_bwd_post(const skp_attn_layer& a, int B, int T, const float* dz, char* ws
   __nv_bfloat16* kT = take(static_cast<size_t>(Bk) * a.C * Tp * 2);
   __nv_bfloat16* qT = take(static_cast<size_t>(B) * a.C * s2 * 2);
   const dim3 tb(32, 8);
-  lr_dz_convert_kernel<<<(::skp::note_launch(), dim3((s2 + 63) / 64, (Tp + 63) / 64, Z)), 256, 0, st>>>(dz, T, s2, Tp, dzb, dzT);
+  if (dz_bf16) dzb = reinterpret_cast<__nv_bfloat16*>(const_cast<float*>(dz));
+  else lr_dz_convert_kernel<<<(::skp::note_launch(), dim3((s2 + 63) / 64, (Tp + 63) / 64, Z)), 256, 0, st>>>(dz, T, s2, Tp, dzb, dzT);
   lr_heads_transposed_kernel<<<(::skp::note_launch(), dim3((a.C + 31) / 32, (Tp + 31) / 32, Bk)), tb, 0, st>>>(a.k, T, Tp, a.C, a.heads, 1.0f, kT);
   lr_heads_transposed_kernel<<<(::skp::note_launch(), dim3((a.C + 31) / 32, (s2 + 31) / 32, B)), tb, 0, st>>>(a.q, s2, s2, a.C, a.heads, 1.0f, qT);
   SKP_LAUNCH_CHECK();
@@ -227,7 +246,8 @@ int lr_bwd_post(const skp_attn_layer& a, int B, int T, const float* dz, char* ws
   {
     LrGradGemmParams G;
     memset(&G, 0, sizeof(G));
-    int rc = tc_encode_map(&G.a_map, dzT, Tp, s2, Z, TC_BM);
+    int rc = dz_bf16 ? tc_encode_map(&G.a_map, dzb, s2, T, Z, 64) : tc_encode_map(&G.a_map, dzT, Tp, s2, Z, TC_BM);
+    G.a_mn = dz_bf16 ? 1 : 0;
     if (rc == SKP_OK) rc = tc_encode_map(&G.b_map, kT, Tp, d, Bk * a.heads, LGG_BN);
     if (rc != SKP_OK) return rc;
     G.out = a.dq; G.out_z = static_cast<int64_t>(s2) * a.C; G.ld = a.C; G.d = d; G.heads = a.heads; G.m_valid = s2; G.K = Tp;
