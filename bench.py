@@ -60,13 +60,15 @@ TOLERANCE = {
     "maps_forward": "rtol 1e-3 vs fp64 oracle (bf16x3 split products, fp32 accumulation): tests/test_full_size_parity_gpu.py",
     "row_stats": "2e-4 abs on m + log2(l) (log2 units)",
     "token_ids_argmax_fps": "bit-exact (rank ties only where fp64 scores differ < 3e-6 rel)",
-    "backward_dq_dk": "<= 1.5e-2 of each gradient's max vs fp64 autograd (gradient products dS^T.W / dS.K / dS^T.Q' take single-bf16 "
-                      "operands, fp32 accumulation; S recompute is bf16x3)",
+    "backward_dq_dk": "<= 1.5e-2 of each gradient's max vs fp64 autograd, measured 3e-3 .. 7e-3 (gradient products dS^T.W / dS.K / "
+                      "dS^T.Q' take single-bf16 operands, fp32 accumulation in TMEM; window sums of the logit gradient are added "
+                      "in bf16 at L2; S recompute is bf16x3)",
     "context_gradient_e2e": "<= 1e-2 of max vs the live reference (tests/test_e2e_gpu.py)",
     "soft_argmax_keypoints": "0.5 px at 512^2 (measured 1e-3)",
 }
 DTYPE = ("f32 I/O and accumulation; forward Q.K^T as bf16x3 split products on tcgen05 (fp32-grade, rtol 1e-3); backward: logit "
-         "recompute bf16x3, gradient products single bf16 with fp32 accumulation (<= 1.5e-2 of max); UNet/VAE trunk stock PyTorch fp32")
+         "recompute bf16x3, gradient products single bf16 with fp32 accumulation, the logit gradient's window sums in bf16 (<= 1.5e-2 "
+         "of max, measured <= 7e-3); UNet/VAE trunk stock PyTorch fp32")
 
 
 def parse():
