@@ -38,8 +38,13 @@ namespace skp {
 // marked events of units BW_TR_U0 .. +BW_TR_N and prints them at the end of the kernel (scripts/bwd_trace.py reads the lines).
 #ifdef SKP_BWD_TRACE
 constexpr int BW_TR_U0 = 40, BW_TR_N = 12, BW_TR_EV = 12, BW_TR_CTA = 2;
+#ifndef SKP_BWD_TRACE_STAGED
+constexpr bool BW_TR_LR = true;      // -DSKP_BWD_TRACE_STAGED: trace the staged kernel instead (event 10 = adjoint done)
+#else
+constexpr bool BW_TR_LR = false;
+#endif
 __device__ long long g_bw_tr[12][BW_TR_N][BW_TR_EV];
-#define BW_TR(ev) { if (LR && !WIDE && blockIdx.x == BW_TR_CTA && lane == 0 && it >= BW_TR_U0 && it < BW_TR_U0 + BW_TR_N) g_bw_tr[warp][it - BW_TR_U0][ev] = clock64(); }
+#define BW_TR(ev) { if (LR == BW_TR_LR && !WIDE && blockIdx.x == BW_TR_CTA && lane == 0 && it >= BW_TR_U0 && it < BW_TR_U0 + BW_TR_N) g_bw_tr[warp][it - BW_TR_U0][ev] = clock64(); }
 #else
 #define BW_TR(ev)
 #endif
@@ -935,6 +940,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
         }
       }
       named_bar_sync(2, TC_SOFTMAX_THREADS);
+      BW_TR(10)
       }
       pf[4] += BW_CLK() - c1;
       c_end = BW_CLK();
@@ -1061,7 +1067,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
     ptx::tmem_dealloc(tmem_base, 512);
   }
 #ifdef SKP_BWD_TRACE
-  if (LR && !WIDE && blockIdx.x == BW_TR_CTA && lane == 0 && (warp == 1 || warp >= BW_SOFTMAX_WARP0))
+  if (LR == BW_TR_LR && !WIDE && blockIdx.x == BW_TR_CTA && lane == 0 && (warp == 1 || warp >= BW_SOFTMAX_WARP0))
     for (int i = 0; i < BW_TR_N; ++i) {
       const long long* e = g_bw_tr[warp][i];
       const long long t0 = g_bw_tr[1][0][0];
