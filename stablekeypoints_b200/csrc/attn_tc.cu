@@ -598,17 +598,37 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
       const float cf = ncol > 0 ? __fdividef(wgt_u * pow2_int(m_own - mg), total) : 0.0f;
       FW_PROF(4)
       if (!SELECT) {
+        // four 16-column chunks, the load of chunk c + 1 in flight under the FMAs of chunk c (unconditional loads, like pass B;
+        // cf is 0 for a thread without columns and the write-out skips columns past T)
+        auto fma16 = [&](int c, const uint32_t (&w)[16]) {
 #pragma unroll
-        for (int c = 0; c < NCH; ++c) {
-          if (32 * c < ncol) {
-            uint32_t v[32];
-            ptx::tmem_ld32(taddr + 32 * c, v);
+          for (int j = 0; j < 16; ++j) acc[16 * c + j] = fmaf(cf, __uint_as_float(w[j]), acc[16 * c + j]);
+        };
+        {
+          uint32_t a0[16];
+          ptx::tmem_ld16(taddr, a0);
+          ptx::tmem_ld_wait();
+          FW_PROF(5)
+          {
+            uint32_t a1[16];
+            ptx::tmem_ld16(taddr + 16, a1);
+            fma16(0, a0);
             ptx::tmem_ld_wait();
-            FW_PROF(5)
-#pragma unroll
-            for (int j = 0; j < 32; ++j) acc[32 * c + j] = fmaf(cf, __uint_as_float(v[j]), acc[32 * c + j]);
-            FW_PROF(6)
+            {
+              uint32_t a2[16];
+              ptx::tmem_ld16(taddr + 32, a2);
+              fma16(1, a1);
+              ptx::tmem_ld_wait();
+              {
+                uint32_t a3[16];
+                ptx::tmem_ld16(taddr + 48, a3);
+                fma16(2, a2);
+                ptx::tmem_ld_wait();
+                fma16(3, a3);
+              }
+            }
           }
+          FW_PROF(6)
         }
       } else {
         // the selected tokens' exponentials of unit uu are in registers (pass B): no TMEM access, no buffer to release
@@ -695,48 +715,70 @@ attn_map_fwd_tc_kernel(const __grid_constant__ TcParams P) {
             }
           }
         }
+        // 16-column chunks, software-pipelined: the load of chunk c + 1 is in flight under the exponentials of chunk c (with
+        // 32-column chunks loaded and waited for one after the other every unit exposed two TMEM round trips per pass, all
+        // four warps of a scheduler at the same time, the MUFU pipe idle; two 16-column buffers cost the registers of one
+        // 32-column chunk)
+        {
+          constexpr int NC16 = FW_QCOLS / 16;
+          // loads are unconditional (columns past T's end are inside the buffer; their chunks are skipped below): straight-line
+          // dataflow for the register allocator
+          auto chunk = [&](int c, uint32_t (&w)[16]) {
+            if (16 * c < ncol) {
+              if (ncol >= 16 * (c + 1)) {
 #pragma unroll
-        for (int c = 0; c < NCH; ++c) {
-          if (32 * c < ncol) {
-            uint32_t v[32];
-            ptx::tmem_ld32(taddr + 32 * c, v);
+                for (int j = 0; j < 16; j += 4) {
+                  const float e0 = ptx::ex2(__uint_as_float(w[j]) - m), e1 = ptx::ex2(__uint_as_float(w[j + 1]) - m);
+                  const float e2 = ptx::ex2(__uint_as_float(w[j + 2]) - m), e3 = ptx::ex2(__uint_as_float(w[j + 3]) - m);
+                  s0 += e0; s1 += e1; s2 += e2; s3 += e3;
+                  w[j] = __float_as_uint(e0); w[j + 1] = __float_as_uint(e1);
+                  w[j + 2] = __float_as_uint(e2); w[j + 3] = __float_as_uint(e3);
+                }
+              } else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                  const float e = (16 * c + j < ncol) ? ptx::ex2(__uint_as_float(w[j]) - m) : 0.0f;
+                  s0 += e;
+                  w[j] = __float_as_uint(e);
+                }
+              }
+              if (!SELECT) ptx::tmem_st16(taddr + 16 * c, w);
+            }
+          };
+          static_assert(NC16 == 4, "four 16-column chunks per thread");
+          {
+            uint32_t a0[16];
+            ptx::tmem_ld16(taddr, a0);
             ptx::tmem_ld_wait();
-            if (SELECT && (c == NCH - 1 || 32 * (c + 1) >= ncol)) {
-              // my columns of the logits are in registers: the tensor pipe may reuse the buffer (unit u + 2)
-              ptx::tc_fence_before();
-              ptx::mbar_arrive(bar_tempty(buf, hf));
-            }
-            FW_PROF(7)
-            if (ncol >= 32 * (c + 1)) {
-#pragma unroll
-              for (int j = 0; j < 32; j += 4) {
-                const float e0 = ptx::ex2(__uint_as_float(v[j]) - m), e1 = ptx::ex2(__uint_as_float(v[j + 1]) - m);
-                const float e2 = ptx::ex2(__uint_as_float(v[j + 2]) - m);
-                const float e3 = FW_POLY_EVERY == 4 ? exp2_poly(__uint_as_float(v[j + 3]) - m) : ptx::ex2(__uint_as_float(v[j + 3]) - m);
-                s0 += e0; s1 += e1; s2 += e2; s3 += e3;
-                v[j] = __float_as_uint(e0); v[j + 1] = __float_as_uint(e1);
-                v[j + 2] = __float_as_uint(e2); v[j + 3] = __float_as_uint(e3);
+            {
+              uint32_t a1[16];
+              ptx::tmem_ld16(taddr + 16, a1);
+              chunk(0, a0);
+              ptx::tmem_ld_wait();
+              {
+                uint32_t a2[16];
+                ptx::tmem_ld16(taddr + 32, a2);
+                chunk(1, a1);
+                ptx::tmem_ld_wait();
+                {
+                  uint32_t a3[16];
+                  ptx::tmem_ld16(taddr + 48, a3);
+                  chunk(2, a2);
+                  ptx::tmem_ld_wait();
+                  if (SELECT) {
+                    // my columns of the logits are in registers: the tensor pipe may reuse the buffer (unit u + 2)
+                    ptx::tc_fence_before();
+                    ptx::mbar_arrive(bar_tempty(buf, hf));
+                  }
+                  chunk(3, a3);
+                }
               }
-            } else {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) {
-                const float e = (32 * c + j < ncol) ? ptx::ex2(__uint_as_float(v[j]) - m) : 0.0f;
-                s0 += e;
-                v[j] = __float_as_uint(e);
-              }
             }
-            FW_PROF(8)
-            if (!SELECT) ptx::tmem_st32(taddr + 32 * c, v);
           }
         }
         const float sum = (s0 + s1) + (s2 + s3);
         if (!SELECT) ptx::tmem_st_wait();
         if (SELECT) {
-          if (ncol <= 0) {                       // no columns of mine: nothing was loaded, release here
-            ptx::tmem_ld_wait();
-            ptx::tc_fence_before();
-            ptx::mbar_arrive(bar_tempty(buf, hf));
-          }
 #pragma unroll
           for (int g = 0; g < TC_MAX_SEL; g += 4) {
             if (static_cast<uint32_t>(g) < n_mine) {
