@@ -119,7 +119,11 @@ int skp_attn_map_fwd_static(const skp_attn_layer* h_layers, int n_layers, int B,
  * layer.dq / layer.dk.  Linear in dmaps_sel, so callers may chunk planes.
  * row_stats: the (B, sum_l heads_l, R*R, 2) tensor skp_attn_map_fwd wrote for the SAME q/k, or
  * NULL.  With it (and dim_head <= 64, n_idx <= 16, T <= 512) the backward runs on tcgen05
- * (attn_tc_bwd.cu); without it the fp32 CUDA-core kernel recomputes the softmax statistics. */
+ * (attn_tc_bwd.cu); without it the fp32 CUDA-core kernel recomputes the softmax statistics.
+ * Arithmetic: the tcgen05 backward recomputes the logits fp32-grade (bf16x3) but takes SINGLE-bf16 operands in its
+ * gradient products (dS, the interpolation table / q' / k) with fp32 accumulation, and adds the window sums of the logit
+ * gradient in bf16: dq / dk are within 1.5e-2 of each gradient's max of fp64 autograd (measured 3e-3 .. 7e-3;
+ * tests/test_full_size_parity_gpu.py), looser than the forward's 1e-3.  SKP_PREC_SIMT_F32 is the fp32 backward (2e-3). */
 int skp_attn_map_bwd(const skp_attn_layer* h_layers, int n_layers, int B, int T, int R,
                      const int64_t* token_idx, int n_idx, int64_t idx_stride, const float* dmaps_sel,
                      const float* row_stats, int precision, void* workspace, size_t workspace_bytes, void* stream);

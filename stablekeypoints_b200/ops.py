@@ -507,7 +507,10 @@ def attention_maps(qs: Sequence[torch.Tensor], ks: Sequence[torch.Tensor], heads
                    precision: str = "auto", return_stats: bool = False, return_workspace: bool = False):
     """qs[l] (B, s_l^2, C_l) low-resolution to_q(x); ks[l] (B or 1, T, C_l) to_k(context).
     -> (B, T', R, R) with T' = len(token_idx) or T.  Differentiable w.r.t. every q and k.
-    return_stats: also return the (B, sum heads, R^2, 2) softmax statistics (for `selected_planes`)."""
+    return_stats: also return the (B, sum heads, R^2, 2) softmax statistics (for `selected_planes`).    `precision`: "auto" / "tc_bf16x3" = tcgen05 with bf16 hi + lo operands (forward fp32-grade, rtol 1e-3; the BACKWARD of
+    these maps takes single-bf16 operands in its gradient products: <= 1.5e-2 of each gradient's max, measured <= 7e-3),
+    "tc_bf16" = plain bf16 forward (rtol 3e-2), "simt_f32" = fp32 CUDA-core kernels in both directions (2e-3, validation).
+    """
     n = len(qs)
     if weights is None:
         weights = [1.0 / n] * n

@@ -188,12 +188,16 @@ def select_tokens_batched(maps, maps_transformed, top_k_strategy, furthest_point
 
 def token_opt_losses(ldm, image, transformed_img, context, transform, controllers, *, layers, noise_level, from_where,
                      device, top_k_strategy, furthest_point_num_samples, top_k, sigma, num_subjects, noise=None,
-                     generator=None):
+                     generator=None, precision="auto"):
     """One image-iteration of `optimize.py:372-429` for a batch of B images on this device.
 
     Both UNet passes of the reference (image, transformed image) run as ONE pass over 2B images
     (every normalisation in the UNet is per-sample, so batching does not change any value).
     Selection and losses of all B images are one launch per stage; nothing is read back to the host.
+    `precision` selects the arithmetic of the attention maps and of their backward (`ops.attention_maps`): "auto" = tcgen05
+    (forward fp32-grade bf16x3; gradient products on single-bf16 operands, <= 1.5e-2 of each gradient's max, measured <= 7e-3);
+    "simt_f32" = the fp32 CUDA-core kernels in both directions (2e-3; ~80 x slower: the A/B of
+    `tests/test_e2e_gpu.py::test_optimisation_converges_alike_with_tensor_core_and_fp32_backward`).
     -> (mean sharpening loss, mean equivariance loss, idx (B, top_k))."""
     from . import ptp_utils
     B = image.shape[0]
@@ -206,11 +210,11 @@ def token_opt_losses(ldm, image, transformed_img, context, transform, controller
     ctrl.reset()
     with torch.no_grad():
         maps, stats, fwd_ws = ops.attention_maps([q.detach() for q in qs], [k.detach() for k in ks], heads, scales, R,
-                                                 return_stats=True, return_workspace=True)               # (2B,T,R,R)
+                                                 precision=precision, return_stats=True, return_workspace=True)   # (2B,T,R,R)
         idx = select_tokens_batched(maps[:B], maps[B:], top_k_strategy, furthest_point_num_samples, top_k, sigma, num_subjects)
     # the backward reuses the native-resolution logits / interpolation tables the forward staged in its workspace
-    sel = ops.selected_planes(maps, torch.cat([idx, idx], dim=0), qs, ks, heads, scales, R, row_stats=stats,
-                              fwd_workspace=fwd_ws)                                                       # (2B,K,R,R)
+    sel = ops.selected_planes(maps, torch.cat([idx, idx], dim=0), qs, ks, heads, scales, R, precision=precision,
+                              row_stats=stats, fwd_workspace=fwd_ws)                                      # (2B,K,R,R)
     per_image = ops.keypoint_losses_batched(sel, transform.inverse_theta(), float(sigma), int(num_subjects))
     return per_image[:, 0].mean(), per_image[:, 1].mean(), idx
 
@@ -261,8 +265,9 @@ def optimize_embedding(
     step_hook=None,
     seed=None,
     grad_hook=None,
+    precision="auto",
 ):
-    """`optimize.py:269-475` with the same arguments.  `num_gpus` keeps the reference's meaning
+    """`optimize.py:269-475` with the same arguments (+ `precision`, see `token_opt_losses`).  `num_gpus` keeps the reference's meaning
     "images per UNet pass" (its DataLoader batch, `optimize.py:356`); here those images share
     ONE GPU.  Across processes (torchrun, one per GPU) every rank runs this function on its own
     shard of each batch and the context gradient is all-reduced (mean) before each optimiser
@@ -308,7 +313,7 @@ def optimize_embedding(
             ldm, image, transformed, context, transform, controllers, layers=layers, noise_level=noise_level,
             from_where=from_where, device=device, top_k_strategy=top_k_strategy,
             furthest_point_num_samples=furthest_point_num_samples, top_k=top_k, sigma=sigma, num_subjects=num_subjects,
-            generator=g_dev)
+            generator=g_dev, precision=precision)
         loss = eq * equivariance_attn_loss_weight + sh * sharpening_loss_weight
         run_eq = run_eq + eq.detach() / accum * equivariance_attn_loss_weight
         run_sh = run_sh + sh.detach() / accum * sharpening_loss_weight
