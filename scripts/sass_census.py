@@ -6,7 +6,7 @@ import collections, os, re, subprocess, sys
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 lib = os.path.join(root, "stablekeypoints_b200", "libskp_b200.so")
 out = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True).stdout
-OPS = ["UTCHMMA", "UTCBAR", "LDTM", "STTM", "UTMALDG", "UBLKCP", "SYNCS", "MUFU.EX2", "REDG", "USETMAXREG", "HMMA", "FFMA", "LDS", "STS", "LDG", "STG", "ATOMG"]
+OPS = ["UTCHMMA", "UTCBAR", "LDTM", "STTM", "UTMALDG", "UTMAREDG", "SYNCS", "MUFU.EX2", "REDG", "USETMAXREG", "HMMA", "UBLKCP", "FFMA", "LDS", "STS", "LDG", "STG", "ATOMG"]
 cur, counts, total = None, collections.OrderedDict(), collections.Counter()
 for ln in out.splitlines():
     m = re.match(r"\s*Function : (\S+)", ln)
