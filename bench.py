@@ -182,14 +182,16 @@ class ImagePool(torch.utils.data.Dataset):
     """A fixed pool of synthetic images held in ONE tensor: on the GPU (the `value` arm: inputs
     resident in HBM) or in pinned host memory (the `e2e` arm: copied in every step)."""
 
-    def __init__(self, images: torch.Tensor):
-        self.images = images
+    def __init__(self, images: torch.Tensor, world: int = 1):
+        # every rank holds its own pool (seed 100 + rank) and `optimize_embedding` shards whatever dataset it is given by
+        # rank: present the pool `world` times so that this rank's shard is the whole pool at any N
+        self.images, self.world = images, world
 
     def __len__(self):
-        return self.images.shape[0]
+        return self.images.shape[0] * self.world
 
     def __getitem__(self, i):
-        return {"img": self.images[i]}
+        return {"img": self.images[i % self.images.shape[0]]}
 
 
 def make_pool(cfg, rank: int) -> torch.Tensor:
@@ -408,12 +410,12 @@ def measure_optimize(args, cfg, env, rank, local_rank, world, pools, *, global_b
     dev, ldm, controllers, context = env
     probe = Probe(rank, local_rank)
     timer = StepTimer(args.warmup, args.steps, probe.on_start, probe.on_end)
-    run_optimize(args, cfg, dev, ldm, controllers, context, ImagePool(pools["dev"]), global_batch, per_pass, False, timer)
+    run_optimize(args, cfg, dev, ldm, controllers, context, ImagePool(pools["dev"], world), global_batch, per_pass, False, timer)
     out = {"ms": max_over_ranks(timer.ms), "probe": probe.rec}
     if e2e:
         timer2 = StepTimer(args.warmup, args.steps)
         losses = []
-        run_optimize(args, cfg, dev, ldm, controllers, context, ImagePool(pools["host"]), global_batch, per_pass, losses.append, timer2)
+        run_optimize(args, cfg, dev, ldm, controllers, context, ImagePool(pools["host"], world), global_batch, per_pass, losses.append, timer2)
         assert all(l["loss"] == l["loss"] for l in losses), "NaN loss in the e2e arm"
         out["ms_e2e"] = max_over_ranks(timer2.ms)
         out["h2d"] = (global_batch // world) * 3 * cfg["image"] ** 2 * 4

@@ -296,8 +296,12 @@ def optimize_embedding(
     accum = batch_size // (per_pass * world)
     host_data = not torch.as_tensor(dataset[0]["img"]).is_cuda
     g_cpu, g_dev = dist_.rank_generators(device, seed)
-    loader = torch.utils.data.DataLoader(dist_.shard_dataset(dataset, rank, world), batch_size=per_pass,
-                                         shuffle=True, drop_last=True, pin_memory=host_data, generator=g_cpu)
+    shard = dist_.shard_dataset(dataset, rank, world)
+    if len(shard) < per_pass:
+        raise ValueError(f"rank {rank}: {len(shard)} image(s) of the {len(dataset)}-image dataset, fewer than the {per_pass} of one UNet "
+                         f"pass (num_gpus): the dataset must hold at least num_gpus * world_size = {per_pass * world} images")
+    loader = torch.utils.data.DataLoader(shard, batch_size=per_pass, shuffle=True, drop_last=True, pin_memory=host_data,
+                                         generator=g_cpu)
     it = iter(loader)
     start = it_start = time.time()
     run_eq = run_sh = run_tot = 0.0
