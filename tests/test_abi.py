@@ -73,3 +73,26 @@ def test_product_package_never_imports_the_oracle():
             if f.endswith(".py"):
                 src = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f"{f} imports oracle/"
+
+
+def test_torch_operator_library_is_registered_with_meta_kernels_and_no_cpu_kernel():
+    """the entry points are also `torch.ops.skp_b200.*` operators (CUDA key only; shapes from Meta kernels)."""
+    import torch
+    import stablekeypoints_b200.torch_ops as T
+    for name in T.SCHEMAS:
+        assert hasattr(torch.ops.skp_b200, name), name
+    qs = [torch.empty(2, 16, 32, device="meta"), torch.empty(2, 64, 16, device="meta")]
+    ks = [torch.empty(1, 40, 32, device="meta"), torch.empty(1, 40, 16, device="meta")]
+    m = torch.ops.skp_b200.attention_maps(qs, ks, [2, 1], [0.25, 0.25], 32, None)
+    assert m.shape == (2, 40, 32, 32) and m.dtype == torch.float32
+    m = torch.ops.skp_b200.attention_maps(qs, ks, [2, 1], [0.25, 0.25], 32, torch.empty(5, dtype=torch.int64, device="meta"))
+    assert m.shape == (2, 5, 32, 32)
+    planes = torch.empty(7, 32, 32, device="meta")
+    assert torch.ops.skp_b200.plane_argmax(planes).shape == (7,)
+    kl, ent, am = torch.ops.skp_b200.plane_stats(planes, 2.0, 1e-5, 1)
+    assert kl.shape == ent.shape == am.shape == (7,) and am.dtype == torch.int64
+    assert torch.ops.skp_b200.find_k_max_pixels(planes, 3).shape == (3, 7, 2)
+    assert torch.ops.skp_b200.bilinear_upsample(planes, 128).shape == (7, 128, 128)
+    import pytest
+    with pytest.raises((NotImplementedError, RuntimeError)):        # no CPU kernel: PyTorch's dispatcher says so
+        torch.ops.skp_b200.plane_argmax(torch.zeros(2, 8, 8))

@@ -468,3 +468,24 @@ def test_config5_sdxl_shapes_16_keypoints(ops):
     # readout of the 16 selected planes: bit-exact argmax
     am = ops.plane_argmax(c[0])
     assert torch.equal(am.cpu(), torch.argmax(c[0].reshape(16, -1), dim=-1).cpu())
+
+
+def test_torch_operator_library_calls_the_same_kernels(ops):
+    """`torch.ops.skp_b200.*` == the `ops` functions they wrap, bit for bit."""
+    import stablekeypoints_b200.torch_ops  # noqa: F401  (registers the library)
+    g = torch.Generator().manual_seed(7)
+    spec = [(8, 64, 4), (16, 32, 2)]
+    qs = [torch.randn(2, s * s, c, generator=g).to(DEV) for s, c, _ in spec]
+    ks = [torch.randn(1, 48, c, generator=g).to(DEV) for _, c, _ in spec]
+    heads, sc = [h for _, _, h in spec], [(c // h) ** -0.5 for _, c, h in spec]
+    a = torch.ops.skp_b200.attention_maps(qs, ks, heads, sc, 32, None)
+    assert torch.equal(a, ops.attention_maps(qs, ks, heads, sc, 32))
+    idx = torch.tensor([3, 40, 7], device=DEV)
+    assert torch.equal(torch.ops.skp_b200.attention_maps(qs, ks, heads, sc, 32, idx), ops.attention_maps(qs, ks, heads, sc, 32, token_idx=idx))
+    planes = a[0].contiguous()
+    assert torch.equal(torch.ops.skp_b200.plane_argmax(planes), ops.plane_argmax(planes))
+    kl, ent, am = torch.ops.skp_b200.plane_stats(planes, 2.0, 1e-5, 1)
+    kl2, ent2, am2 = ops.plane_stats(planes, 2.0, 1e-5, 1, want_kl=True, want_entropy=True, want_argmax=True)
+    assert torch.equal(kl, kl2) and torch.equal(ent, ent2) and torch.equal(am, am2)
+    assert torch.equal(torch.ops.skp_b200.rank_ascending(kl, 10), ops.rank_ascending(kl, 10))
+    assert torch.equal(torch.ops.skp_b200.bilinear_upsample(planes, 64), ops.bilinear_upsample(planes, 64))
