@@ -33,6 +33,8 @@ struct LrGradGemmParams {
   int nsum, a_zstride, b_zstride;   // the sum over z: A batch = za + i * a_zstride, B batch = zb + i * b_zstride
   int b_shared;           // B batch ignores the image (dq product with a shared k)
   int a_mn;               // A is stored [k][m] (m contiguous): a_map = (M, K_rows, Z) with box (64, 64, 1), two 64-wide M slabs per stage
+  int split;              // the sum over z is cut into `split` CTAs per output tile (blockIdx.y = zg * split + part); their
+                          // epilogues add with vector reductions instead of the single owner's read-modify-write
   float alpha;
 };
 
@@ -96,7 +98,8 @@ __global__ void __launch_bounds__(LGG_THREADS) lr_grad_gemm_kernel(const __grid_
   const uint32_t base = (raw + 1023u) & ~1023u;
   uint8_t* base_ptr = smem_raw + (base - raw);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int mt = blockIdx.x, zg = blockIdx.y;           // zg = output batch * heads + head
+  const int split = P.split > 1 ? P.split : 1;
+  const int mt = blockIdx.x, zg = blockIdx.y / split, part = blockIdx.y - zg * split;   // zg = output batch * heads + head
   const int n0 = blockIdx.z * LGG_BN;                   // first dim_head column of this CTA (dim_head > 64: several N chunks)
   const int zo = zg / P.heads, head = zg - zo * P.heads;
   auto bar_full = [&](int s) { return base + LGG_STAGES * LGG_STAGE + 8u * s; };
@@ -121,7 +124,8 @@ __global__ void __launch_bounds__(LGG_THREADS) lr_grad_gemm_kernel(const __grid_
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
   const int nkb = (P.K + TC_BK - 1) / TC_BK;
-  const int total = nkb * P.nsum;
+  const int i_lo = part * P.nsum / split, i_hi = (part + 1) * P.nsum / split;      // my slice of the sum over z
+  const int total = nkb * (i_hi - i_lo);
 
   if (warp == 0) {
     if (lane == 0) {
@@ -138,7 +142,7 @@ __global__ void __launch_bounds__(LGG_THREADS) lr_grad_gemm_kernel(const __grid_
         return d;
       };
       auto load = [&](int it) {
-        const int i = it / nkb, kb = it - i * nkb;
+        const int i = i_lo + it / nkb, kb = it % nkb;
         const int s = it % LGG_STAGES;
         const int za = (zo * P.heads + head) + i * P.a_zstride;
         const int zb = (P.b_shared ? head : zo * P.heads + head) + i * P.b_zstride;
@@ -189,12 +193,18 @@ __global__ void __launch_bounds__(LGG_THREADS) lr_grad_gemm_kernel(const __grid_
         for (int q = 0; q < 8; ++q) {
           if (c * 32 + q * 4 < dn) {
             float4* p4 = reinterpret_cast<float4*>(o + c * 32 + q * 4);
-            float4 cur = *p4;
-            cur.x = fmaf(P.alpha, __uint_as_float(v[4 * q]), cur.x);
-            cur.y = fmaf(P.alpha, __uint_as_float(v[4 * q + 1]), cur.y);
-            cur.z = fmaf(P.alpha, __uint_as_float(v[4 * q + 2]), cur.z);
-            cur.w = fmaf(P.alpha, __uint_as_float(v[4 * q + 3]), cur.w);
-            *p4 = cur;
+            if (split > 1) {
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p4), "f"(P.alpha * __uint_as_float(v[4 * q])),
+                           "f"(P.alpha * __uint_as_float(v[4 * q + 1])), "f"(P.alpha * __uint_as_float(v[4 * q + 2])),
+                           "f"(P.alpha * __uint_as_float(v[4 * q + 3])) : "memory");
+            } else {
+              float4 cur = *p4;
+              cur.x = fmaf(P.alpha, __uint_as_float(v[4 * q]), cur.x);
+              cur.y = fmaf(P.alpha, __uint_as_float(v[4 * q + 1]), cur.y);
+              cur.z = fmaf(P.alpha, __uint_as_float(v[4 * q + 2]), cur.z);
+              cur.w = fmaf(P.alpha, __uint_as_float(v[4 * q + 3]), cur.w);
+              *p4 = cur;
+            }
           }
         }
       }
@@ -264,7 +274,10 @@ int lr_bwd_post(const skp_attn_layer& a, int B, int T, const float* dz, char* ws
     if (rc != SKP_OK) return rc;
     G.out = a.dk; G.out_z = static_cast<int64_t>(T) * a.C; G.ld = a.C; G.d = d; G.heads = a.heads; G.m_valid = T; G.K = s2;
     G.nsum = a.k_shared ? B : 1; G.a_zstride = a.heads; G.b_zstride = a.heads; G.b_shared = 0; G.alpha = a.scale;
-    lr_grad_gemm_kernel<<<(::skp::note_launch(), dim3((T + TC_BM - 1) / TC_BM, Bk * a.heads, (d + LGG_BN - 1) / LGG_BN)), LGG_THREADS, LGG_DYNAMIC, st>>>(G);
+    // a shared k sums over the images: with one CTA per (token tile, head) that is 80 CTAs walking 8 images each; up to four
+    // CTAs share the sum
+    G.split = G.nsum >= 4 ? 4 : (G.nsum >= 2 ? 2 : 1);
+    lr_grad_gemm_kernel<<<(::skp::note_launch(), dim3((T + TC_BM - 1) / TC_BM, Bk * a.heads * G.split, (d + LGG_BN - 1) / LGG_BN)), LGG_THREADS, LGG_DYNAMIC, st>>>(G);
     SKP_LAUNCH_CHECK();
   }
   return SKP_OK;
