@@ -103,3 +103,17 @@ def test_cpu_pipeline_port_matches_reference_golden():
     assert abs(sh.item() - float(d["ref_sharp"])) < 1e-6 and abs(eq.item() - float(d["ref_equiv"])) < 1e-7
     want = torch.from_numpy(d["ref_context_grad"])
     assert (ctx.grad - want).abs().max().item() <= 1e-4 * want.abs().max().item()
+
+
+def test_optimize_embedding_names_a_dataset_smaller_than_one_unet_pass():
+    """A shard with fewer images than one UNet pass used to surface as a bare StopIteration from the DataLoader (bench.py
+    --workload sdxl at 8 ranks); the argument check happens before anything touches the GPU."""
+    from stablekeypoints_b200 import optimize
+    from stablekeypoints_b200.datasets import SyntheticKeypoints
+    ds = SyntheticKeypoints(length=1, image_size=32)
+    with pytest.raises(ValueError, match="fewer than the 2 of one UNet pass"):
+        optimize.optimize_embedding(None, wandb_log=False, context=torch.zeros(1, 4, 8), device="cpu", num_steps=1, batch_size=2,
+                                    num_gpus=2, dataset=ds)
+    with pytest.raises(ValueError, match="multiple of num_gpus"):
+        optimize.optimize_embedding(None, wandb_log=False, context=torch.zeros(1, 4, 8), device="cpu", num_steps=1, batch_size=3,
+                                    num_gpus=2, dataset=ds)
