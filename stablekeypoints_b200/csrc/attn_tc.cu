@@ -5,20 +5,21 @@
 // replaces the captured branch of the reference's patched CrossAttention.forward
 // (unsupervised_keypoints/ptp_utils.py:508-538) and collect_maps (optimize.py:27-79).
 //
-// Design (DESIGN.md has the long version):
-//  * prep kernels: bicubic-upsample the module's low-resolution q to R x R, fold scale*log2(e)
-//    in, and write it as bf16 (hi [+ lo residual]) in a K-major [b*h][pixel][d] layout; k likewise
-//    as [h][token][d].  bf16x3 mode (hi*hi + hi*lo + lo*hi, fp32 accumulate) is the fp32-grade
-//    "parity" arithmetic; plain bf16 is the fast mode.
-//  * main kernel: one CTA per (image, 128 consecutive feature pixels, 256-token slice); a
-//    cluster of NSPLIT CTAs covers all tokens of the same pixels.  Warp 0 = TMA producer
-//    (128B-swizzled tiles, mbarrier ring), warp 1 = single-thread tcgen05.mma issuer
-//    (M=128, N=256, K=16, accumulators in TMEM, two 256-column buffers ping-pong across
-//    (layer, head) units), warps 2-9 = softmax: thread (row, column half) reads its logits with
-//    tcgen05.ld, takes max / exp2 / sum, parks the exponentials back in TMEM (tcgen05.st),
-//    exchanges (max, sum) with the other column half and the other CTAs of the cluster
-//    through (distributed) shared memory + mbarriers, then accumulates weight * P into 128
-//    fp32 registers.  The (h, R^2, T) probability tensor never exists; the output is written once.
+// Design (DESIGN.md section 4 A has the long version and the measurements):
+//  * operands.  Default ("upsample after the logits", template LR, attn_tc_lr.cu): A = the bicubic interpolation table of
+//    the pixel tile (resident in shared memory: it depends on the source size only), B = the tile's window of
+//    NATIVE-resolution logits s_low = scale*log2(e) * q.k (bf16 hi + lo), so S_tile = W_tile . s_low^T needs K = 64 / 128
+//    taps whatever dim_head is.  Staged form (wide windows): q bicubic-upsampled to R x R by prep kernels, K = dim_head.
+//    bf16x3 (hi*hi + hi*lo + lo*hi, fp32 accumulate) is the fp32-grade "parity" arithmetic; plain bf16 is the fast mode.
+//  * main kernel: one CTA per (image, 128 consecutive feature pixels, 256-token slice); a cluster of NSPLIT CTAs covers all
+//    tokens of the same pixels.  Warp 0 = TMA producer (128B-swizzled tiles, mbarrier ring), warp 1 = tcgen05.mma issuer
+//    (warp-uniform, elected issue; M=128, N=256, K=16, accumulators in TMEM, two 256-column buffers ping-pong across the
+//    (layer, head) units), 16 softmax warps: thread (row, 64-token quarter) reads its logits in four pipelined 16-column
+//    tcgen05.ld chunks, exponentiates (constant shift per (image, head) when the logit range is bounded, else row max),
+//    parks the exponentials back in TMEM, exchanges (max, sum) with the other quarters and the other CTA of the cluster
+//    through (distributed) shared memory + mbarriers, and one unit later accumulates weight * P into 64 fp32 registers.
+//    SELECT (mode C): the few selected tokens of a thread's columns are a compact list, their exponentials live in registers,
+//    nothing is parked.  The (h, R^2, T) probability tensor never exists; the output is written once.
 #include <cstdlib>
 
 #include "attn_tc.cuh"

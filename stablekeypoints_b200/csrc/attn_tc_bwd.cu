@@ -10,11 +10,18 @@
 //   S_sel = Q' K_sel^T          (the n_idx selected tokens' logits, N = 16, TMEM)
 //   P     = exp2(S - m) / l     with the row max / sum (m, l) SAVED BY THE FORWARD (row_stats)
 //   delta = sum_j P_sel[j] dP[j],  dS = P * (dP - delta)      -> bf16 tile in shared memory
+// staged layers (template LR = false):
 //   dQ'   = dS K                (tcgen05; A = dS K-major, B = K hi as an MN-major operand)
 //   dK   += dS^T Q'             (tcgen05; A = dS and B = Q' hi both as MN-major operands; TMEM-
 //                                resident across all units of a head, flushed once per head)
 //   dq   += U^T dQ'             (adjoint of the bicubic upsample, separable: x-gather through
 //                                shared memory, y taps as red.global.add.v4.f32)
+// "upsample after the logits" layers (LR = true; Q' = the tile's interpolation table W, K = its window of native-resolution logits):
+//   dz   += dS^T W              (tcgen05; TMEM-resident over the tiles that share a window, flushed through shared memory
+//                                and a TMA reduce-add into a bf16 dz; attn_tc_bwd_lr.cu turns dz into dq / dk)
+// Roles (12 warps): TMA producer (3 hi / 2 lo operand slots, windows fetched a unit ahead), S issuer and dS-product issuer
+// (whole warps, elected issue), 8 softmax warps (S preloaded to registers, the accumulator handed back at once; the next
+// unit's scalar prep and row prologue inside the dense pass).  DESIGN.md section 4 A' has the measurement behind each choice.
 // No cluster, no cross-CTA exchange: the two token halves only meet in the global reductions.
 #include <cstdlib>
 
