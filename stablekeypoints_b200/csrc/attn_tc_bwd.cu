@@ -251,7 +251,8 @@ constexpr int BW_THREADS = 384;
 constexpr int BW_REGS_LAUNCH = 168, BW_REGS_SMALL = 64, BW_REGS_SOFTMAX = 216;
 static_assert(4 * (BW_REGS_LAUNCH - BW_REGS_SMALL) >= 8 * (BW_REGS_SOFTMAX - BW_REGS_LAUNCH), "setmaxnreg budget");
 #ifndef BW_LR_HOLD
-#define BW_LR_HOLD 2      // chunks (32 tokens each) of a row's dS kept in registers across the wait for the previous dz product
+#define BW_LR_HOLD 3      // chunks (32 tokens each) of a row's dS kept in registers across the wait for the previous dz product
+                          // (measured on the final kernel, per 8-image call: 1: 3.04 ms, 2: 3.04, 3: 2.98, 4: 3.50)
 #endif
 constexpr int BW_SOFTMAX_WARP0 = 4;
 // LR: "upsample after the logits" gradient.  The dQ' / dK products and the bicubic adjoint are replaced by ONE product
