@@ -250,6 +250,12 @@ constexpr int BW_THREADS = 384;
 // must cover what the eight softmax warps take, or setmaxnreg.inc waits forever
 constexpr int BW_REGS_LAUNCH = 168, BW_REGS_SMALL = 64, BW_REGS_SOFTMAX = 216;
 static_assert(4 * (BW_REGS_LAUNCH - BW_REGS_SMALL) >= 8 * (BW_REGS_SOFTMAX - BW_REGS_LAUNCH), "setmaxnreg budget");
+#ifndef BW_PREP_CHUNK
+#define BW_PREP_CHUNK 0     // dense chunk behind which the next unit's scalar prep and row prefetch sit (1: 3.14 vs 2.98 ms)
+#endif
+#ifndef BW_PROLOGUE_LEAD
+#define BW_PROLOGUE_LEAD 1  // chunks between the next unit's S_sel load and the last chunk, where its row prologue runs (2: same time)
+#endif
 #ifndef BW_LR_HOLD
 #define BW_LR_HOLD 3      // chunks (32 tokens each) of a row's dS kept in registers across the wait for the previous dz product
                           // (measured on the final kernel, per 8-image call: 1: 3.04 ms, 2: 3.04, 3: 2.98, 4: 3.50)
@@ -770,7 +776,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
             ptx::tmem_ld_wait();
             if (c < NCHUNK - 1) ptx::tmem_ld32(tm_S + lane_off + col0 + 32 * (c + 1), v[(c + 1) & 1]);
           }
-          if (AHEAD && c == NCHUNK - 2 && u + 1 < u_end) prologue_load(it + 1, sv_n);
+          if (AHEAD && c == NCHUNK - 1 - BW_PROLOGUE_LEAD && u + 1 < u_end) prologue_load(it + 1, sv_n);
           if (AHEAD && c == NCHUNK - 1) {
             ptx::tmem_ld_wait();
             prologue_math(sv_n, wgt, m_n, nd_n, pv_n);
@@ -798,7 +804,7 @@ attn_map_bwd_tc_kernel(const __grid_constant__ BwdParams P) {
               pk[c][j] = *reinterpret_cast<const uint32_t*>(&h2);
             }
           }
-          if (c == 0) {
+          if (c == BW_PREP_CHUNK) {
             // PREP: the next unit's tuple; LR: its row statistics / upstream gradients go out now and land under the rest
             // of this unit (there is no long MMA wait at the end of an LR unit to hide them).  Unconditional (the last unit
             // re-reads its own row): a load under a branch made the compiler copy the loaded registers right behind it,
