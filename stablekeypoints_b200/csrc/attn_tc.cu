@@ -234,23 +234,8 @@ __device__ __forceinline__ float pow2_int(float d) {
   return __int_as_float((bits << 23) + 0x3f800000);
 }
 
-// 2^x for x <= 0 on the FMA / ALU pipes instead of MUFU (pass B is MUFU-bound at 16 ex2/clk/SM while the FMA pipe idles,
-// so every FW_POLY_EVERY-th exponential goes this way): round-to-nearest split x = n + f via the 1.5 * 2^23 trick,
-// degree-5 interpolant of 2^f on [-0.5, 0.5] (max relative error 2.4e-7 in fp32 Horner, the same 2 ulp class as
-// ex2.approx), n added into the exponent field.  Inputs below -126 clamp to 2^-126 (~1e-38; they would flush to 0).
-constexpr int FW_POLY_EVERY = 0;     // 4 = every fourth exponential; measured neutral (the kernel is issue-slot bound: 12 vs 3 instructions)
-__device__ __forceinline__ float exp2_poly(float x) {
-  x = fmaxf(x, -126.0f);
-  const float t = x + 12582912.0f;
-  const float f = x - (t - 12582912.0f);
-  float p = 0.0013390863314270973f;
-  p = fmaf(p, f, 0.009676031768321991f);
-  p = fmaf(p, f, 0.055503569543361664f);
-  p = fmaf(p, f, 0.2402210682630539f);
-  p = fmaf(p, f, 0.6931471824645996f);
-  p = fmaf(p, f, 1.0000001192092896f);
-  return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
-}
+// (A degree-5 polynomial exp2 on the FMA pipe for every fourth exponential was measured neutral in round 1 and slower in round 2 --
+// twelve instructions against three in an issue-bound loop -- and is gone; DESIGN.md section 4 A.)
 
 // 20 warps = 5 warpgroups: warpgroup 0 = {TMA producer, MMA issuer, 2 idle warps} gives registers back
 // (setmaxnreg.dec), warpgroups 1-4 = 16 softmax warps take them (setmaxnreg.inc): 64 fp32 accumulators + one

@@ -101,9 +101,8 @@ __global__ void k_max_pixels_kernel(const float* __restrict__ maps, int N, int H
   const float* p = maps + static_cast<int64_t>(blockIdx.x) * H * W;
   Discs d;
   d.n = 0;
-  float rad = 0.05f * static_cast<float>(H);   // python: 0.05*h (double) -> compared in fp32
+  // python: rad = 0.05*h in double, squared and compared in fp32
   d.rad2 = static_cast<float>((0.05 * static_cast<double>(H)) * (0.05 * static_cast<double>(H)));
-  (void)rad;
   for (int s = 0; s < num; ++s) {
     unsigned long long key = block_masked_argmax(p, H, W, d, scratch);
     uint32_t idx = argmax_key_index(key);
@@ -176,7 +175,6 @@ __global__ void plane_stats_kernel(const float* __restrict__ maps, int H, int W,
                                    int num_subjects, float* kl_out, float* ent_out, int64_t* argmax_out) {
   __shared__ unsigned long long scratch[32];
   __shared__ double dscratch[32];
-  __shared__ float fscratch[32];
   const int n = H * W;
   const float* p = maps + static_cast<int64_t>(blockIdx.x) * n;
   // subjects: successive masked maxima (find_k_max_pixels); centres in pixel units as the
