@@ -251,7 +251,7 @@ constexpr int BW_THREADS = 384;
 constexpr int BW_REGS_LAUNCH = 168, BW_REGS_SMALL = 64, BW_REGS_SOFTMAX = 216;
 static_assert(4 * (BW_REGS_LAUNCH - BW_REGS_SMALL) >= 8 * (BW_REGS_SOFTMAX - BW_REGS_LAUNCH), "setmaxnreg budget");
 #ifndef BW_PREP_CHUNK
-#define BW_PREP_CHUNK 0     // dense chunk behind which the next unit's scalar prep and row prefetch sit (1: 3.14 vs 2.98 ms)
+#define BW_PREP_CHUNK 0     // dense chunk behind which the next unit's scalar prep and row prefetch sit (1: 3.14 vs 2.98 ms; under the TMEM round trip of the S preload, ahead of s_free: 3.06)
 #endif
 #ifndef BW_PROLOGUE_LEAD
 #define BW_PROLOGUE_LEAD 1  // chunks between the next unit's S_sel load and the last chunk, where its row prologue runs (2: same time)
