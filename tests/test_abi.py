@@ -96,3 +96,19 @@ def test_torch_operator_library_is_registered_with_meta_kernels_and_no_cpu_kerne
     import pytest
     with pytest.raises((NotImplementedError, RuntimeError)):        # no CPU kernel: PyTorch's dispatcher says so
         torch.ops.skp_b200.plane_argmax(torch.zeros(2, 8, 8))
+
+
+def test_torch_operators_trace_under_fake_tensors():
+    """The Meta kernels are enough for `make_fx` to trace a graph through the registered operators on a machine without a GPU."""
+    import torch
+    from torch.fx.experimental.proxy_tensor import make_fx
+    import stablekeypoints_b200.torch_ops  # noqa: F401
+
+    def readout(planes):
+        kl, ent, am = torch.ops.skp_b200.plane_stats(planes, 2.0, 1e-5, 1)
+        return torch.ops.skp_b200.rank_ascending(kl, 4), torch.ops.skp_b200.bilinear_upsample(planes, 64)
+
+    gm = make_fx(readout, tracing_mode="fake")(torch.empty(9, 16, 16, device="meta"))
+    targets = [str(n.target) for n in gm.graph.nodes if n.op == "call_function"]
+    assert any("skp_b200.plane_stats" in t for t in targets) and any("skp_b200.rank_ascending" in t for t in targets)
+    assert any("skp_b200.bilinear_upsample" in t for t in targets)
